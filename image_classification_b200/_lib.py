@@ -1,0 +1,99 @@
+"""ctypes binding of libcnx_b200.so — the only way Python reaches the CUDA kernels.
+
+There is deliberately no fallback: if the shared library is missing or the device is not sm_100,
+every op raises.  (The reference loop swallows per-batch exceptions,
+/root/reference/train_advanced_v4.py:277-279, so callers that want loud failures should not rely
+on that loop to surface them; see `train_step.py`.)
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_float, c_int, c_int32, c_int64, c_size_t, c_void_p
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libcnx_b200.so")
+
+
+class CnxError(RuntimeError):
+    """A libcnx_b200 entry point returned a non-zero status."""
+
+
+class MixPlanEntry(ctypes.Structure):
+    """Mirror of `cnx_mix_plan_entry` (include/cnx_b200.h)."""
+
+    _fields_ = [
+        ("mode", c_int32),
+        ("partner", c_int32),
+        ("lam", c_float),
+        ("one_minus_lam", c_float),
+        ("bbx1", c_int32),
+        ("bby1", c_int32),
+        ("bbx2", c_int32),
+        ("bby2", c_int32),
+    ]
+
+
+P = c_void_p
+I = c_int
+I64 = c_int64
+F = c_float
+
+# name -> (restype, argtypes); must list every symbol include/cnx_b200.h declares
+SIGNATURES = {
+    "cnx_version": (I, []),
+    "cnx_last_error_string": (c_char_p, []),
+    "cnx_check_device": (I, []),
+    "cnx_workspace_bytes": (c_size_t, [I, I, I, I, I]),
+    "cnx_prep_block_weights": (I, [P] * 8 + [P] * 7 + [I, P]),
+    "cnx_unfold_block_grads": (I, [P] * 11 + [P] * 7 + [I, P]),
+    "cnx_dwconv_ln_fwd": (I, [P, P, P, P, P, P, I, I, I, I, F, P]),
+    "cnx_dwconv_ln_bwd": (I, [P] * 10 + [I, I, I, I, P, c_size_t, P]),
+    "cnx_gemm_bf16": (I, [P, I64, I, P, I64, I, I, I, I, I, P, I64, P, I64, P, P, I64, P, P]),
+    "cnx_fc1_gelu_fwd": (I, [P, P, P, P, P, I, I, P]),
+    "cnx_fc2_residual_fwd": (I, [P, P, P, P, P, I, I, P]),
+    "cnx_mlp_bwd_dz": (I, [P, P, P, P, P, I, I, P]),
+    "cnx_mlp_bwd_dxhat": (I, [P, P, P, I, I, P]),
+    "cnx_mlp_bwd_wgrad": (I, [P, P, P, P, P, P, I, I, P]),
+    "cnx_mix_batch": (I, [P, P, P, P, P, I, I, I, I, I, P]),
+    "cnx_softce_fwd_bwd": (I, [P, P, P, P, I, I, F, P]),
+    "cnx_ema_lerp_multi": (I, [P, P, P, P, I, I64, F, F, P]),
+    "cnx_ema_chunk_elems": (I, []),
+    "cnx_nchw_f32_to_nhwc_bf16": (I, [P, P, I, I, I, I, P]),
+    "cnx_nhwc_bf16_to_nchw_f32": (I, [P, P, I, I, I, I, P]),
+}
+
+_lib = None
+
+
+def load() -> ctypes.CDLL:
+    """Load libcnx_b200.so (built in-tree by `image_classification_b200.build`)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise CnxError(
+            f"{LIB_PATH} is missing: build it with `python -m image_classification_b200.build` "
+            "(there is no PyTorch/CPU fallback for these ops)")
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (restype, argtypes) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError here = header/library mismatch
+        fn.restype = restype
+        fn.argtypes = argtypes
+    _lib = lib
+    return lib
+
+
+def last_error() -> str:
+    msg = load().cnx_last_error_string()
+    return msg.decode("utf-8", "replace") if msg else ""
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise CnxError(f"{what} failed with status {rc}: {last_error()}")
+
+
+def call(name: str, *args) -> None:
+    """Invoke an int-returning entry point and raise CnxError on failure."""
+    check(getattr(load(), name)(*args), name)

@@ -1,0 +1,181 @@
+"""ConvNeXtBlockB200 — the drop-in `torch.nn.Module` for timm's `ConvNeXtBlock`.
+
+Boundary: same constructor meaning, same parameter/submodule names as timm
+(`conv_dw.{weight,bias}` with `.out_channels` — read at /root/reference/train_advanced_v4.py:108-109,
+`norm.{weight,bias}`, `mlp.fc1.{weight,bias}`, `mlp.fc2.{weight,bias}`, `gamma`), NCHW in / NCHW
+out, fp32 master parameters and fp32 parameter gradients, so `state_dict()`, `EMA`, AdamW,
+`clip_grad_norm_` and checkpoints (/root/reference/train_advanced_v4.py:71,228,466,506-510) see
+nothing new.  All arithmetic happens in libcnx_b200 (five kernels forward incl. weight folding,
+six backward); this file only routes tensors.
+"""
+from __future__ import annotations
+
+import torch
+from torch import nn
+
+from . import _lib, ops
+
+
+class _Mlp(nn.Module):
+    """Parameter container named like timm's `Mlp` (fc1 / act / fc2)."""
+
+    def __init__(self, dim: int, hidden: int):
+        super().__init__()
+        self.fc1 = nn.Linear(dim, hidden)
+        self.act = nn.GELU()
+        self.fc2 = nn.Linear(hidden, dim)
+
+
+class _BlockFn(torch.autograd.Function):
+    """x: [B,C,H,W] bf16, channels_last (physically NHWC).  Returns the same layout."""
+
+    @staticmethod
+    def forward(ctx, x, conv_w, conv_b, norm_w, norm_b, fc1_w, fc1_b, fc2_w, fc2_b, gamma, module):
+        B, C, H, W = x.shape
+        x_nhwc = x.permute(0, 2, 3, 1)
+        assert x_nhwc.is_contiguous() and x.dtype == torch.bfloat16
+        fw = module._folded(conv_w, norm_w, norm_b, fc1_w, fc1_b, fc2_w, fc2_b, gamma)
+        xhat, _mean, rstd = ops.dwconv_ln_fwd(x_nhwc, fw.wt_dw, conv_b.detach())
+        M = B * H * W
+        z, h = ops.fc1_gelu_fwd(xhat.view(M, C), fw.w1f, fw.b1f)
+        y = ops.fc2_residual_fwd(h, fw.w2f, fw.b2f, x_nhwc.reshape(M, C))
+        ctx.save_for_backward(x, xhat, rstd, z, h, norm_w, norm_b, fc1_w, fc2_w, fc2_b, gamma)
+        ctx.fw = fw
+        return y.view(B, H, W, C).permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, xhat, rstd, z, h, norm_w, norm_b, fc1_w, fc2_w, fc2_b, gamma = ctx.saved_tensors
+        fw = ctx.fw
+        B, C, H, W = x.shape
+        M = B * H * W
+        dy_nhwc = dy.permute(0, 2, 3, 1)
+        if dy_nhwc.dtype != torch.bfloat16 or not dy_nhwc.is_contiguous():
+            dy_nhwc = dy_nhwc.to(torch.bfloat16).contiguous()
+        dy2d = dy_nhwc.view(M, C)
+        dz, db1f = ops.mlp_bwd_dz(dy2d, fw.w2fT, z)
+        dxhat = ops.mlp_bwd_dxhat(dz, fw.w1fT)
+        dw2f, dw1f = ops.mlp_bwd_wgrad(dy2d, h, dz, xhat.view(M, C))
+        dx, dwt, dbias, db2f = ops.dwconv_ln_bwd(dxhat.view(B, H, W, C), xhat, rstd,
+                                                 x.permute(0, 2, 3, 1), dy_nhwc, fw.wt_dw)
+        d_conv_w, d_norm_w, d_norm_b, d_fc1_w, d_fc2_w, d_fc2_b, d_gamma = ops.unfold_block_grads(
+            dw1f, db1f, dw2f, db2f, dwt, norm_w.detach(), norm_b.detach(), fc1_w.detach(),
+            fc2_w.detach(), fc2_b.detach(), gamma.detach())
+        return (dx.permute(0, 3, 1, 2), d_conv_w, dbias, d_norm_w, d_norm_b, d_fc1_w, db1f,
+                d_fc2_w, d_fc2_b, d_gamma, None)
+
+
+class _NchwF32ToNhwcBf16(torch.autograd.Function):
+    """fp32 contiguous NCHW -> bf16 channels_last, and the reverse for the gradient."""
+
+    @staticmethod
+    def forward(ctx, x):
+        return ops.nchw_f32_to_nhwc_bf16(x).permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, g):
+        g = g.permute(0, 2, 3, 1)
+        if g.dtype != torch.bfloat16 or not g.is_contiguous():
+            g = g.to(torch.bfloat16).contiguous()
+        return ops.nhwc_bf16_to_nchw_f32(g)
+
+
+class _NhwcBf16ToNchwF32(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, y):
+        return ops.nhwc_bf16_to_nchw_f32(y.permute(0, 2, 3, 1))
+
+    @staticmethod
+    def backward(ctx, g):
+        return ops.nchw_f32_to_nhwc_bf16(g.float().contiguous()).permute(0, 3, 1, 2)
+
+
+class ConvNeXtBlockB200(nn.Module):
+    """dwconv7x7 -> LayerNorm(C) -> Linear C->4C -> GELU -> Linear 4C->C -> *gamma -> +shortcut.
+
+    `forward` accepts what a timm stage hands it:
+      * bf16 channels_last  -> zero-copy, returns bf16 channels_last (the fast path a
+        channels_last bf16 model such as `convnext.ConvNeXtTimmLike` uses end to end);
+      * fp32 contiguous NCHW (the reference's autocast residual stream) -> converted by the
+        library's own transpose kernels on the way in and out, returns fp32 NCHW;
+      * anything else       -> converted with torch ops to bf16 channels_last and back.
+    """
+
+    def __init__(self, dim: int, ls_init_value: float | None = 1e-6, mlp_ratio: int = 4):
+        super().__init__()
+        if mlp_ratio != 4:
+            raise ValueError("ConvNeXtBlockB200 implements the mlp_ratio=4 block only")
+        self.conv_dw = nn.Conv2d(dim, dim, kernel_size=7, padding=3, groups=dim, bias=True)
+        self.norm = nn.LayerNorm(dim, eps=ops.LN_EPS)
+        self.mlp = _Mlp(dim, 4 * dim)
+        init = 1.0 if ls_init_value is None else ls_init_value
+        self.gamma = nn.Parameter(init * torch.ones(dim), requires_grad=ls_init_value is not None)
+        self.drop_path = nn.Identity()   # create_model passes no drop_path_rate (:488-492)
+        self._fold_key = None
+        self._fold = None
+
+    # -- folded bf16 weights, cached per weight version -------------------------------------
+    def _folded(self, *params) -> ops.FoldedWeights:
+        key = tuple((p.data_ptr(), p._version) for p in params)
+        if self._fold is None or key != self._fold_key:
+            self._fold = ops.prep_block_weights(*[p.detach() for p in params])
+            self._fold_key = key
+        return self._fold
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if not x.is_cuda:
+            raise _lib.CnxError("ConvNeXtBlockB200 runs on sm_100a CUDA devices only; use the "
+                                "oracle block for CPU reference computations")
+        mode = 0
+        if x.dtype == torch.bfloat16 and x.permute(0, 2, 3, 1).is_contiguous():
+            xin = x
+        elif x.dtype == torch.float32 and x.is_contiguous():
+            mode = 1
+            xin = _NchwF32ToNhwcBf16.apply(x)
+        else:
+            mode = 2
+            xin = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+            if not xin.permute(0, 2, 3, 1).is_contiguous():   # degenerate 1x1 / C==1 stride cases
+                xin = xin.permute(0, 2, 3, 1).contiguous().permute(0, 3, 1, 2)
+        y = _BlockFn.apply(xin, self.conv_dw.weight, self.conv_dw.bias, self.norm.weight,
+                           self.norm.bias, self.mlp.fc1.weight, self.mlp.fc1.bias,
+                           self.mlp.fc2.weight, self.mlp.fc2.bias, self.gamma, self)
+        if mode == 1:
+            return _NhwcBf16ToNchwF32.apply(y)
+        if mode == 2:
+            return y.to(x.dtype)
+        return y
+
+    @torch.no_grad()
+    def load_from(self, other: nn.Module) -> "ConvNeXtBlockB200":
+        """Copy parameters from any module exposing timm's ConvNeXtBlock attribute names."""
+        self.conv_dw.weight.copy_(other.conv_dw.weight)
+        self.conv_dw.bias.copy_(other.conv_dw.bias)
+        self.norm.weight.copy_(other.norm.weight)
+        self.norm.bias.copy_(other.norm.bias)
+        self.mlp.fc1.weight.copy_(other.mlp.fc1.weight)
+        self.mlp.fc1.bias.copy_(other.mlp.fc1.bias)
+        self.mlp.fc2.weight.copy_(other.mlp.fc2.weight)
+        self.mlp.fc2.bias.copy_(other.mlp.fc2.bias)
+        if getattr(other, "gamma", None) is not None:
+            self.gamma.copy_(other.gamma.reshape(-1))
+        return self
+
+
+def swap_blocks(model: nn.Module) -> int:
+    """Replace every timm-style ConvNeXt block in `model.stages[i].blocks[j]` by a
+    ConvNeXtBlockB200 holding the same weights.  Returns the number of blocks swapped."""
+    n = 0
+    for stage in model.stages:
+        for j, blk in enumerate(stage.blocks):
+            if isinstance(blk, ConvNeXtBlockB200):
+                continue
+            if not all(hasattr(blk, a) for a in ("conv_dw", "norm", "mlp", "gamma")):
+                raise _lib.CnxError(f"block {type(blk).__name__} does not expose timm's "
+                                    "ConvNeXtBlock attributes")
+            dim = blk.conv_dw.out_channels
+            new = ConvNeXtBlockB200(dim).to(blk.conv_dw.weight.device).load_from(blk)
+            new.train(blk.training)
+            stage.blocks[j] = new
+            n += 1
+    return n

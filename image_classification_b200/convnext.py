@@ -1,0 +1,103 @@
+"""A timm-compatible ConvNeXt skeleton to host the block.
+
+`timm` is not installable here, so the object `timm.create_model('convnext_base',
+num_classes=44)` returns (/root/reference/train_advanced_v4.py:488-492) is re-stated with the
+same attribute layout the reference touches: `stem`, `stages[i].downsample`, `stages[i].blocks[j]`,
+`head.{global_pool,norm,flatten,drop,fc}` (:106-111, :131-143).  Stem / downsample / head stay
+plain PyTorch (SURVEY.md §8 f-1 marks them "next"); only the 36 blocks are libcnx_b200 kernels.
+The residual stream is kept channels_last so the NHWC kernels are zero-copy between blocks.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+from .block import ConvNeXtBlockB200
+
+CONVNEXT_CFGS = {
+    "convnext_tiny": dict(depths=(3, 3, 9, 3), dims=(96, 192, 384, 768)),
+    "convnext_small": dict(depths=(3, 3, 27, 3), dims=(96, 192, 384, 768)),
+    "convnext_base": dict(depths=(3, 3, 27, 3), dims=(128, 256, 512, 1024)),
+    "convnext_large": dict(depths=(3, 3, 27, 3), dims=(192, 384, 768, 1536)),
+}
+
+
+class LayerNorm2d(nn.LayerNorm):
+    """LayerNorm over the channel dim of an NCHW tensor (timm's LayerNorm2d)."""
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        x = x.permute(0, 2, 3, 1)
+        x = F.layer_norm(x, self.normalized_shape, self.weight, self.bias, self.eps)
+        return x.permute(0, 3, 1, 2)
+
+
+class ConvNeXtStage(nn.Module):
+    def __init__(self, in_chs: int, out_chs: int, depth: int, stride: int, block_cls, ls_init_value):
+        super().__init__()
+        if in_chs != out_chs or stride > 1:
+            self.downsample = nn.Sequential(
+                LayerNorm2d(in_chs, eps=1e-6),
+                nn.Conv2d(in_chs, out_chs, kernel_size=stride, stride=stride),
+            )
+        else:
+            self.downsample = nn.Identity()
+        self.blocks = nn.Sequential(*[block_cls(out_chs, ls_init_value=ls_init_value)
+                                      for _ in range(depth)])
+
+    def forward(self, x):
+        return self.blocks(self.downsample(x))
+
+
+class _Head(nn.Module):
+    def __init__(self, dim: int, num_classes: int):
+        super().__init__()
+        self.global_pool = nn.AdaptiveAvgPool2d(1)
+        self.norm = LayerNorm2d(dim, eps=1e-6)
+        self.flatten = nn.Flatten(1)
+        self.drop = nn.Dropout(0.0)
+        self.fc = nn.Linear(dim, num_classes)
+
+    def forward(self, x):
+        return self.fc(self.drop(self.flatten(self.norm(self.global_pool(x)))))
+
+
+class ConvNeXtTimmLike(nn.Module):
+    """stem -> 4 stages -> head, attribute-compatible with timm's ConvNeXt."""
+
+    def __init__(self, depths=(3, 3, 27, 3), dims=(128, 256, 512, 1024), num_classes: int = 44,
+                 in_chans: int = 3, ls_init_value: float = 1e-6, block_cls=ConvNeXtBlockB200):
+        super().__init__()
+        self.num_classes = num_classes
+        self.stem = nn.Sequential(nn.Conv2d(in_chans, dims[0], kernel_size=4, stride=4),
+                                  LayerNorm2d(dims[0], eps=1e-6))
+        stages, prev = [], dims[0]
+        for i, (d, c) in enumerate(zip(depths, dims)):
+            stages.append(ConvNeXtStage(prev, c, d, 1 if i == 0 else 2, block_cls, ls_init_value))
+            prev = c
+        self.stages = nn.Sequential(*stages)
+        self.num_features = prev
+        self.head = _Head(prev, num_classes)
+        self.apply(self._init_weights)
+
+    @staticmethod
+    def _init_weights(m):
+        # trunc-normal(0.02) weights, zero bias: timm's and torchvision's ConvNeXt init
+        if isinstance(m, (nn.Conv2d, nn.Linear)):
+            nn.init.trunc_normal_(m.weight, std=0.02)
+            if m.bias is not None:
+                nn.init.zeros_(m.bias)
+
+    def forward_features(self, x):
+        return self.stages(self.stem(x))
+
+    def forward(self, x):
+        return self.head(self.forward_features(x))
+
+
+def create_convnext(name: str = "convnext_base", num_classes: int = 44, block_cls=ConvNeXtBlockB200,
+                    ls_init_value: float = 1e-6) -> ConvNeXtTimmLike:
+    """Stand-in for `timm.create_model(name, pretrained=False, num_classes=...)`."""
+    cfg = CONVNEXT_CFGS[name]
+    return ConvNeXtTimmLike(cfg["depths"], cfg["dims"], num_classes, block_cls=block_cls,
+                            ls_init_value=ls_init_value)

@@ -1,0 +1,78 @@
+// cnx_kernels.h — internal host-side launchers (C++), one per kernel family.
+// The public C ABI in include/cnx_b200.h forwards to these after argument checks.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace cnx {
+
+// ---- dwconv_ln_fwd.cu
+int dwconv_ln_fwd(const void* x, const float* wt, const float* bias, void* xhat, float* mean,
+                  float* rstd, int B, int H, int W, int C, float eps, cudaStream_t stream);
+
+// ---- dwconv_ln_bwd.cu
+size_t dwconv_ln_bwd_workspace_bytes(int B, int H, int W, int C);
+int dwconv_ln_bwd(const void* dxhat, const void* xhat, const float* rstd, const void* x,
+                  const void* dy, const float* wt, void* dx, float* dwt, float* dbias,
+                  float* dy_colsum, int B, int H, int W, int C, void* workspace, size_t ws_bytes,
+                  cudaStream_t stream);
+
+// ---- mlp_gemm.cu  (tcgen05 / TMEM / TMA)
+enum GemmEpilogue : int {
+  EPI_STORE_BF16 = 0,       // D = acc                                  (bf16 out)
+  EPI_BIAS_GELU = 1,        // z = acc + bias[n]; D0 = z, D1 = gelu(z)  (both bf16)
+  EPI_BIAS_RESIDUAL = 2,    // D = acc + bias[n] + R[m,n]               (bf16 out, R bf16)
+  EPI_GELU_GRAD = 3,        // D = acc * gelu'(Z[m,n]); colsum[n] += D  (bf16 out, Z bf16)
+  EPI_STORE_F32 = 4,        // D = acc                                  (fp32 out; weight grads)
+};
+struct GemmArgs {
+  // D[M,N] = A[M,K] * B[N,K]^T.  a_mn_major / b_mn_major: operand stored as [K,M] / [K,N].
+  const void* A; int64_t lda;   // elements between consecutive rows of the STORED matrix
+  const void* B; int64_t ldb;
+  int M, N, K;
+  int a_mn_major, b_mn_major;
+  int epilogue;
+  void* D0; int64_t ldd0;
+  void* D1; int64_t ldd1;       // second output (EPI_BIAS_GELU)
+  const float* bias;            // [N]
+  const void* R; int64_t ldr;   // residual (EPI_BIAS_RESIDUAL) or Z (EPI_GELU_GRAD), bf16
+  float* colsum;                // [N] fp32, atomically accumulated (EPI_GELU_GRAD), may be null
+};
+int gemm_bf16(const GemmArgs& a, cudaStream_t stream);
+
+// ---- elementwise.cu
+struct MixPlanEntry {          // one per sample; integers are bit-exact vs the reference RNG order
+  int32_t mode;                // 0 passthrough, 1 mixup, 2 cutmix
+  int32_t partner;             // index into the batch
+  float lam;                   // float32(lam)
+  float one_minus_lam;         // float32(1 - lam) with the subtraction done in float64
+  int32_t bbx1, bby1, bbx2, bby2;
+};
+int mix_batch(const float* x, const int64_t* labels, const MixPlanEntry* plan, float* out,
+              float* targets, int B, int CH, int H, int W, int num_classes, cudaStream_t stream);
+int softce_fwd_bwd(const float* logits, const float* targets, float* loss, float* dlogits, int B,
+                   int NC, float label_smoothing, cudaStream_t stream);
+int ema_lerp_multi(const void* const* param_ptrs, void* const* shadow_ptrs,
+                   const int64_t* numels, const int64_t* chunk_prefix, int num_tensors,
+                   int64_t total_chunks, float one_minus_decay, float decay, cudaStream_t stream);
+constexpr int kEmaChunkElems = 8192;
+
+// ---- prep.cu : weight folding before the GEMMs and its adjoint after them
+int prep_block_weights(const float* dw_w, const float* ln_w, const float* ln_b, const float* fc1_w,
+                       const float* fc1_b, const float* fc2_w, const float* fc2_b,
+                       const float* ls_gamma, float* wt_dw, void* w1f, void* w1fT, float* b1f,
+                       void* w2f, void* w2fT, float* b2f, int C, cudaStream_t stream);
+int unfold_block_grads(const float* dw1f, const float* db1f, const float* dw2f, const float* db2f,
+                       const float* dwt_dw, const float* ln_w, const float* ln_b,
+                       const float* fc1_w, const float* fc2_w, const float* fc2_b,
+                       const float* ls_gamma, float* d_dw_w, float* d_ln_w, float* d_ln_b,
+                       float* d_fc1_w, float* d_fc2_w, float* d_fc2_b, float* d_ls_gamma, int C,
+                       cudaStream_t stream);
+
+// ---- layout.cu : NCHW fp32 <-> NHWC bf16 at the module boundary
+int nchw_f32_to_nhwc_bf16(const float* src, void* dst, int B, int C, int H, int W,
+                          cudaStream_t stream);
+int nhwc_bf16_to_nchw_f32(const void* src, float* dst, int B, int C, int H, int W,
+                          cudaStream_t stream);
+
+}  // namespace cnx

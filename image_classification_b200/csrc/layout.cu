@@ -1,0 +1,91 @@
+// layout.cu — NCHW fp32 <-> NHWC bf16 conversion at the nn.Module boundary.
+//
+// timm blocks take and return NCHW tensors; the kernels of this library work
+// on NHWC bf16.  A model whose residual stream already is channels_last bf16 never calls these;
+// they exist so ConvNeXtBlockB200 is a drop-in when handed a contiguous fp32 NCHW activation.
+// Per image this is a [C][HW] <-> [HW][C] transpose: 32x32 tiles through padded shared memory,
+// coalesced on both sides.
+#include "cnx_common.cuh"
+#include "cnx_kernels.h"
+
+namespace cnx {
+
+namespace {
+
+__global__ void __launch_bounds__(256)
+nchw_to_nhwc_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int C, int HW) {
+  __shared__ float tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const size_t img = static_cast<size_t>(blockIdx.z) * C * HW;
+  const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+#pragma unroll
+  for (int i = 0; i < 32; i += 8) {
+    const int c = c0 + ty + i, p = p0 + tx;
+    tile[ty + i][tx] = (c < C && p < HW) ? src[img + static_cast<size_t>(c) * HW + p] : 0.f;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 32; i += 8) {
+    const int p = p0 + ty + i, c = c0 + tx;
+    if (p < HW && c < C)
+      dst[img + static_cast<size_t>(p) * C + c] = __float2bfloat16_rn(tile[tx][ty + i]);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+nhwc_to_nchw_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, int C, int HW) {
+  __shared__ float tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const size_t img = static_cast<size_t>(blockIdx.z) * C * HW;
+  const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+#pragma unroll
+  for (int i = 0; i < 32; i += 8) {
+    const int p = p0 + ty + i, c = c0 + tx;
+    tile[ty + i][tx] =
+        (c < C && p < HW) ? __bfloat162float(src[img + static_cast<size_t>(p) * C + c]) : 0.f;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 32; i += 8) {
+    const int c = c0 + ty + i, p = p0 + tx;
+    if (p < HW && c < C) dst[img + static_cast<size_t>(c) * HW + p] = tile[tx][ty + i];
+  }
+}
+
+}  // namespace
+
+int nchw_f32_to_nhwc_bf16(const float* src, void* dst, int B, int C, int H, int W,
+                          cudaStream_t stream) {
+  if (B <= 0 || C <= 0 || H <= 0 || W <= 0 || B > 65535) {
+    set_last_error("nchw_f32_to_nhwc_bf16: bad shape B=%d C=%d H=%d W=%d", B, C, H, W);
+    return CNX_ERR_BAD_SHAPE;
+  }
+  const int HW = H * W;
+  dim3 grid((HW + 31) / 32, (C + 31) / 32, B);
+  nchw_to_nhwc_kernel<<<grid, 256, 0, stream>>>(src, static_cast<__nv_bfloat16*>(dst), C, HW);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_last_error("nchw_f32_to_nhwc_bf16 launch: %s", cudaGetErrorString(e));
+    return CNX_ERR_LAUNCH;
+  }
+  return CNX_OK;
+}
+
+int nhwc_bf16_to_nchw_f32(const void* src, float* dst, int B, int C, int H, int W,
+                          cudaStream_t stream) {
+  if (B <= 0 || C <= 0 || H <= 0 || W <= 0 || B > 65535) {
+    set_last_error("nhwc_bf16_to_nchw_f32: bad shape B=%d C=%d H=%d W=%d", B, C, H, W);
+    return CNX_ERR_BAD_SHAPE;
+  }
+  const int HW = H * W;
+  dim3 grid((HW + 31) / 32, (C + 31) / 32, B);
+  nhwc_to_nchw_kernel<<<grid, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(src), dst, C, HW);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_last_error("nhwc_bf16_to_nchw_f32 launch: %s", cudaGetErrorString(e));
+    return CNX_ERR_LAUNCH;
+  }
+  return CNX_OK;
+}
+
+}  // namespace cnx

@@ -1,0 +1,213 @@
+// prep.cu — weight folding before the block's GEMMs and its adjoint after them.
+//
+// The block computes   y = x + gamma * (fc2(gelu(fc1(ln_w * xhat + ln_b))))
+// Both diagonal scalings are folded into the GEMM weights once per weight version so that no
+// activation-sized elementwise pass exists for them:
+//     W1f = fc1_w * diag(ln_w)      b1f = fc1_b + fc1_w @ ln_b
+//     W2f = diag(gamma) * fc2_w     b2f = gamma * fc2_b
+// (bf16 copies in both orientations: the data-gradient GEMMs want the transposed weight K-major).
+// unfold_block_grads applies the exact adjoint of that map to the gradients of the folded
+// parameters, producing gradients for the nine timm-named parameters of the block.
+#include "cnx_common.cuh"
+#include "cnx_kernels.h"
+
+namespace cnx {
+
+namespace {
+
+// in [R][Cc] fp32 (row-major) -> out [R][Cc] bf16 and outT [Cc][R] bf16, scaled by
+// row_scale[r] (nullable) and col_scale[c] (nullable).  32x32 tile through padded smem.
+__global__ void __launch_bounds__(256)
+scale_cast_transpose_kernel(const float* __restrict__ in, const float* __restrict__ row_scale,
+                            const float* __restrict__ col_scale, __nv_bfloat16* __restrict__ out,
+                            __nv_bfloat16* __restrict__ outT, int R, int Cc) {
+  __shared__ float tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  const int c = blockIdx.x * 32 + tx;
+#pragma unroll
+  for (int i = 0; i < 32; i += 8) {
+    const int r = blockIdx.y * 32 + ty + i;
+    float v = 0.f;
+    if (r < R && c < Cc) {
+      v = in[static_cast<size_t>(r) * Cc + c];
+      if (row_scale) v *= row_scale[r];
+      if (col_scale) v *= col_scale[c];
+      out[static_cast<size_t>(r) * Cc + c] = __float2bfloat16_rn(v);
+    }
+    tile[ty + i][tx] = v;
+  }
+  __syncthreads();
+  const int r2 = blockIdx.y * 32 + tx;  // transposed: threads run along original rows
+#pragma unroll
+  for (int i = 0; i < 32; i += 8) {
+    const int c2 = blockIdx.x * 32 + ty + i;
+    if (r2 < R && c2 < Cc)
+      outT[static_cast<size_t>(c2) * R + r2] = __float2bfloat16_rn(tile[tx][ty + i]);
+  }
+}
+
+// b1f[j] = fc1_b[j] + sum_c fc1_w[j,c] * ln_b[c]      (one warp per row j)
+__global__ void __launch_bounds__(256)
+fold_bias1_kernel(const float* __restrict__ w, const float* __restrict__ b,
+                  const float* __restrict__ ln_b, float* __restrict__ b1f, int R, int Cc) {
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= R) return;
+  float s = 0.f;
+  for (int c = lane; c < Cc; c += 32) s = fmaf(w[static_cast<size_t>(row) * Cc + c], ln_b[c], s);
+  s = warp_sum(s);
+  if (lane == 0) b1f[row] = b[row] + s;
+}
+
+// wt_dw[t][c] = dw_w[c][t];  b2f[c] = gamma[c] * fc2_b[c]
+__global__ void __launch_bounds__(256)
+prep_small_kernel(const float* __restrict__ dw_w, const float* __restrict__ gamma,
+                  const float* __restrict__ fc2_b, float* __restrict__ wt_dw,
+                  float* __restrict__ b2f, int C) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < 49 * C) {
+    const int t = i / C, c = i % C;
+    wt_dw[i] = dw_w[c * 49 + t];
+  }
+  if (i < C) b2f[i] = gamma[i] * fc2_b[i];
+}
+
+// fc1 side of the adjoint.  grid (ceil(C/32), row_splits), block 32x8.
+//   d_fc1_w[j,c] = dW1f[j,c]*ln_w[c] + db1f[j]*ln_b[c]
+//   d_ln_w[c]   += sum_j dW1f[j,c]*fc1_w[j,c]        d_ln_b[c] += sum_j db1f[j]*fc1_w[j,c]
+__global__ void __launch_bounds__(256)
+unfold_fc1_kernel(const float* __restrict__ dw1f, const float* __restrict__ db1f,
+                  const float* __restrict__ fc1_w, const float* __restrict__ ln_w,
+                  const float* __restrict__ ln_b, float* __restrict__ d_fc1_w,
+                  float* __restrict__ d_ln_w, float* __restrict__ d_ln_b, int R, int Cc,
+                  int rows_per_block) {
+  __shared__ float s1[8][33], s2[8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + tx;
+  const int r_begin = blockIdx.y * rows_per_block;
+  const int r_end = min(R, r_begin + rows_per_block);
+  float a1 = 0.f, a2 = 0.f;
+  if (c < Cc) {
+    const float g = ln_w[c], bt = ln_b[c];
+    for (int r = r_begin + ty; r < r_end; r += 8) {
+      const size_t idx = static_cast<size_t>(r) * Cc + c;
+      const float dw = dw1f[idx], w = fc1_w[idx], db = db1f[r];
+      d_fc1_w[idx] = fmaf(dw, g, db * bt);
+      a1 = fmaf(dw, w, a1);
+      a2 = fmaf(db, w, a2);
+    }
+  }
+  s1[ty][tx] = a1;
+  s2[ty][tx] = a2;
+  __syncthreads();
+  if (ty == 0 && c < Cc) {
+#pragma unroll
+    for (int i = 1; i < 8; ++i) { a1 += s1[i][tx]; a2 += s2[i][tx]; }
+    atomicAdd(d_ln_w + c, a1);
+    atomicAdd(d_ln_b + c, a2);
+  }
+}
+
+// fc2 side of the adjoint: one CTA per output channel c (row of fc2_w [C][4C]).
+//   d_fc2_w[c,j] = gamma[c]*dW2f[c,j]   d_fc2_b[c] = gamma[c]*db2f[c]
+//   d_gamma[c]   = sum_j dW2f[c,j]*fc2_w[c,j] + db2f[c]*fc2_b[c]
+__global__ void __launch_bounds__(256)
+unfold_fc2_kernel(const float* __restrict__ dw2f, const float* __restrict__ db2f,
+                  const float* __restrict__ fc2_w, const float* __restrict__ fc2_b,
+                  const float* __restrict__ gamma, float* __restrict__ d_fc2_w,
+                  float* __restrict__ d_fc2_b, float* __restrict__ d_gamma, int Cc, int R4) {
+  __shared__ float sred[8];
+  const int c = blockIdx.x;
+  const float g = gamma[c];
+  float a = 0.f;
+  for (int j = threadIdx.x; j < R4; j += 256) {
+    const size_t idx = static_cast<size_t>(c) * R4 + j;
+    const float dw = dw2f[idx];
+    d_fc2_w[idx] = g * dw;
+    a = fmaf(dw, fc2_w[idx], a);
+  }
+  a = warp_sum(a);
+  if ((threadIdx.x & 31) == 0) sred[threadIdx.x >> 5] = a;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += sred[i];
+    d_gamma[c] = fmaf(db2f[c], fc2_b[c], t);
+    d_fc2_b[c] = g * db2f[c];
+  }
+}
+
+// d_dw_w[c][t] = dwt_dw[t][c]
+__global__ void __launch_bounds__(256)
+unfold_dw_kernel(const float* __restrict__ dwt, float* __restrict__ d_dw_w, int C) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < 49 * C) {
+    const int c = i / 49, t = i % 49;
+    d_dw_w[i] = dwt[t * C + c];
+  }
+}
+
+int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_last_error("%s launch: %s", what, cudaGetErrorString(e));
+    return CNX_ERR_LAUNCH;
+  }
+  return CNX_OK;
+}
+
+}  // namespace
+
+int prep_block_weights(const float* dw_w, const float* ln_w, const float* ln_b, const float* fc1_w,
+                       const float* fc1_b, const float* fc2_w, const float* fc2_b,
+                       const float* ls_gamma, float* wt_dw, void* w1f, void* w1fT, float* b1f,
+                       void* w2f, void* w2fT, float* b2f, int C, cudaStream_t stream) {
+  if (C <= 0 || (C % 8) != 0) {
+    set_last_error("prep_block_weights: C=%d must be a positive multiple of 8", C);
+    return CNX_ERR_BAD_SHAPE;
+  }
+  const int R4 = 4 * C;
+  {  // fc1_w [4C][C], columns scaled by ln_w
+    dim3 grid((C + 31) / 32, (R4 + 31) / 32);
+    scale_cast_transpose_kernel<<<grid, 256, 0, stream>>>(
+        fc1_w, nullptr, ln_w, static_cast<__nv_bfloat16*>(w1f), static_cast<__nv_bfloat16*>(w1fT),
+        R4, C);
+  }
+  {  // fc2_w [C][4C], rows scaled by gamma
+    dim3 grid((R4 + 31) / 32, (C + 31) / 32);
+    scale_cast_transpose_kernel<<<grid, 256, 0, stream>>>(
+        fc2_w, ls_gamma, nullptr, static_cast<__nv_bfloat16*>(w2f),
+        static_cast<__nv_bfloat16*>(w2fT), C, R4);
+  }
+  fold_bias1_kernel<<<(R4 + 7) / 8, 256, 0, stream>>>(fc1_w, fc1_b, ln_b, b1f, R4, C);
+  prep_small_kernel<<<(49 * C + 255) / 256, 256, 0, stream>>>(dw_w, ls_gamma, fc2_b, wt_dw, b2f, C);
+  return check_launch("prep_block_weights");
+}
+
+int unfold_block_grads(const float* dw1f, const float* db1f, const float* dw2f, const float* db2f,
+                       const float* dwt_dw, const float* ln_w, const float* ln_b,
+                       const float* fc1_w, const float* fc2_w, const float* fc2_b,
+                       const float* ls_gamma, float* d_dw_w, float* d_ln_w, float* d_ln_b,
+                       float* d_fc1_w, float* d_fc2_w, float* d_fc2_b, float* d_ls_gamma, int C,
+                       cudaStream_t stream) {
+  if (C <= 0 || (C % 8) != 0) {
+    set_last_error("unfold_block_grads: C=%d must be a positive multiple of 8", C);
+    return CNX_ERR_BAD_SHAPE;
+  }
+  const int R4 = 4 * C;
+  cudaMemsetAsync(d_ln_w, 0, sizeof(float) * C, stream);
+  cudaMemsetAsync(d_ln_b, 0, sizeof(float) * C, stream);
+  {
+    const int rows_per_block = 128;
+    dim3 grid((C + 31) / 32, (R4 + rows_per_block - 1) / rows_per_block);
+    unfold_fc1_kernel<<<grid, 256, 0, stream>>>(dw1f, db1f, fc1_w, ln_w, ln_b, d_fc1_w, d_ln_w,
+                                                d_ln_b, R4, C, rows_per_block);
+  }
+  unfold_fc2_kernel<<<C, 256, 0, stream>>>(dw2f, db2f, fc2_w, fc2_b, ls_gamma, d_fc2_w, d_fc2_b,
+                                           d_ls_gamma, C, R4);
+  unfold_dw_kernel<<<(49 * C + 255) / 256, 256, 0, stream>>>(dwt_dw, d_dw_w, C);
+  return check_launch("unfold_block_grads");
+}
+
+}  // namespace cnx

@@ -1,0 +1,89 @@
+"""EMA of the parameters as one multi-tensor launch.
+
+Same interface and semantics as the reference's `EMA` class
+(/root/reference/train_advanced_v4.py:62-94): `register()` clones every `requires_grad`
+parameter into `shadow[name]`, `update()` sets `shadow = (1 - decay) * param + decay * shadow`,
+`apply_shadow()` / `restore()` swap `param.data` for evaluation.  The reference's `update()` is a
+Python loop of ~3 elementwise kernels + 2 allocations per tensor (~1 400 launches per optimizer
+step for ConvNeXt-Base); here it is a single kernel over a device-side pointer table, and the
+result is bit-identical (separately rounded multiplies and add, like the eager expression).
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import _lib
+
+
+class EMAB200:
+    def __init__(self, model: torch.nn.Module, decay: float):
+        self.model = model
+        self.decay = decay
+        self.shadow: dict[str, torch.Tensor] = {}
+        self.backup: dict[str, torch.Tensor] = {}
+        self._table = None
+        self._table_key = None
+        self.register()
+
+    # ---- reference API -------------------------------------------------------------------
+    def register(self):
+        for name, param in self.model.named_parameters():
+            if param.requires_grad:
+                self.shadow[name] = param.data.clone()
+        self._table = None
+
+    def update(self):
+        params, shadows = [], []
+        for name, param in self.model.named_parameters():
+            if param.requires_grad:
+                assert name in self.shadow
+                params.append(param.data)
+                shadows.append(self.shadow[name])
+        if not params:
+            return
+        dev = params[0].device
+        if dev.type != "cuda":
+            raise _lib.CnxError("EMAB200.update: parameters must live on a CUDA device")
+        key = tuple(p.data_ptr() for p in params) + tuple(s.data_ptr() for s in shadows)
+        if self._table is None or self._table_key != key:
+            self._build_table(params, shadows, dev)
+            self._table_key = key
+        pp, sp, numels, prefix, T, total = self._table
+        # the reference evaluates (1.0 - decay) in float64, then the product in float32
+        omd = float(np.float32(1.0 - self.decay))
+        d = float(np.float32(self.decay))
+        _lib.call("cnx_ema_lerp_multi", pp.data_ptr(), sp.data_ptr(), numels.data_ptr(),
+                  prefix.data_ptr(), T, total, omd, d, torch.cuda.current_stream(dev).cuda_stream)
+
+    def apply_shadow(self):
+        for name, param in self.model.named_parameters():
+            if param.requires_grad:
+                assert name in self.shadow
+                self.backup[name] = param.data
+                param.data = self.shadow[name]
+
+    def restore(self):
+        for name, param in self.model.named_parameters():
+            if param.requires_grad:
+                assert name in self.backup
+                param.data = self.backup[name]
+        self.backup = {}
+
+    # ---- device table --------------------------------------------------------------------
+    def _build_table(self, params, shadows, dev):
+        chunk = _lib.load().cnx_ema_chunk_elems()
+        for p, s in zip(params, shadows):
+            if p.dtype != torch.float32 or s.dtype != torch.float32:
+                raise _lib.CnxError("EMAB200: parameters and shadows must be float32")
+            if not p.is_contiguous() or not s.is_contiguous():
+                raise _lib.CnxError("EMAB200: parameters and shadows must be contiguous")
+        numel = np.array([p.numel() for p in params], dtype=np.int64)
+        nchunks = (numel + chunk - 1) // chunk
+        prefix = np.zeros(len(params) + 1, dtype=np.int64)
+        np.cumsum(nchunks, out=prefix[1:])
+        pp = np.array([p.data_ptr() for p in params], dtype=np.int64)
+        sp = np.array([s.data_ptr() for s in shadows], dtype=np.int64)
+        to_dev = lambda a: torch.from_numpy(a).to(dev)
+        self._table = (to_dev(pp), to_dev(sp), to_dev(numel), to_dev(prefix), len(params),
+                       int(prefix[-1]))

@@ -1,0 +1,103 @@
+"""Batch-level MixUp/CutMix: host planner (integers bit-exact with the reference RNG order) +
+one fused device kernel.
+
+Mirrors `MixUpCutMixDataset` (/root/reference/dataset.py:70-190): same constructor arguments,
+same per-sample RNG call order (`random()` gate :167, `randint(len)` partner :175, `random()`
+mode :185, `beta` :83/:112, `randint(W)` then `randint(H)` :135-136), same box clipping
+(:138-141), same lambda re-adjustment (:152).  The reference mixes one sample at a time on CPU
+DataLoader workers and draws the partner from the whole dataset; here the "dataset" is the batch
+already resident in HBM (partners are drawn inside the local micro-batch).
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+
+import numpy as np
+import torch
+
+from . import _lib
+
+MODE_PASS, MODE_MIXUP, MODE_CUTMIX = 0, 1, 2
+
+PLAN_DTYPE = np.dtype([
+    ("mode", np.int32), ("partner", np.int32), ("lam", np.float32), ("one_minus_lam", np.float32),
+    ("bbx1", np.int32), ("bby1", np.int32), ("bbx2", np.int32), ("bby2", np.int32),
+])
+assert PLAN_DTYPE.itemsize == ctypes.sizeof(_lib.MixPlanEntry) == 32
+
+
+def plan_mix_batch(batch_size: int, height: int, width: int, *, mixup_alpha: float = 1.0,
+                   cutmix_alpha: float = 1.0, prob: float = 0.5, rng=None) -> np.ndarray:
+    """Draw the per-sample mixing plan with the reference's RNG call order.
+
+    `rng` is anything with legacy `random()/randint()/beta()` (the `np.random` module itself, which
+    is what the reference uses, or a `np.random.RandomState`).  Returns a structured array of
+    `PLAN_DTYPE`; `lam` is the float64 value rounded to float32 exactly as `tensor * lam` does.
+    """
+    rng = np.random if rng is None else rng
+    plan = np.zeros(batch_size, dtype=PLAN_DTYPE)
+    H, W = height, width
+    for i in range(batch_size):
+        e = plan[i]
+        if rng.random() > prob:                      # dataset.py:167
+            e["mode"], e["partner"], e["lam"], e["one_minus_lam"] = MODE_PASS, i, 1.0, 0.0
+            continue
+        e["partner"] = rng.randint(batch_size)       # dataset.py:175
+        if rng.random() < 0.5 and mixup_alpha > 0:   # dataset.py:185
+            lam = rng.beta(mixup_alpha, mixup_alpha)  # dataset.py:83
+            e["mode"] = MODE_MIXUP
+        else:
+            lam = rng.beta(cutmix_alpha, cutmix_alpha) if cutmix_alpha > 0 else 1  # :112-114
+            cut_rat = np.sqrt(1.0 - lam)             # dataset.py:131
+            cut_w = int(W * cut_rat)
+            cut_h = int(H * cut_rat)
+            cx = rng.randint(W)                      # dataset.py:135 (x first, then y)
+            cy = rng.randint(H)
+            bbx1 = int(np.clip(cx - cut_w // 2, 0, W))
+            bby1 = int(np.clip(cy - cut_h // 2, 0, H))
+            bbx2 = int(np.clip(cx + cut_w // 2, 0, W))
+            bby2 = int(np.clip(cy + cut_h // 2, 0, H))
+            lam = 1 - ((bbx2 - bbx1) * (bby2 - bby1) / (W * H))   # dataset.py:152
+            e["mode"] = MODE_CUTMIX
+            e["bbx1"], e["bby1"], e["bbx2"], e["bby2"] = bbx1, bby1, bbx2, bby2
+        e["lam"] = np.float32(lam)
+        e["one_minus_lam"] = np.float32(1 - lam)     # the subtraction happens in float64
+    return plan
+
+
+def mix_batch(images: torch.Tensor, labels: torch.Tensor, plan: np.ndarray, num_classes: int):
+    """Apply `plan` on the device: images [B,CH,H,W] fp32 (NCHW), labels [B] int64 ->
+    (mixed images, soft targets [B,num_classes] fp32)."""
+    if not images.is_cuda:
+        raise _lib.CnxError("mix_batch: images must be a CUDA tensor (no CPU path)")
+    if images.dtype != torch.float32 or not images.is_contiguous():
+        raise _lib.CnxError("mix_batch: images must be contiguous float32 NCHW")
+    B, CH, H, W = images.shape
+    if plan.dtype != PLAN_DTYPE or plan.shape != (B,):
+        raise _lib.CnxError("mix_batch: plan must come from plan_mix_batch for this batch size")
+    labels = labels.to(device=images.device, dtype=torch.int64).contiguous()
+    plan_dev = torch.from_numpy(plan.view(np.uint8).reshape(-1).copy()).to(images.device,
+                                                                            non_blocking=True)
+    out = torch.empty_like(images)
+    targets = torch.empty(B, num_classes, device=images.device, dtype=torch.float32)
+    _lib.call("cnx_mix_batch", images.data_ptr(), labels.data_ptr(), plan_dev.data_ptr(),
+              out.data_ptr(), targets.data_ptr(), B, CH, H, W, num_classes,
+              torch.cuda.current_stream(images.device).cuda_stream)
+    return out, targets
+
+
+@dataclass
+class BatchMixUpCutMix:
+    """Drop-in for the role of `MixUpCutMixDataset`, applied to a whole device-resident batch."""
+
+    mixup_alpha: float = 1.0
+    cutmix_alpha: float = 1.0
+    prob: float = 0.5
+    num_classes: int | None = None
+
+    def __call__(self, images: torch.Tensor, labels: torch.Tensor, rng=None):
+        B, _, H, W = images.shape
+        plan = plan_mix_batch(B, H, W, mixup_alpha=self.mixup_alpha, cutmix_alpha=self.cutmix_alpha,
+                              prob=self.prob, rng=rng)
+        return mix_batch(images, labels, plan, self.num_classes)

@@ -1,0 +1,218 @@
+"""Tensor-level wrappers over the C ABI: argument checks, output allocation (by PyTorch's caching
+allocator — the library owns no memory), current-stream plumbing.  Nothing here computes."""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import torch
+
+from . import _lib
+
+LN_EPS = 1e-6  # timm ConvNeXtBlock norm eps
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _chk(t: torch.Tensor, dtype: torch.dtype, name: str) -> torch.Tensor:
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise _lib.CnxError(f"{name}: expected a CUDA tensor (libcnx_b200 has no CPU path)")
+    if t.dtype != dtype:
+        raise _lib.CnxError(f"{name}: expected dtype {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise _lib.CnxError(f"{name}: expected a contiguous tensor, got strides {t.stride()}")
+    return t
+
+
+def _p(t):
+    return None if t is None else t.data_ptr()
+
+
+# ------------------------------------------------------------------ weight folding
+@dataclass
+class FoldedWeights:
+    """Output of cnx_prep_block_weights for one block (see csrc/prep.cu)."""
+
+    wt_dw: torch.Tensor   # [49, C] fp32
+    w1f: torch.Tensor     # [4C, C] bf16
+    w1fT: torch.Tensor    # [C, 4C] bf16
+    b1f: torch.Tensor     # [4C] fp32
+    w2f: torch.Tensor     # [C, 4C] bf16
+    w2fT: torch.Tensor    # [4C, C] bf16
+    b2f: torch.Tensor     # [C] fp32
+
+
+def prep_block_weights(conv_dw_w, norm_w, norm_b, fc1_w, fc1_b, fc2_w, fc2_b, gamma) -> FoldedWeights:
+    C = gamma.numel()
+    f32 = torch.float32
+    for n, t in (("conv_dw.weight", conv_dw_w), ("norm.weight", norm_w), ("norm.bias", norm_b),
+                 ("mlp.fc1.weight", fc1_w), ("mlp.fc1.bias", fc1_b), ("mlp.fc2.weight", fc2_w),
+                 ("mlp.fc2.bias", fc2_b), ("gamma", gamma)):
+        _chk(t, f32, n)
+    dev = gamma.device
+    fw = FoldedWeights(
+        wt_dw=torch.empty(49, C, device=dev, dtype=f32),
+        w1f=torch.empty(4 * C, C, device=dev, dtype=torch.bfloat16),
+        w1fT=torch.empty(C, 4 * C, device=dev, dtype=torch.bfloat16),
+        b1f=torch.empty(4 * C, device=dev, dtype=f32),
+        w2f=torch.empty(C, 4 * C, device=dev, dtype=torch.bfloat16),
+        w2fT=torch.empty(4 * C, C, device=dev, dtype=torch.bfloat16),
+        b2f=torch.empty(C, device=dev, dtype=f32),
+    )
+    _lib.call("cnx_prep_block_weights", _p(conv_dw_w), _p(norm_w), _p(norm_b), _p(fc1_w),
+              _p(fc1_b), _p(fc2_w), _p(fc2_b), _p(gamma), _p(fw.wt_dw), _p(fw.w1f), _p(fw.w1fT),
+              _p(fw.b1f), _p(fw.w2f), _p(fw.w2fT), _p(fw.b2f), C, _stream(gamma))
+    return fw
+
+
+def unfold_block_grads(dw1f, db1f, dw2f, db2f, dwt_dw, norm_w, norm_b, fc1_w, fc2_w, fc2_b, gamma):
+    """-> (d_conv_dw_w [C,1,7,7], d_norm_w, d_norm_b, d_fc1_w, d_fc2_w, d_fc2_b, d_gamma)."""
+    C = gamma.numel()
+    dev, f32 = gamma.device, torch.float32
+    d_dw = torch.empty(C, 1, 7, 7, device=dev, dtype=f32)
+    d_nw = torch.empty(C, device=dev, dtype=f32)
+    d_nb = torch.empty(C, device=dev, dtype=f32)
+    d_f1 = torch.empty(4 * C, C, device=dev, dtype=f32)
+    d_f2 = torch.empty(C, 4 * C, device=dev, dtype=f32)
+    d_f2b = torch.empty(C, device=dev, dtype=f32)
+    d_g = torch.empty(C, device=dev, dtype=f32)
+    _lib.call("cnx_unfold_block_grads", _p(dw1f), _p(db1f), _p(dw2f), _p(db2f), _p(dwt_dw),
+              _p(norm_w), _p(norm_b), _p(fc1_w), _p(fc2_w), _p(fc2_b), _p(gamma), _p(d_dw),
+              _p(d_nw), _p(d_nb), _p(d_f1), _p(d_f2), _p(d_f2b), _p(d_g), C, _stream(gamma))
+    return d_dw, d_nw, d_nb, d_f1, d_f2, d_f2b, d_g
+
+
+# ------------------------------------------------------------------ dwconv + LN
+def dwconv_ln_fwd(x_nhwc: torch.Tensor, wt_dw: torch.Tensor, bias: torch.Tensor, eps: float = LN_EPS):
+    """x [B,H,W,C] bf16 -> (xhat [B,H,W,C] bf16, mean [B*H*W] f32, rstd [B*H*W] f32)."""
+    _chk(x_nhwc, torch.bfloat16, "x")
+    _chk(wt_dw, torch.float32, "wt_dw")
+    _chk(bias, torch.float32, "conv_dw.bias")
+    B, H, W, C = x_nhwc.shape
+    xhat = torch.empty_like(x_nhwc)
+    mean = torch.empty(B * H * W, device=x_nhwc.device, dtype=torch.float32)
+    rstd = torch.empty_like(mean)
+    _lib.call("cnx_dwconv_ln_fwd", _p(x_nhwc), _p(wt_dw), _p(bias), _p(xhat), _p(mean), _p(rstd),
+              B, H, W, C, eps, _stream(x_nhwc))
+    return xhat, mean, rstd
+
+
+def dwconv_ln_bwd(dxhat, xhat, rstd, x_nhwc, dy, wt_dw):
+    """-> (dx [B,H,W,C] bf16, dwt [49,C] f32, dbias [C] f32, dy_colsum [C] f32)."""
+    for n, t in (("dxhat", dxhat), ("xhat", xhat), ("x", x_nhwc), ("dy", dy)):
+        _chk(t, torch.bfloat16, n)
+    _chk(rstd, torch.float32, "rstd")
+    _chk(wt_dw, torch.float32, "wt_dw")
+    B, H, W, C = x_nhwc.shape
+    dev = x_nhwc.device
+    dx = torch.empty_like(x_nhwc)
+    dwt = torch.empty(49, C, device=dev, dtype=torch.float32)
+    dbias = torch.empty(C, device=dev, dtype=torch.float32)
+    dycs = torch.empty(C, device=dev, dtype=torch.float32)
+    _lib.call("cnx_dwconv_ln_bwd", _p(dxhat), _p(xhat), _p(rstd), _p(x_nhwc), _p(dy), _p(wt_dw),
+              _p(dx), _p(dwt), _p(dbias), _p(dycs), B, H, W, C, None, 0, _stream(x_nhwc))
+    return dx, dwt, dbias, dycs
+
+
+# ------------------------------------------------------------------ MLP GEMMs
+EPI_STORE_BF16, EPI_BIAS_GELU, EPI_BIAS_RESIDUAL, EPI_GELU_GRAD, EPI_STORE_F32 = range(5)
+
+
+def gemm_bf16(A, B, *, a_mn_major=False, b_mn_major=False, epilogue=EPI_STORE_BF16, bias=None,
+              R=None, colsum=None):
+    """D = epilogue(A @ B^T); A is [M,K] (or [K,M] if a_mn_major), B is [N,K] (or [K,N])."""
+    _chk(A, torch.bfloat16, "A")
+    _chk(B, torch.bfloat16, "B")
+    if a_mn_major:
+        K, M = A.shape
+    else:
+        M, K = A.shape
+    if b_mn_major:
+        Kb, N = B.shape
+    else:
+        N, Kb = B.shape
+    if K != Kb:
+        raise _lib.CnxError(f"gemm_bf16: K mismatch {K} vs {Kb}")
+    dev = A.device
+    out_dtype = torch.float32 if epilogue == EPI_STORE_F32 else torch.bfloat16
+    if epilogue == EPI_STORE_F32:
+        D0 = torch.zeros(M, N, device=dev, dtype=out_dtype)
+    else:
+        D0 = torch.empty(M, N, device=dev, dtype=out_dtype)
+    D1 = torch.empty(M, N, device=dev, dtype=torch.bfloat16) if epilogue == EPI_BIAS_GELU else None
+    if bias is not None:
+        _chk(bias, torch.float32, "bias")
+    if R is not None:
+        _chk(R, torch.bfloat16, "R")
+    if colsum is not None:
+        _chk(colsum, torch.float32, "colsum")
+    _lib.call("cnx_gemm_bf16", _p(A), A.shape[1], int(a_mn_major), _p(B), B.shape[1],
+              int(b_mn_major), M, N, K, epilogue, _p(D0), N, _p(D1), N, _p(bias), _p(R),
+              N if R is not None else 0, _p(colsum), _stream(A))
+    return (D0, D1) if D1 is not None else D0
+
+
+def fc1_gelu_fwd(xhat2d, w1f, b1f):
+    M, C = xhat2d.shape
+    z = torch.empty(M, 4 * C, device=xhat2d.device, dtype=torch.bfloat16)
+    h = torch.empty_like(z)
+    _lib.call("cnx_fc1_gelu_fwd", _p(_chk(xhat2d, torch.bfloat16, "xhat")),
+              _p(_chk(w1f, torch.bfloat16, "w1f")), _p(_chk(b1f, torch.float32, "b1f")), _p(z),
+              _p(h), M, C, _stream(xhat2d))
+    return z, h
+
+
+def fc2_residual_fwd(h, w2f, b2f, x2d):
+    M, C = x2d.shape
+    y = torch.empty_like(x2d)
+    _lib.call("cnx_fc2_residual_fwd", _p(_chk(h, torch.bfloat16, "h")),
+              _p(_chk(w2f, torch.bfloat16, "w2f")), _p(_chk(b2f, torch.float32, "b2f")),
+              _p(_chk(x2d, torch.bfloat16, "x")), _p(y), M, C, _stream(x2d))
+    return y
+
+
+def mlp_bwd_dz(dy2d, w2fT, z):
+    M, C = dy2d.shape
+    dz = torch.empty_like(z)
+    db1f = torch.zeros(4 * C, device=z.device, dtype=torch.float32)
+    _lib.call("cnx_mlp_bwd_dz", _p(_chk(dy2d, torch.bfloat16, "dy")),
+              _p(_chk(w2fT, torch.bfloat16, "w2fT")), _p(_chk(z, torch.bfloat16, "z")), _p(dz),
+              _p(db1f), M, C, _stream(z))
+    return dz, db1f
+
+
+def mlp_bwd_dxhat(dz, w1fT):
+    M, C4 = dz.shape
+    C = C4 // 4
+    dxhat = torch.empty(M, C, device=dz.device, dtype=torch.bfloat16)
+    _lib.call("cnx_mlp_bwd_dxhat", _p(_chk(dz, torch.bfloat16, "dz")),
+              _p(_chk(w1fT, torch.bfloat16, "w1fT")), _p(dxhat), M, C, _stream(dz))
+    return dxhat
+
+
+def mlp_bwd_wgrad(dy2d, h, dz, xhat2d):
+    M, C = dy2d.shape
+    dw2f = torch.zeros(C, 4 * C, device=h.device, dtype=torch.float32)
+    dw1f = torch.zeros(4 * C, C, device=h.device, dtype=torch.float32)
+    _lib.call("cnx_mlp_bwd_wgrad", _p(_chk(dy2d, torch.bfloat16, "dy")),
+              _p(_chk(h, torch.bfloat16, "h")), _p(_chk(dz, torch.bfloat16, "dz")),
+              _p(_chk(xhat2d, torch.bfloat16, "xhat")), _p(dw2f), _p(dw1f), M, C, _stream(h))
+    return dw2f, dw1f
+
+
+# ------------------------------------------------------------------ layout
+def nchw_f32_to_nhwc_bf16(x: torch.Tensor) -> torch.Tensor:
+    _chk(x, torch.float32, "x")
+    B, C, H, W = x.shape
+    out = torch.empty(B, H, W, C, device=x.device, dtype=torch.bfloat16)
+    _lib.call("cnx_nchw_f32_to_nhwc_bf16", _p(x), _p(out), B, C, H, W, _stream(x))
+    return out
+
+
+def nhwc_bf16_to_nchw_f32(x: torch.Tensor) -> torch.Tensor:
+    _chk(x, torch.bfloat16, "x")
+    B, H, W, C = x.shape
+    out = torch.empty(B, C, H, W, device=x.device, dtype=torch.float32)
+    _lib.call("cnx_nhwc_bf16_to_nchw_f32", _p(x), _p(out), B, C, H, W, _stream(x))
+    return out

@@ -1,0 +1,157 @@
+/* cnx_b200.h — public C ABI of libcnx_b200.so (sm_100a only, no fallback path).
+ *
+ * The reference (Garhlz/image_classification) has no FFI of its own: its hot path is reached
+ * through torch.nn.Module calls into the un-vendored `timm` package.  Each entry
+ * point below therefore cites the reference call site / third-party op sequence it replaces.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless stated otherwise; the library never allocates,
+ *     frees or retains device memory; all work is enqueued on `stream` (a cudaStream_t) with no
+ *     internal synchronisation;
+ *   - activations are NHWC bf16, i.e. row-major [M, C] with M = B*H*W tokens; parameters and
+ *     their gradients are fp32 in the exact shapes timm uses;
+ *   - return value: 0 on success, negative cnx_status otherwise (never throws, never exits);
+ *     cnx_last_error_string() gives the reason for the calling thread;
+ *   - C must be a multiple of 8 and splittable into <= 8 equal slabs of <= 128 channels
+ *     (ConvNeXt-T/S/B/L/XL widths all qualify).
+ */
+#ifndef CNX_B200_H_
+#define CNX_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum cnx_status {
+  CNX_OK = 0,
+  CNX_ERR_BAD_SHAPE = -1,
+  CNX_ERR_BAD_ARG = -2,
+  CNX_ERR_WORKSPACE = -3,
+  CNX_ERR_NOT_SM100 = -4,
+  CNX_ERR_DRIVER = -5,
+  CNX_ERR_LAUNCH = -6
+} cnx_status;
+
+typedef enum cnx_op {
+  CNX_OP_DWCONV_LN_FWD = 0,
+  CNX_OP_DWCONV_LN_BWD = 1,
+  CNX_OP_MLP_FWD = 2,
+  CNX_OP_MLP_BWD = 3,
+  CNX_OP_MIX_BATCH = 4,
+  CNX_OP_SOFTCE = 5,
+  CNX_OP_EMA = 6
+} cnx_op;
+
+/* GEMM epilogues of cnx_gemm_bf16 (the MLP entry points below are thin presets of it). */
+typedef enum cnx_epilogue {
+  CNX_EPI_STORE_BF16 = 0,    /* D0 = acc                                   */
+  CNX_EPI_BIAS_GELU = 1,     /* D0 = z = acc + bias ; D1 = gelu(z)         */
+  CNX_EPI_BIAS_RESIDUAL = 2, /* D0 = acc + bias + R                        */
+  CNX_EPI_GELU_GRAD = 3,     /* D0 = acc * gelu'(R) ; colsum += sum_m D0   */
+  CNX_EPI_STORE_F32 = 4      /* D0 (fp32, zero-filled by caller) += acc    */
+} cnx_epilogue;
+
+/* One entry of the host-generated MixUp/CutMix plan (see cnx_mix_batch). 32 bytes. */
+typedef struct cnx_mix_plan_entry {
+  int32_t mode;          /* 0 passthrough, 1 mixup, 2 cutmix */
+  int32_t partner;       /* index of the second sample inside the batch */
+  float lam;             /* float32(lam) */
+  float one_minus_lam;   /* float32(1.0 - lam), subtraction in float64 */
+  int32_t bbx1, bby1, bbx2, bby2; /* cutmix box, [x1,x2) x [y1,y2) */
+} cnx_mix_plan_entry;
+
+int cnx_version(void);
+const char* cnx_last_error_string(void);
+/* 0 if the current CUDA device is sm_100, CNX_ERR_NOT_SM100 otherwise. */
+int cnx_check_device(void);
+/* Scratch bytes an op needs for the given problem (currently 0 for every op). */
+size_t cnx_workspace_bytes(int op, int B, int H, int W, int C);
+
+/* Fold LN affine into fc1 and layer-scale into fc2, cast to bf16 in both orientations, and
+ * transpose the depthwise taps to [49][C].  Inputs are the nine timm ConvNeXtBlock parameters
+ * (conv_dw.weight [C,1,7,7], norm.weight/bias [C], mlp.fc1.weight [4C,C], mlp.fc1.bias [4C],
+ * mlp.fc2.weight [C,4C], mlp.fc2.bias [C], gamma [C]); call once per weight version
+ * (after optimizer.step(), /root/reference/train_advanced_v4.py:229). */
+int cnx_prep_block_weights(const float* conv_dw_w, const float* norm_w, const float* norm_b, const float* fc1_w,
+                           const float* fc1_b, const float* fc2_w, const float* fc2_b,
+                           const float* gamma, float* wt_dw /*[49][C]*/, void* w1f /*[4C][C] bf16*/,
+                           void* w1fT /*[C][4C] bf16*/, float* b1f /*[4C]*/,
+                           void* w2f /*[C][4C] bf16*/, void* w2fT /*[4C][C] bf16*/,
+                           float* b2f /*[C]*/, int C, void* stream);
+
+/* Adjoint of cnx_prep_block_weights: gradients of the folded tensors -> gradients of the timm
+ * parameters (d_fc1_b equals db1f and d_conv_dw_b equals dbias of cnx_dwconv_ln_bwd). */
+int cnx_unfold_block_grads(const float* dw1f, const float* db1f, const float* dw2f,
+                           const float* db2f, const float* dwt_dw, const float* norm_w,
+                           const float* norm_b, const float* fc1_w, const float* fc2_w,
+                           const float* fc2_b, const float* gamma, float* d_conv_dw_w,
+                           float* d_norm_w, float* d_norm_b, float* d_fc1_w, float* d_fc2_w,
+                           float* d_fc2_b, float* d_gamma, int C, void* stream);
+
+/* conv_dw (7x7 depthwise, pad 3, +bias) -> permute -> LayerNorm(C, eps) WITHOUT the affine
+ * (folded into fc1).  Replaces the first three ops of timm ConvNeXtBlock.forward reached from
+ * /root/reference/train_advanced_v4.py:134-135.  x, xhat: [B,H,W,C] bf16; mean, rstd: [B*H*W]. */
+int cnx_dwconv_ln_fwd(const void* x, const float* wt_dw, const float* conv_dw_b, void* xhat,
+                      float* mean, float* rstd, int B, int H, int W, int C, float eps, void* stream);
+
+/* Backward of the above plus the shortcut edge: dx = dy + dwconv^T(LN^T(dxhat)); dwt [49][C],
+ * dbias [C] and dy_colsum [C] (= gradient of the folded fc2 bias) are overwritten. */
+int cnx_dwconv_ln_bwd(const void* dxhat, const void* xhat, const float* rstd, const void* x,
+                      const void* dy, const float* wt_dw, void* dx, float* dwt, float* dbias,
+                      float* dy_colsum, int B, int H, int W, int C, void* workspace,
+                      size_t workspace_bytes, void* stream);
+
+/* Generic tensor-core GEMM: D[M,N] = epilogue(A[M,K] * B[N,K]^T), bf16 in, fp32 accumulate.
+ * a_mn_major / b_mn_major != 0: the operand is stored [K, rows] (row-major) instead. */
+int cnx_gemm_bf16(const void* A, int64_t lda, int a_mn_major, const void* B, int64_t ldb,
+                  int b_mn_major, int M, int N, int K, int epilogue, void* D0, int64_t ldd0,
+                  void* D1, int64_t ldd1, const float* bias, const void* R, int64_t ldr,
+                  float* colsum, void* stream);
+
+/* mlp.fc1 + GELU(erf): z = xhat @ w1f^T + b1f (bf16), h = gelu(z) (bf16); [M,4C] each. */
+int cnx_fc1_gelu_fwd(const void* xhat, const void* w1f, const float* b1f, void* z, void* h, int M,
+                     int C, void* stream);
+/* mlp.fc2 * gamma + shortcut: y = x + h @ w2f^T + b2f   ([M,C] bf16). */
+int cnx_fc2_residual_fwd(const void* h, const void* w2f, const float* b2f, const void* x, void* y,
+                         int M, int C, void* stream);
+/* dz = (dy @ w2f) * gelu'(z) ([M,4C] bf16); db1f[4C] (zero-filled by caller) += column sums. */
+int cnx_mlp_bwd_dz(const void* dy, const void* w2fT, const void* z, void* dz, float* db1f, int M,
+                   int C, void* stream);
+/* dxhat = dz @ w1f   ([M,C] bf16). */
+int cnx_mlp_bwd_dxhat(const void* dz, const void* w1fT, void* dxhat, int M, int C, void* stream);
+/* dw2f[C,4C] += dy^T @ h ; dw1f[4C,C] += dz^T @ xhat   (fp32, zero-filled by caller). */
+int cnx_mlp_bwd_wgrad(const void* dy, const void* h, const void* dz, const void* xhat, float* dw2f,
+                      float* dw1f, int M, int C, void* stream);
+
+/* Batch-level MixUp/CutMix (MixUpCutMixDataset, /root/reference/dataset.py:81-190) from a host
+ * plan: x [B,CH,H,W] fp32 NCHW -> out (same shape, must not alias x); labels [B] int64 ->
+ * targets [B,num_classes] fp32.  Pixels and targets are bit-identical to the reference. */
+int cnx_mix_batch(const float* x, const int64_t* labels, const cnx_mix_plan_entry* plan,
+                  float* out, float* targets, int B, int CH, int H, int W, int num_classes,
+                  void* stream);
+
+/* nn.CrossEntropyLoss(label_smoothing) on probability targets
+ * (/root/reference/train_advanced_v4.py:626,221): loss (scalar, mean over B) and, if dlogits is
+ * non-NULL, d loss / d logits.  logits, targets, dlogits: [B,NC] fp32. */
+int cnx_softce_fwd_bwd(const float* logits, const float* targets, float* loss, float* dlogits,
+                       int B, int NC, float label_smoothing, void* stream);
+
+/* EMA.update (/root/reference/train_advanced_v4.py:75-80) over all tensors in one launch:
+ * shadow[t] = one_minus_decay * param[t] + decay * shadow[t].  All four tables are DEVICE arrays;
+ * chunk_prefix[t] = number of 8192-element chunks before tensor t, [num_tensors + 1]. */
+int cnx_ema_lerp_multi(const void* const* param_ptrs, void* const* shadow_ptrs,
+                       const int64_t* numels, const int64_t* chunk_prefix, int num_tensors,
+                       int64_t total_chunks, float one_minus_decay, float decay, void* stream);
+int cnx_ema_chunk_elems(void);
+
+/* Module-boundary layout conversion (timm blocks are NCHW): [B,C,H,W] fp32 <-> [B,H,W,C] bf16. */
+int cnx_nchw_f32_to_nhwc_bf16(const float* src, void* dst, int B, int C, int H, int W, void* stream);
+int cnx_nhwc_bf16_to_nchw_f32(const void* src, float* dst, int B, int C, int H, int W, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CNX_B200_H_ */
