@@ -15,6 +15,8 @@ namespace cnx {
 // error codes (cnx_status) come from the public header
 void set_last_error(const char* fmt, ...);
 const char* last_error();
+int* timeout_flag_ptr();             // device-visible mapped host int set by a timed-out wait
+int read_and_clear_timeout_flag();   // host side; call after synchronising the stream
 int  check_device_sm100();           // CNX_OK or CNX_ERR_NOT_SM100 (cached per device)
 int  sm_count();
 
@@ -97,14 +99,28 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded wait: a protocol bug traps (=> launch error reported by the C ABI) instead
-// of hanging the GPU box.  try_wait sleeps in hardware, so the cap is generous.
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+// Bounded wait: a protocol bug must neither hang the GPU box nor raise a device fault, so after
+// ~2 s of wall time (or as soon as another thread has given up) the wait returns, leaving a flag
+// the host reads (a mapped pinned int, see timeout_flag_ptr()); results of that launch are then garbage.
+__device__ __forceinline__ uint64_t globaltimer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int* timeout_flag) {
+  uint64_t t0 = 0;
 #pragma unroll 1
-  for (uint32_t it = 0; it < (1u << 26); ++it) {
+  for (uint32_t it = 0;; ++it) {
     if (mbar_try_wait(bar, parity)) return;
+    if ((it & 1023u) == 1023u) {
+      const uint64_t now = globaltimer_ns();
+      if (t0 == 0) t0 = now;
+      if (now - t0 > 2000000000ull || *reinterpret_cast<volatile int*>(timeout_flag) != 0) {
+        *reinterpret_cast<volatile int*>(timeout_flag) = 1;
+        return;
+      }
+    }
   }
-  __trap();
 }
 
 // ------------------------------------------------------------------------ TMA

@@ -42,6 +42,32 @@ void set_last_error(const char* fmt, ...) {
 
 const char* last_error() { return g_err; }
 
+namespace {
+int* g_flag_host = nullptr;
+int* g_flag_dev = nullptr;
+std::once_flag g_flag_once;
+}  // namespace
+
+int* timeout_flag_ptr() {
+  std::call_once(g_flag_once, [] {
+    void* h = nullptr;
+    if (cudaHostAlloc(&h, sizeof(int), cudaHostAllocMapped) != cudaSuccess) return;
+    *static_cast<int*>(h) = 0;
+    void* d = nullptr;
+    if (cudaHostGetDevicePointer(&d, h, 0) != cudaSuccess) return;
+    g_flag_host = static_cast<int*>(h);
+    g_flag_dev = static_cast<int*>(d);
+  });
+  return g_flag_dev;
+}
+
+int read_and_clear_timeout_flag() {
+  if (timeout_flag_ptr() == nullptr) return -1;
+  const int v = *reinterpret_cast<volatile int*>(g_flag_host);
+  *reinterpret_cast<volatile int*>(g_flag_host) = 0;
+  return v;
+}
+
 int check_device_sm100() {
   std::call_once(g_dev_once, query_device);
   if (g_cc_major != 10) {

@@ -33,6 +33,7 @@ constexpr int MH = 2, MW = 4;
 constexpr int kAccRows = 51;  // 49 taps + dbias + dy_colsum
 
 struct BwdParams {
+  int* timeout_flag;
   const float* rstd;           // [B*H*W]
   const __nv_bfloat16* x;      // [B,H,W,C] block input
   const __nv_bfloat16* dy;     // [B,H,W,C] gradient of block output
@@ -49,7 +50,8 @@ template <bool kCluster>
 __global__ void __launch_bounds__(kThreads, 1)
 dwconv_ln_bwd_kernel(const __grid_constant__ CUtensorMap dxhat_map,
                      const __grid_constant__ CUtensorMap xhat_map, const BwdParams p) {
-  extern __shared__ __align__(128) unsigned char smem_raw[];
+  extern __shared__ __align__(128) unsigned char smem_dyn[];
+  unsigned char* smem_raw = smem_dyn + ((128u - (smem_u32(smem_dyn) & 127u)) & 127u);
   __shared__ __align__(8) uint64_t tma_bar;
   __shared__ float2 s_part[448];   // per halo pixel (sum dxhat, sum dxhat*xhat) of this slab
   __shared__ float4 s_coef[448];   // per halo pixel (rstd, rstd*m1, rstd*m2, -)
@@ -81,7 +83,7 @@ dwconv_ln_bwd_kernel(const __grid_constant__ CUtensorMap dxhat_map,
     tma_load_4d(tile_d, &dxhat_map, &tma_bar, c0, w0 - 3, h0 - 3, n);
     tma_load_4d(tile_x, &xhat_map, &tma_bar, c0, w0 - 3, h0 - 3, n);
   }
-  mbar_wait(&tma_bar, 0);
+  mbar_wait(&tma_bar, 0, p.timeout_flag);
 
   // ---- phase 2: per-halo-pixel partial sums over this slab (thread per pixel, rotated channel
   //      order so the 32 lanes of a warp hit 32 different banks)
@@ -315,6 +317,11 @@ int dwconv_ln_bwd(const void* dxhat, const void* xhat, const float* rstd, const 
   if (rc != CNX_OK) return rc;
 
   BwdParams p;
+  p.timeout_flag = timeout_flag_ptr();
+  if (p.timeout_flag == nullptr) {
+    set_last_error("could not map the timeout flag (cudaHostAlloc failed)");
+    return CNX_ERR_DRIVER;
+  }
   p.rstd = rstd;
   p.x = static_cast<const __nv_bfloat16*>(x);
   p.dy = static_cast<const __nv_bfloat16*>(dy);
@@ -331,6 +338,7 @@ int dwconv_ln_bwd(const void* dxhat, const void* xhat, const float* rstd, const 
   const size_t taps = static_cast<size_t>(49) * (CS / 2) * sizeof(float2);
   if (smem < red) smem = red;
   if (tile < taps) smem = tile + taps > smem ? tile + taps : smem;
+  smem += 128;   // manual 128-byte alignment slack
   if (smem > 212 * 1024) {   // + ~11 KB of static tables must stay under the 227 KB CTA limit
     set_last_error("dwconv_ln_bwd: shared-memory request %zu exceeds the SM", smem);
     return CNX_ERR_BAD_SHAPE;

@@ -33,6 +33,7 @@ constexpr int MH = 2, MW = 4;               // output micro-tile per thread
 constexpr int kPixPerChunk = kPG * MH * MW; // 32
 
 struct FwdParams {
+  int* timeout_flag;
   __nv_bfloat16* xhat;   // [B,H,W,C]
   float* mean;           // [B*H*W]
   float* rstd;           // [B*H*W]
@@ -48,7 +49,9 @@ struct FwdParams {
 template <bool kCluster>
 __global__ void __launch_bounds__(kThreads, 1)
 dwconv_ln_fwd_kernel(const __grid_constant__ CUtensorMap x_map, const FwdParams p) {
-  extern __shared__ __align__(128) unsigned char smem_raw[];
+  extern __shared__ __align__(128) unsigned char smem_dyn[];
+  // TMA destinations must be 128-byte aligned; do not rely on the toolchain's placement
+  unsigned char* smem_raw = smem_dyn + ((128u - (smem_u32(smem_dyn) & 127u)) & 127u);
   __shared__ __align__(8) uint64_t tma_bar;
   __shared__ float2 s_part[2][kPixPerChunk][2];  // (mean_w, M2_w) per chunk pixel per warp-in-group
   __shared__ float2 s_final[kPixPerChunk];       // (mean, rstd)
@@ -97,7 +100,7 @@ dwconv_ln_fwd_kernel(const __grid_constant__ CUtensorMap x_map, const FwdParams 
   const int n_w = max(0, min(64, CS - 64 * wig));
   const float inv_nw = n_w > 0 ? 1.0f / static_cast<float>(n_w) : 0.f;
 
-  mbar_wait(&tma_bar, 0);
+  mbar_wait(&tma_bar, 0, p.timeout_flag);
 
   const int mt_w = p.TW / MW;
   const int nmt = (p.TH / MH) * mt_w;
@@ -273,6 +276,11 @@ int dwconv_ln_fwd(const void* x, const float* wt, const float* bias, void* xhat,
   if (rc != CNX_OK) return rc;
 
   FwdParams p;
+  p.timeout_flag = timeout_flag_ptr();
+  if (p.timeout_flag == nullptr) {
+    set_last_error("could not map the timeout flag (cudaHostAlloc failed)");
+    return CNX_ERR_DRIVER;
+  }
   p.xhat = static_cast<__nv_bfloat16*>(xhat);
   p.mean = mean;
   p.rstd = rstd;
@@ -283,7 +291,7 @@ int dwconv_ln_fwd(const void* x, const float* wt, const float* bias, void* xhat,
   p.tiles_w = (W + TW - 1) / TW;
   p.eps = eps;
   const int tiles_h = (H + TH - 1) / TH;
-  const size_t smem = static_cast<size_t>(TH + 6) * (TW + 6) * CS * 2;
+  const size_t smem = static_cast<size_t>(TH + 6) * (TW + 6) * CS * 2 + 128;
 
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(p.tiles_w * tiles_h, B, nslab);

@@ -40,6 +40,7 @@ struct SmemLayout {
 };
 
 struct GemmParams {
+  int* timeout_flag;
   int M, N, K;
   int a_mn, b_mn;
   int kb_per_split;
@@ -152,7 +153,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     for (int i = 0; i < nkb; ++i) {
       const int s = i % kStages;
       const uint32_t ph = (i / kStages) & 1;
-      mbar_wait(&empty_bar[s], ph ^ 1);
+      mbar_wait(&empty_bar[s], ph ^ 1, p.timeout_flag);
       unsigned char* sa = smem + s * L::kStageBytes;
       unsigned char* sb = sa + L::kABytes;
       mbar_arrive_expect_tx(&full_bar[s], L::kStageBytes);
@@ -178,7 +179,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     for (int i = 0; i < nkb; ++i) {
       const int s = i % kStages;
       const uint32_t ph = (i / kStages) & 1;
-      mbar_wait(&full_bar[s], ph);
+      mbar_wait(&full_bar[s], ph, p.timeout_flag);
       tc_fence_after();
       const uint32_t sa = smem_u32(smem + s * L::kStageBytes);
       const uint32_t sb = sa + L::kABytes;
@@ -200,7 +201,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   __syncwarp();
 
   // ------------------------------------------------------------------ epilogue
-  mbar_wait(tmem_full_bar, 0);
+  mbar_wait(tmem_full_bar, 0, p.timeout_flag);
   tc_fence_after();
 
   const int q = warp & 3;                  // TMEM lane quarter this warp may read
@@ -395,6 +396,11 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   }
 
   GemmParams p;
+  p.timeout_flag = timeout_flag_ptr();
+  if (p.timeout_flag == nullptr) {
+    set_last_error("could not map the timeout flag (cudaHostAlloc failed)");
+    return CNX_ERR_DRIVER;
+  }
   p.M = a.M; p.N = a.N; p.K = a.K;
   p.a_mn = a.a_mn_major ? 1 : 0;
   p.b_mn = a.b_mn_major ? 1 : 0;
@@ -421,6 +427,12 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   splits = (nkb + kbps - 1) / kbps;             // no empty split
   p.kb_per_split = kbps;
 
+  auto misaligned = [](const void* q) { return q && (reinterpret_cast<uintptr_t>(q) & 15) != 0; };
+  if (misaligned(a.D0) || misaligned(a.D1) || misaligned(a.bias) || misaligned(a.R) ||
+      misaligned(a.colsum)) {
+    set_last_error("gemm_bf16: every operand pointer must be 16-byte aligned");
+    return CNX_ERR_BAD_ARG;
+  }
   if ((a.ldd0 % 8) != 0 || (a.D1 && (a.ldd1 % 8) != 0) || (a.R && (a.ldr % 8) != 0)) {
     set_last_error("gemm_bf16: output/residual leading dimensions must be multiples of 8");
     return CNX_ERR_BAD_SHAPE;

@@ -67,6 +67,9 @@ int cnx_version(void);
 const char* cnx_last_error_string(void);
 /* 0 if the current CUDA device is sm_100, CNX_ERR_NOT_SM100 otherwise. */
 int cnx_check_device(void);
+/* Debug: 1 if a kernel gave up waiting on an mbarrier since the last call (then that launch's
+ * results are garbage), 0 otherwise; clears the flag.  Call after synchronising the stream. */
+int cnx_debug_timeout_flag(void);
 /* Scratch bytes an op needs for the given problem (currently 0 for every op). */
 size_t cnx_workspace_bytes(int op, int B, int H, int W, int C);
 

@@ -1,0 +1,204 @@
+"""GPU parity (through the C ABI) of the glue kernels: mix, soft-CE, EMA, layout, weight folding.
+Bit-exact where the reference is integer/deterministic fp32 (mix, EMA); 1e-4 relative in fp32."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import block_oracle, mix_oracle  # noqa: E402  (checker only)
+
+
+def _dev():
+    assert torch.cuda.is_available(), "GPU tests need a B200"
+    return torch.device("cuda:0")
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name))
+
+
+# ------------------------------------------------------------------------------------- mix
+@pytest.mark.parametrize("seed", [0, 1, 2, 3, 4])
+def test_mix_batch_bit_exact_vs_reference_golden(cnx_lib, golden_dir, seed):
+    from image_classification_b200 import mix
+    g = _load(golden_dir, "mix_reference.npz")
+    _, N, CH, H, W, NC = [int(v) for v in g[f"s{seed}_cfg"]]
+    ma, ca, prob = [float(v) for v in g[f"s{seed}_alphas"]]
+    gen = torch.Generator().manual_seed(seed)
+    images = torch.randn(N, CH, H, W, generator=gen)
+    labels = torch.randint(0, NC, (N,), generator=gen)
+    plan = mix.plan_mix_batch(N, H, W, mixup_alpha=ma, cutmix_alpha=ca, prob=prob,
+                              rng=np.random.RandomState(seed))
+    out, targets = mix.mix_batch(images.to(_dev()), labels.to(_dev()), plan, NC)
+    out, targets = out.cpu().numpy(), targets.cpu().numpy()
+    assert np.array_equal(targets, g[f"s{seed}_targets"])
+    if f"s{seed}_mixed" in g:
+        assert np.array_equal(out, g[f"s{seed}_mixed"])
+    else:
+        assert np.array_equal(out[:, :, H // 2, :], g[f"s{seed}_mixed_row"])
+        assert np.array_equal(out.astype(np.float64).sum(axis=(1, 2, 3)), g[f"s{seed}_mixed_sum"])
+
+
+def test_mix_batch_full_size_vs_oracle(cnx_lib):
+    """BASELINE config 2 shape (B=128, 3x224x224), reference settings, bit-exact vs the oracle."""
+    from image_classification_b200 import mix
+    N, CH, H, W, NC = 128, 3, 224, 224, 44
+    gen = torch.Generator().manual_seed(0)
+    images = torch.randn(N, CH, H, W, generator=gen)
+    labels = torch.randint(0, NC, (N,), generator=gen)
+    ref, ref_t, _ = mix_oracle.mix_dataset_ref(images.numpy(), labels.numpy(), mixup_alpha=0.2,
+                                               cutmix_alpha=1.0, prob=0.5, num_classes=NC,
+                                               rng=np.random.RandomState(0))
+    mixer = mix.BatchMixUpCutMix(mixup_alpha=0.2, cutmix_alpha=1.0, prob=0.5, num_classes=NC)
+    out, targets = mixer(images.to(_dev()), labels.to(_dev()), rng=np.random.RandomState(0))
+    assert np.array_equal(out.cpu().numpy(), ref)
+    assert np.array_equal(targets.cpu().numpy(), ref_t)
+    # size-independent properties: rows sum to 1 (within 1 ulp), passthrough rows are one-hot
+    assert torch.all((targets.sum(1) - 1).abs() < 1e-6)
+
+
+def test_mix_rejects_bad_arguments(cnx_lib):
+    from image_classification_b200 import _lib, mix
+    x = torch.zeros(2, 3, 4, 6, device=_dev())   # W not a multiple of 4
+    plan = mix.plan_mix_batch(2, 4, 6, rng=np.random.RandomState(0))
+    with pytest.raises(_lib.CnxError):
+        mix.mix_batch(x, torch.zeros(2, dtype=torch.long, device=_dev()), plan, 5)
+    with pytest.raises(_lib.CnxError):
+        mix.mix_batch(torch.zeros(2, 3, 4, 8), torch.zeros(2, dtype=torch.long), plan, 5)  # CPU
+
+
+# ---------------------------------------------------------------------------------- soft CE
+@pytest.mark.parametrize("case", [0, 1, 2, 3])
+def test_softce_vs_torch_golden(cnx_lib, golden_dir, case):
+    from image_classification_b200.loss import SoftTargetCrossEntropyB200
+    g = _load(golden_dir, "softce_torch.npz")
+    z = torch.from_numpy(g[f"c{case}_z"]).to(_dev()).requires_grad_()
+    t = torch.from_numpy(g[f"c{case}_t"]).to(_dev())
+    crit = SoftTargetCrossEntropyB200(label_smoothing=float(g[f"c{case}_eps"]))
+    loss = crit(z, t)
+    (loss * 3.0).backward()      # exercises the upstream-gradient scaling (GradScaler)
+    np.testing.assert_allclose(loss.item(), g[f"c{case}_loss"], rtol=1e-4)          # fp32: 1e-4
+    ref_dz = g[f"c{case}_dz"] * 3.0
+    err = np.abs(z.grad.cpu().numpy() - ref_dz).max() / np.abs(ref_dz).max()
+    assert err < 1e-4, err
+
+
+def test_softce_hard_labels_and_bf16_logits(cnx_lib):
+    from image_classification_b200.loss import SoftTargetCrossEntropyB200
+    torch.manual_seed(0)
+    z = torch.randn(16, 44, device=_dev()).bfloat16().requires_grad_()
+    y = torch.randint(0, 44, (16,), device=_dev())
+    loss = SoftTargetCrossEntropyB200(0.1)(z, y)
+    ref = torch.nn.functional.cross_entropy(z.float(), y, label_smoothing=0.1)
+    assert abs(loss.item() - ref.item()) < 1e-4 * abs(ref.item())
+    loss.backward()
+    assert z.grad.dtype == torch.bfloat16
+
+
+# -------------------------------------------------------------------------------------- EMA
+def test_ema_bit_exact_vs_reference_golden(cnx_lib, golden_dir):
+    from image_classification_b200.ema import EMAB200
+    g = _load(golden_dir, "ema_reference.npz")
+    model = torch.nn.Sequential(torch.nn.Linear(7, 5), torch.nn.Conv2d(3, 4, 3),
+                                torch.nn.LayerNorm(9)).to(_dev())
+    with torch.no_grad():
+        for name, p in model.named_parameters():
+            p.copy_(torch.from_numpy(g[f"init_shadow_{name}"]))
+    ema = EMAB200(model, float(g["decay"]))
+    for step in range(3):
+        with torch.no_grad():
+            for name, p in model.named_parameters():
+                p.copy_(torch.from_numpy(g[f"step{step}_param_{name}"]))
+        ema.update()
+        for name, s in ema.shadow.items():
+            assert np.array_equal(s.cpu().numpy(), g[f"step{step}_shadow_{name}"]), (step, name)
+
+
+def test_ema_many_ragged_tensors_and_swap(cnx_lib):
+    from image_classification_b200.ema import EMAB200
+    torch.manual_seed(1)
+    sizes = [1, 3, 4, 5, 8191, 8192, 8193, 3 * 8192 + 7, 100_003, 44, 1024 * 49]
+    model = torch.nn.ParameterList([torch.nn.Parameter(torch.randn(n, device=_dev())) for n in sizes])
+    frozen = torch.nn.Parameter(torch.randn(10, device=_dev()), requires_grad=False)
+    model.append(frozen)
+    ema = EMAB200(model, 0.9997)
+    assert len(ema.shadow) == len(sizes)                  # requires_grad only (:72)
+    ref = {k: v.clone() for k, v in ema.shadow.items()}
+    for _ in range(2):
+        with torch.no_grad():
+            for p in model:
+                if p.requires_grad:
+                    p.add_(torch.randn_like(p))
+        ema.update()
+        for (k, s), p in zip(ref.items(), [p for p in model if p.requires_grad]):
+            ref[k] = block_oracle.ema_update_ref(s, p.data, 0.9997)
+    for k in ref:
+        assert torch.equal(ema.shadow[k], ref[k]), k
+    before = [p.data.clone() for p in model]
+    ema.apply_shadow()
+    assert all(torch.equal(p.data, ema.shadow[n]) for n, p in model.named_parameters() if p.requires_grad)
+    ema.restore()
+    assert all(torch.equal(p.data, b) for p, b in zip(model, before))
+
+
+# ----------------------------------------------------------------------------------- layout
+def test_layout_round_trip(cnx_lib):
+    from image_classification_b200 import ops
+    torch.manual_seed(0)
+    for shape in [(2, 96, 7, 5), (1, 128, 14, 14), (3, 40, 9, 33)]:
+        x = torch.randn(*shape, device=_dev())
+        nhwc = ops.nchw_f32_to_nhwc_bf16(x)
+        assert torch.equal(nhwc, x.permute(0, 2, 3, 1).contiguous().bfloat16())
+        back = ops.nhwc_bf16_to_nchw_f32(nhwc)
+        assert torch.equal(back, x.bfloat16().float())
+
+
+# ----------------------------------------------------------------- weight folding / adjoint
+def _rand_block_params(C, dev, gamma_scale=1.0):
+    torch.manual_seed(C)
+    f = lambda *s, std=0.2: (torch.randn(*s, device=dev) * std)
+    return dict(conv_w=f(C, 1, 7, 7), conv_b=f(C), norm_w=1 + f(C), norm_b=f(C),
+                fc1_w=f(4 * C, C, std=0.1), fc1_b=f(4 * C), fc2_w=f(C, 4 * C, std=0.1),
+                fc2_b=f(C), gamma=(torch.rand(C, device=dev) * 0.9 + 0.1) * gamma_scale)
+
+
+@pytest.mark.parametrize("C", [64, 96, 128, 512])
+def test_prep_block_weights(cnx_lib, C):
+    from image_classification_b200 import ops
+    p = _rand_block_params(C, _dev())
+    fw = ops.prep_block_weights(p["conv_w"], p["norm_w"], p["norm_b"], p["fc1_w"], p["fc1_b"],
+                                p["fc2_w"], p["fc2_b"], p["gamma"])
+    w1 = (p["fc1_w"] * p["norm_w"][None, :]).bfloat16()
+    w2 = (p["gamma"][:, None] * p["fc2_w"]).bfloat16()
+    assert torch.equal(fw.w1f, w1) and torch.equal(fw.w1fT, w1.t().contiguous())
+    assert torch.equal(fw.w2f, w2) and torch.equal(fw.w2fT, w2.t().contiguous())
+    assert torch.equal(fw.wt_dw, p["conv_w"].reshape(C, 49).t().contiguous())
+    torch.testing.assert_close(fw.b1f, p["fc1_b"] + p["fc1_w"] @ p["norm_b"], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(fw.b2f, p["gamma"] * p["fc2_b"], rtol=1e-6, atol=0)
+
+
+@pytest.mark.parametrize("C", [64, 96, 256])
+def test_unfold_block_grads_is_adjoint_of_prep(cnx_lib, C):
+    from image_classification_b200 import ops
+    dev = _dev()
+    p = {k: v.double().requires_grad_() for k, v in _rand_block_params(C, dev).items()}
+    w1f = p["fc1_w"] * p["norm_w"][None, :]
+    b1f = p["fc1_b"] + p["fc1_w"] @ p["norm_b"]
+    w2f = p["gamma"][:, None] * p["fc2_w"]
+    b2f = p["gamma"] * p["fc2_b"]
+    wt = p["conv_w"].reshape(C, 49).t()
+    torch.manual_seed(1)
+    up = [torch.randn_like(t) for t in (w1f, b1f, w2f, b2f, wt)]
+    torch.autograd.backward([w1f, b1f, w2f, b2f, wt], up)
+    f32 = lambda t: t.detach().float().contiguous()
+    d_dw, d_nw, d_nb, d_f1, d_f2, d_f2b, d_g = ops.unfold_block_grads(
+        f32(up[0]), f32(up[1]), f32(up[2]), f32(up[3]), f32(up[4]), f32(p["norm_w"]),
+        f32(p["norm_b"]), f32(p["fc1_w"]), f32(p["fc2_w"]), f32(p["fc2_b"]), f32(p["gamma"]))
+    for got, key in ((d_dw, "conv_w"), (d_nw, "norm_w"), (d_nb, "norm_b"), (d_f1, "fc1_w"),
+                     (d_f2, "fc2_w"), (d_f2b, "fc2_b"), (d_g, "gamma")):
+        ref = p[key].grad.float()
+        err = (got - ref).abs().max() / ref.abs().max()
+        assert err < 1e-4, (key, float(err))
