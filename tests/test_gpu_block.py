@@ -96,6 +96,8 @@ def test_gemm_mn_major_operands(cnx_lib, shape, a_mn, b_mn):
     """Weight-gradient form: operands stored [K, rows]; K (tokens) may be ragged."""
     from image_classification_b200 import ops
     M, N, K = shape
+    if K % 8 != 0 and not (a_mn and b_mn):
+        pytest.skip("a K-major operand needs K % 8 == 0 (16-byte TMA row pitch)")
     dev = _dev()
     torch.manual_seed(M * 3 + N + K)
     A = torch.randn(M, K, device=dev).bfloat16()
@@ -156,7 +158,7 @@ def test_dwconv_ln_bwd_vs_oracle_autograd(cnx_lib, shape):
     ref_dx = x.grad + dy.double()
     ref_dwt = w.grad.reshape(C, 49).t()
     # kernel inputs: what the forward kernel would have saved
-    xhat_in = xhat_ref.detach().float().bfloat16()
+    xhat_in = xhat_ref.detach().float().bfloat16().contiguous()
     rstd_in = rstd_ref.detach().float().contiguous()
     wt = w.detach().float().reshape(C, 49).t().contiguous()
     dx, dwt, dbias, dycs = ops.dwconv_ln_bwd(dxhat.bfloat16(), xhat_in, rstd_in,
