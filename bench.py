@@ -1,0 +1,436 @@
+"""bench.py — ConvNeXt-Base 224x224 bf16 training throughput (images/s) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
+
+One "step" = one optimizer step of the reference loop (/root/reference/train_advanced_v4.py:
+215-237): 2 accumulation micro-batches of 128 images per GPU, each = device MixUp/CutMix ->
+ConvNeXt-Base forward (36 libcnx_b200 blocks) -> label-smoothed soft-target CE -> backward; then
+unscale / clip 1.0 / AdamW / scheduler / EMA.  `value` = images all ranks processed / max-over-
+ranks device time with the raw batch already in HBM; `e2e` = same loop fed from pinned host
+buffers through the public API (H2D copy of every micro-batch and a D2H read of the loss inside
+the timed region).  Weak scaling: per-GPU work is fixed, global batch = 256 * N.
+
+`--impl reference` times the reference's CPU PyTorch path for the same metric (oracle port of the
+model, the reference loop order, bounded micro-batches) on the host cores of rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np
+import torch
+
+METRIC = "ConvNeXt-Base 224 bf16 train images/sec"
+UNIT = "images/s"
+NUM_CLASSES = 44
+MICRO_BATCH = 128
+ACCUM = 2
+RES = 224
+DIMS = (128, 256, 512, 1024)
+DEPTHS = (3, 3, 27, 3)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", type=str, default="b200", choices=["b200", "reference"])
+    ap.add_argument("--res", type=int, default=RES)
+    ap.add_argument("--micro-batch", type=int, default=MICRO_BATCH)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    """Measured roofline denominators (driver-written) or the profiling guide's fallback."""
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return dict(hbm_gbs=d["hbm_gbs"], bf16_tflops=d["bf16_tflops"],
+                    bf16_tflops_sustained=d.get("bf16_tflops_sustained", d["bf16_tflops"]),
+                    source="measured (MEASURED_PEAKS.json)")
+    return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, bf16_tflops_sustained=1400.0,
+                source="fallback (B200_PROFILING.md)")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}",
+                 "--format=csv,noheader,nounits", "-lms", "200"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, power, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0])); smax.append(float(parts[1])); power.append(float(parts[2]))
+            except ValueError:
+                continue
+            for name, val in zip(names, parts[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": max(smax) if smax else None,
+                "power_w_max": max(power) if power else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU arm: the reference's PyTorch path on the host cores (oracle port; bounded micro-batches)
+# ---------------------------------------------------------------------------------------------
+def run_cpu_reference(steps: int, warmup: int, micro_batch: int, res: int, model_name: str):
+    """-> (images/s, ms per step, cores, sample description)."""
+    from oracle import loop_oracle   # the checker, timed here only as the stated CPU baseline
+    from image_classification_b200.train_step import get_cosine_schedule_with_warmup
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.manual_seed(0)
+    model = loop_oracle.build_oracle_model(model_name, NUM_CLASSES).train()
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-4, weight_decay=1e-2)   # config.py:35-36
+    sched = get_cosine_schedule_with_warmup(opt, 10, 1000, 1e-6)
+    ema = loop_oracle.EMARef(model, 0.9997)
+    g = torch.Generator().manual_seed(0)
+    images = torch.randn(ACCUM, micro_batch, 3, res, res, generator=g)
+    labels = torch.randint(0, NUM_CLASSES, (ACCUM, micro_batch), generator=g)
+    rng = np.random.RandomState(0)
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        loop_oracle.reference_cpu_step(model, opt, sched, ema, images, labels, accum=ACCUM,
+                                       clip=1.0, label_smoothing=0.1, num_classes=NUM_CLASSES,
+                                       rng=rng)
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    total = sum(times)
+    ips = steps * ACCUM * micro_batch / total
+    sample = (f"{model_name} fp32 CPU, {steps} optimizer steps of {ACCUM}x{micro_batch} images at "
+              f"{res}x{res} (reference loop order: per-sample MixUp/CutMix, CE(ls=0.1), "
+              f"accumulate {ACCUM}, clip 1.0, AdamW, Python EMA), {warmup} warm-up")
+    return ips, 1e3 * total / steps, cores, sample
+
+
+def main_reference(args):
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return 0
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    # bounded sample: a ConvNeXt-Base step of 2x8 images is ~seconds of CPU work; shrink the
+    # micro-batch when many steps are requested so the whole run stays within a few minutes
+    total = steps + warmup
+    micro = 8 if total <= 30 else (4 if total <= 80 else 2)
+    ips, ms, cores, sample = run_cpu_reference(steps, warmup, micro, args.res, "convnext_base")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": round(ips, 3), "unit": UNIT,
+        "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": round(ms, 2),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": f"ConvNeXt-Base 44-class {args.res}x{args.res} training step, "
+                               f"reference CPU PyTorch path (bounded sample: micro-batch {micro})",
+                   "micro_batch": micro, "accumulation": ACCUM, "optimizer": "AdamW", "ema": 0.9997},
+        "cpu_baseline": {"value": round(ips, 3), "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": round(ips, 3), "unit": UNIT, "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------
+# B200 arm
+# ---------------------------------------------------------------------------------------------
+class B200Trainer:
+    """Everything one rank needs to run optimizer steps through the repo's public API."""
+
+    def __init__(self, device, world, rank, micro_batch, res):
+        from image_classification_b200 import ddp, ema, loss, mix, train_step
+        from image_classification_b200.convnext import create_convnext
+        self.device, self.world, self.rank = device, world, rank
+        self.micro_batch, self.res = micro_batch, res
+        torch.manual_seed(0)                      # identical replicas on every rank
+        self.model = create_convnext("convnext_base", NUM_CLASSES).to(device).train()
+        for m in self.model.modules():            # stem / downsample convs produce NHWC directly
+            if isinstance(m, torch.nn.Conv2d) and m.groups == 1:
+                m.to(memory_format=torch.channels_last)
+        self.params = [p for p in self.model.parameters() if p.requires_grad]
+        self.opt = torch.optim.AdamW(self.params, lr=1e-4, weight_decay=1e-2, fused=True)
+        self.sched = train_step.get_cosine_schedule_with_warmup(self.opt, 10, 100000, 1e-6)
+        self.scaler = torch.amp.GradScaler("cuda")            # kept: reference control flow (:432)
+        self.ema = ema.EMAB200(self.model, 0.9997)            # config.py:47
+        self.criterion = loss.SoftTargetCrossEntropyB200(0.1)  # config.py:31
+        self.mixer = mix.BatchMixUpCutMix(0.2, 1.0, 0.5, NUM_CLASSES)   # config.py:16-17, :593-599
+        self.rng = np.random.RandomState(1234 + rank)
+        self.reducer = ddp.BucketedGradReducer(self.params) if world > 1 else None
+        cfg = train_step.StepConfig(gradient_accumulation_steps=ACCUM, gradient_clip_val=1.0,
+                                    num_classes=NUM_CLASSES)
+        self.step_obj = train_step.TrainStep(self.model, self.criterion, self.opt, self.sched,
+                                             self.scaler, self.ema, cfg, self.reducer)
+        g = torch.Generator().manual_seed(100 + rank)
+        # synthetic "normalised pixels" (dataset.py:233-236) and hard labels, pinned on the host
+        self.host_images = [torch.randn(micro_batch, 3, res, res, generator=g).pin_memory()
+                            for _ in range(ACCUM)]
+        self.host_labels = [torch.randint(0, NUM_CLASSES, (micro_batch,), generator=g).pin_memory()
+                            for _ in range(ACCUM)]
+        self.dev_images = [t.to(device) for t in self.host_images]
+        self.dev_labels = [t.to(device) for t in self.host_labels]
+        self.batch_idx = 0
+
+    def _micro(self, images, labels):
+        mixed, targets = self.mixer(images, labels, rng=self.rng)
+        mixed = mixed.contiguous(memory_format=torch.channels_last)
+        loss = self.step_obj.micro_step(mixed, targets, self.batch_idx)
+        self.batch_idx += 1
+        return loss
+
+    def step_resident(self):
+        """inputs already in HBM"""
+        for i in range(ACCUM):
+            loss = self._micro(self.dev_images[i], self.dev_labels[i])
+        return loss
+
+    def step_e2e(self) -> float:
+        """pinned host -> device every micro-batch, loss read back to the host every step"""
+        for i in range(ACCUM):
+            images = self.host_images[i].to(self.device, non_blocking=True)
+            labels = self.host_labels[i].to(self.device, non_blocking=True)
+            loss = self._micro(images, labels)
+        return float(loss.item())
+
+    @property
+    def h2d_bytes_per_step(self):
+        return ACCUM * (self.host_images[0].numel() * 4 + self.host_labels[0].numel() * 8)
+
+
+def timed_region(fn, steps, world, device):
+    """barrier + sync, K steps between CUDA events on the current stream, max over ranks (ms)."""
+    import torch.distributed as dist
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(device)
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(steps):
+        fn()
+    e.record()
+    torch.cuda.synchronize(device)
+    ms = torch.tensor([s.elapsed_time(e)], device=device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.barrier()
+    return float(ms.item())
+
+
+# per entry point: (family, bound, work(args) in bytes or flops) — SURVEY.md §8(d) accounting
+def _work_table():
+    def dw_fwd(a):   # (x, wt, b, xhat, mean, rstd, B, H, W, C, eps, stream)
+        return 2.0 * a[6] * a[7] * a[8] * a[9] * 2
+    def dw_bwd(a):   # (dxhat, xhat, rstd, x, dy, wt, dx, dwt, dbias, dycs, B, H, W, C, ...)
+        return 4.0 * a[10] * a[11] * a[12] * a[13] * 2     # dxhat, xhat, x in + dx out (dy not counted)
+    def mlp(a, mi, ci, mult=1.0):
+        return mult * 8.0 * a[mi] * a[ci] * a[ci]           # 2 * M * 4C * C
+    return {
+        "cnx_dwconv_ln_fwd": ("dwconv_ln_fwd", "hbm", dw_fwd),
+        "cnx_dwconv_ln_bwd": ("dwconv_ln_bwd", "hbm", dw_bwd),
+        "cnx_fc1_gelu_fwd": ("mlp_gemm", "tensor", lambda a: mlp(a, 5, 6)),
+        "cnx_fc2_residual_fwd": ("mlp_gemm", "tensor", lambda a: mlp(a, 5, 6)),
+        "cnx_mlp_bwd_dz": ("mlp_gemm", "tensor", lambda a: mlp(a, 5, 6)),
+        "cnx_mlp_bwd_dxhat": ("mlp_gemm", "tensor", lambda a: mlp(a, 3, 4)),
+        "cnx_mlp_bwd_wgrad": ("mlp_gemm", "tensor", lambda a: mlp(a, 6, 7, 2.0)),
+    }
+
+
+def profile_kernels(trainer, device):
+    """One extra optimizer step with a CUDA-event pair around every library call (after the
+    timed region, so the events do not perturb `value`).  -> {family: stats}, launches/step."""
+    from image_classification_b200 import _lib
+    table = _work_table()
+    recs, open_ev = [], {}
+
+    def hook(name, phase, args):
+        if phase == "pre":
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            open_ev[name] = ev
+        else:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            recs.append((name, open_ev.pop(name), ev, args))
+
+    trainer.step_resident()                       # re-warm after the e2e loop
+    torch.cuda.synchronize(device)
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    _lib.call_hook = hook
+    try:
+        s.record()
+        trainer.step_resident()
+        e.record()
+        torch.cuda.synchronize(device)
+    finally:
+        _lib.call_hook = None
+    step_ms = s.elapsed_time(e)
+    fam = {}
+    for name, e0, e1, args in recs:
+        family, bound, work = table.get(name, (name.replace("cnx_", ""), "hbm", None))
+        d = fam.setdefault(family, dict(bound=bound, calls=0, launches=0, ms=0.0, work=0.0))
+        d["calls"] += 1
+        d["launches"] += _lib.LAUNCHES_PER_CALL.get(name, 1)
+        d["ms"] += e0.elapsed_time(e1)
+        if work is not None:
+            d["work"] += work(args)
+    return fam, step_ms
+
+
+def main_b200(args):
+    rank, world, local = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 arm has no CPU fallback "
+                         "(use --impl reference for the CPU baseline)")
+    device = torch.device("cuda", local)
+    torch.cuda.set_device(device)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
+    from image_classification_b200 import _lib
+    _lib.load()
+    _lib.check(_lib.load().cnx_check_device(), "cnx_check_device")
+
+    tr = B200Trainer(device, world, rank, args.micro_batch, args.res)
+    imgs_per_step = ACCUM * args.micro_batch * world
+    for _ in range(max(3, args.warmup)):
+        tr.step_resident()
+    if tr.reducer is not None:
+        tr.reducer.discover_unused()
+    torch.cuda.synchronize(device)
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = _lib.launch_count
+    ms = timed_region(tr.step_resident, args.steps, world, device)
+    launches = _lib.launch_count - l0
+    clocks = sampler.stop() if rank == 0 else None
+    value = imgs_per_step * args.steps / (ms * 1e-3)
+
+    e2e = None
+    if not args.no_e2e:
+        for _ in range(2):
+            tr.step_e2e()
+        ms_e2e = timed_region(tr.step_e2e, args.steps, world, device)
+        e2e = {"value": round(imgs_per_step * args.steps / (ms_e2e * 1e-3), 2), "unit": UNIT,
+               "h2d_bytes_per_step": tr.h2d_bytes_per_step, "d2h_bytes_per_step": 4,
+               "ms_per_step": round(ms_e2e / args.steps, 3)}
+
+    fam, prof_step_ms = profile_kernels(tr, device)
+    timeout_flag = _lib.load().cnx_debug_timeout_flag()
+    if rank != 0:
+        if world > 1:
+            torch.distributed.destroy_process_group()
+        return 0
+
+    pk = peaks()
+    kernels = {}
+    for name, d in fam.items():
+        k = {"launches_per_step": d["launches"], "ms_per_step": round(d["ms"], 4),
+             "share_of_step": round(d["ms"] / prof_step_ms, 4)}
+        if d["work"] > 0:
+            if d["bound"] == "hbm":
+                k.update(bound="hbm", achieved=round(d["work"] / d["ms"] * 1e-6, 1), unit="GB/s",
+                         peak=pk["hbm_gbs"])
+            else:
+                k.update(bound="tensor", achieved=round(d["work"] / d["ms"] * 1e-9, 1),
+                         unit="TFLOP/s", peak=pk["bf16_tflops_sustained"])
+            k["frac"] = round(k["achieved"] / k["peak"], 4)
+        kernels[name] = k
+    dom = max((n for n in kernels if "frac" in kernels[n]), key=lambda n: kernels[n]["ms_per_step"])
+    roof = {"kernel": dom, "bound": kernels[dom]["bound"], "achieved": kernels[dom]["achieved"],
+            "peak": kernels[dom]["peak"], "unit": kernels[dom]["unit"], "frac": kernels[dom]["frac"],
+            "traffic": None, "peak_source": pk["source"] +
+            (" sustained bf16" if kernels[dom]["bound"] == "tensor" else " copy bandwidth"),
+            "how": "sum of algorithmic work over this family's launches in one optimizer step / "
+                   "sum of their CUDA-event durations (instrumented step after the timed region)"}
+
+    cpu = None
+    if not args.no_cpu_baseline and world == 1:
+        ips, cms, cores, sample = run_cpu_reference(2, 1, 8, args.res, "convnext_base")
+        cpu = {"value": round(ips, 3), "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": sample, "ms_per_step": round(cms, 1)}
+
+    line = {
+        "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": round(ms / args.steps, 3),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+        "data": "synthetic",
+        "config": {"workload": f"ConvNeXt-Base 44-class {args.res}x{args.res} bf16 AMP training "
+                               f"step, micro-batch {args.micro_batch} x accumulation {ACCUM} per "
+                               "GPU (BASELINE config 2; config 3 layout for N>1)",
+                   "global_batch": imgs_per_step, "micro_batch_per_gpu": args.micro_batch,
+                   "accumulation": ACCUM, "parallelism": f"dp{world}",
+                   "step": "mixup/cutmix + fwd + soft-CE + bwd (x2) + unscale + clip 1.0 + "
+                           "AdamW + scheduler + EMA",
+                   "l2": "per-step working set (activations + 350 MB fp32 weights, >10 GB) "
+                         "exceeds the 126 MB L2; no explicit flush"},
+        "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+        "roofline": roof, "kernels": kernels, "cpu_baseline": cpu,
+        "profiled_step_ms": round(prof_step_ms, 3), "timeout_flag": timeout_flag,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        torch.distributed.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    _args = parse_args()
+    sys.exit(main_reference(_args) if _args.impl == "reference" else main_b200(_args))

@@ -95,6 +95,27 @@ def check(rc: int, what: str) -> None:
         raise CnxError(f"{what} failed with status {rc}: {last_error()}")
 
 
+# kernels launched by one successful call of each entry point (bench.py's `gpu_launches` claim;
+# cudaMemsetAsync nodes are not counted)
+LAUNCHES_PER_CALL = {
+    "cnx_prep_block_weights": 4, "cnx_unfold_block_grads": 3, "cnx_dwconv_ln_fwd": 1,
+    "cnx_dwconv_ln_bwd": 1, "cnx_gemm_bf16": 1, "cnx_fc1_gelu_fwd": 1, "cnx_fc2_residual_fwd": 1,
+    "cnx_mlp_bwd_dz": 1, "cnx_mlp_bwd_dxhat": 1, "cnx_mlp_bwd_wgrad": 2, "cnx_mix_batch": 1,
+    "cnx_softce_fwd_bwd": 1, "cnx_ema_lerp_multi": 1, "cnx_nchw_f32_to_nhwc_bf16": 1,
+    "cnx_nhwc_bf16_to_nchw_f32": 1,
+}
+launch_count = 0          # total kernels launched through this binding
+call_hook = None          # optional callable(name, phase, args), phase in {"pre", "post"} (profiling)
+
+
 def call(name: str, *args) -> None:
     """Invoke an int-returning entry point and raise CnxError on failure."""
-    check(getattr(load(), name)(*args), name)
+    global launch_count
+    fn = getattr(load(), name)
+    if call_hook is not None:
+        call_hook(name, "pre", args)
+    rc = fn(*args)
+    if call_hook is not None:
+        call_hook(name, "post", args)
+    check(rc, name)
+    launch_count += LAUNCHES_PER_CALL.get(name, 0)

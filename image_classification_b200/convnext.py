@@ -27,9 +27,11 @@ class LayerNorm2d(nn.LayerNorm):
     """LayerNorm over the channel dim of an NCHW tensor (timm's LayerNorm2d)."""
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        x = x.permute(0, 2, 3, 1)
-        x = F.layer_norm(x, self.normalized_shape, self.weight, self.bias, self.eps)
-        return x.permute(0, 3, 1, 2)
+        y = x.permute(0, 2, 3, 1)
+        y = F.layer_norm(y, self.normalized_shape, self.weight, self.bias, self.eps)
+        # autocast runs layer_norm in fp32; hand the stream back in the dtype it came in so the
+        # blocks keep their zero-copy bf16 channels_last path
+        return y.to(x.dtype).permute(0, 3, 1, 2)
 
 
 class ConvNeXtStage(nn.Module):

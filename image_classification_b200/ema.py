@@ -76,8 +76,13 @@ class EMAB200:
         for p, s in zip(params, shadows):
             if p.dtype != torch.float32 or s.dtype != torch.float32:
                 raise _lib.CnxError("EMAB200: parameters and shadows must be float32")
-            if not p.is_contiguous() or not s.is_contiguous():
-                raise _lib.CnxError("EMAB200: parameters and shadows must be contiguous")
+            # the lerp is elementwise over the storage: any dense layout works (channels_last
+            # conv weights included) as long as parameter and shadow share it
+            dense = p.is_contiguous() or (p.dim() == 4 and
+                                          p.is_contiguous(memory_format=torch.channels_last))
+            if not dense or p.stride() != s.stride():
+                raise _lib.CnxError("EMAB200: parameters must be dense and laid out like their "
+                                    f"shadows (got strides {p.stride()} vs {s.stride()})")
         numel = np.array([p.numel() for p in params], dtype=np.int64)
         nchunks = (numel + chunk - 1) // chunk
         prefix = np.zeros(len(params) + 1, dtype=np.int64)

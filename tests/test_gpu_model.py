@@ -1,0 +1,133 @@
+"""GPU parity at model / training-step level: the block dropped into a timm-style ConvNeXt, and the
+reference loop's ordering (AMP, accumulate 2, clip, AdamW, scheduler, EMA) on top of it."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import block_oracle, loop_oracle  # noqa: E402  (checker only)
+
+BF16_REL = 2e-2
+
+
+def _dev():
+    assert torch.cuda.is_available(), "GPU tests need a B200"
+    return torch.device("cuda:0")
+
+
+def _rel(a, b):
+    a, b = a.double(), b.double()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def _pair(depths, dims, dev, gamma_mode="o1"):
+    """(oracle fp32 model, product model with swapped blocks), identical weights."""
+    from image_classification_b200.block import swap_blocks
+    from image_classification_b200.convnext import ConvNeXtTimmLike
+    torch.manual_seed(0)
+    ref = ConvNeXtTimmLike(depths, dims, 44, block_cls=block_oracle.OracleConvNeXtBlock).to(dev)
+    with torch.no_grad():
+        for n, p in ref.named_parameters():
+            if n.endswith("gamma"):
+                p.copy_(torch.rand_like(p) * 0.9 + 0.1 if gamma_mode == "o1" else torch.full_like(p, 1e-6))
+            elif "blocks" in n and p.dim() == 1 and "norm.weight" not in n:
+                p.copy_(torch.randn_like(p) * 0.1)
+            elif "blocks" in n and p.dim() > 1:
+                p.mul_(3.0)          # make the branch matter at random init
+    prod = ConvNeXtTimmLike(depths, dims, 44, block_cls=block_oracle.OracleConvNeXtBlock).to(dev)
+    prod.load_state_dict(ref.state_dict())
+    n = swap_blocks(prod)
+    assert n == sum(depths)
+    assert sorted(prod.state_dict()) == sorted(ref.state_dict())     # timm names survive the swap
+    return ref, prod
+
+
+@pytest.mark.parametrize("gamma_mode", ["o1", "1e-6"])
+def test_model_logits_loss_and_grads_vs_oracle(cnx_lib, gamma_mode):
+    from image_classification_b200.loss import SoftTargetCrossEntropyB200
+    dev = _dev()
+    ref, prod = _pair((1, 1, 2, 1), (96, 192, 384, 768), dev, gamma_mode)   # Tiny widths
+    torch.manual_seed(3)
+    x = torch.randn(4, 3, 64, 64, device=dev)
+    t = torch.softmax(torch.randn(4, 44, device=dev) * 3, 1)
+    # oracle: fp32 everywhere
+    lo = ref(x)
+    loss_o = block_oracle.soft_ce_ref(lo, t, 0.1)
+    loss_o.backward()
+    # product: bf16 autocast like the training loop
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        lp = prod(x.contiguous(memory_format=torch.channels_last))
+        loss_p = SoftTargetCrossEntropyB200(0.1)(lp, t)
+    loss_p.backward()
+    assert _rel(lp.float(), lo) < BF16_REL, _rel(lp.float(), lo)
+    assert abs(loss_p.item() - loss_o.item()) < BF16_REL * abs(loss_o.item())
+    gn_o = torch.sqrt(sum((p.grad.double() ** 2).sum() for p in ref.parameters()))
+    gn_p = torch.sqrt(sum((p.grad.double() ** 2).sum() for p in prod.parameters()))
+    assert abs(gn_p - gn_o) < BF16_REL * gn_o
+    worst = max(((_rel(p.grad, q.grad), n) for (n, p), (_, q) in
+                 zip(prod.named_parameters(), ref.named_parameters())), key=lambda v: v[0])
+    # per-tensor max error grows with depth in bf16; the block-level tests hold 2e-2 per kernel
+    assert worst[0] < 6e-2, worst
+
+
+def test_train_step_follows_reference_ordering(cnx_lib):
+    """accumulate 2: optimizer/scheduler/EMA move on every 2nd micro-batch only (:225-237);
+    the AMP-branch loss is NOT divided by the accumulation steps (:223)."""
+    from image_classification_b200 import ema as ema_mod, loss as loss_mod, mix, train_step
+    dev = _dev()
+    _, model = _pair((1, 1, 1, 1), (64, 128, 256, 512), dev)
+    model.train()
+    params = [p for p in model.parameters() if p.requires_grad]
+    opt = torch.optim.AdamW(params, lr=1e-3, weight_decay=1e-2)
+    sched = train_step.get_cosine_schedule_with_warmup(opt, 2, 20, 1e-6)
+    scaler = torch.amp.GradScaler("cuda")
+    ema = ema_mod.EMAB200(model, 0.9997)
+    crit = loss_mod.SoftTargetCrossEntropyB200(0.1)
+    step = train_step.TrainStep(model, crit, opt, sched, scaler, ema,
+                                train_step.StepConfig(2, 1.0, 44))
+    mixer = mix.BatchMixUpCutMix(0.2, 1.0, 0.5, 44)
+    rng = np.random.RandomState(0)
+    g = torch.Generator().manual_seed(0)
+    w0 = params[0].detach().clone()
+    s0 = {k: v.clone() for k, v in ema.shadow.items()}
+    losses = []
+    for i in range(6):
+        x = torch.randn(8, 3, 64, 64, generator=g).to(dev)
+        y = torch.randint(0, 44, (8,), generator=g).to(dev)
+        xm, t = mixer(x, y, rng=rng)
+        losses.append(step.micro_step(xm, t, i).item())
+        boundary = (i + 1) % 2 == 0
+        if i == 0:
+            assert torch.equal(params[0], w0) and params[0].grad is not None     # no step yet
+            assert all(torch.equal(ema.shadow[k], s0[k]) for k in s0)
+        if boundary:
+            assert all(p.grad is None or float(p.grad.abs().sum()) == 0 for p in params)
+    assert not torch.equal(params[0], w0)
+    assert sched.last_epoch == 3                     # one scheduler step per optimizer step
+    assert all(np.isfinite(losses)) and losses[0] > 2.0    # un-divided CE of 44 classes ~ ln 44
+    # EMA shadow is exactly three reference lerps behind the parameters' trajectory: check last
+    name = next(iter(ema.shadow))
+    assert not torch.equal(ema.shadow[name], s0[name])
+
+
+def test_loop_mirror_matches_oracle_loop_on_first_steps(cnx_lib):
+    """Same data, same init: the B200 loop (bf16 AMP branch) and the oracle CPU loop (reference
+    order, fp32) see the same first losses within bf16 tolerance."""
+    from image_classification_b200 import loss as loss_mod, train_step
+    dev = _dev()
+    ref, prod = _pair((1, 1, 1, 1), (64, 128, 256, 512), dev)
+    ref = ref.cpu().train()
+    prod.train()
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(2, 8, 3, 64, 64, generator=g)
+    t = torch.softmax(torch.randn(2, 8, 44, generator=g) * 2, -1)
+    crit_o = torch.nn.CrossEntropyLoss(label_smoothing=0.1)
+    lo = [crit_o(ref(x[i]), t[i]).item() for i in range(2)]
+    step = train_step.TrainStep(prod, loss_mod.SoftTargetCrossEntropyB200(0.1),
+                                torch.optim.AdamW(prod.parameters(), lr=1e-4),
+                                None, torch.amp.GradScaler("cuda"), None,
+                                train_step.StepConfig(2, 1.0, 44))
+    lp = [step.micro_step(x[i].to(dev), t[i].to(dev), i).item() for i in range(2)]
+    for a, b in zip(lp, lo):
+        assert abs(a - b) < BF16_REL * abs(b), (lp, lo)

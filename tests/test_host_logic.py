@@ -1,0 +1,138 @@
+"""CPU-side checks: host logic, layering rules, and the N>1 gradient exchange on gloo (world 2)."""
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+import torch
+
+from conftest import ROOT
+
+
+def test_product_never_imports_the_oracle():
+    """A product path that routes through oracle/ voids every parity claim."""
+    pkg = os.path.join(ROOT, "image_classification_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", text, re.M), f
+                assert "/root/reference" not in text or f.endswith(".py") or "//" in text
+
+
+def test_nothing_on_the_gpu_path_reads_the_reference_tree():
+    """/root/reference does not exist on the GPU box: only oracle/ref_loader.py and
+    oracle/gen_golden.py (container-only tools) may open it; citations in comments are fine."""
+    for rel in ("bench.py", "__graft_entry__.py", "image_classification_b200/mix.py",
+                "image_classification_b200/ema.py", "image_classification_b200/train_step.py"):
+        text = open(os.path.join(ROOT, rel)).read()
+        assert "ref_loader" not in text and "load_reference" not in text, rel
+
+
+def test_ops_fail_loudly_without_cuda():
+    from image_classification_b200 import _lib, ops
+    from image_classification_b200.block import ConvNeXtBlockB200
+    from image_classification_b200.loss import SoftTargetCrossEntropyB200
+    with pytest.raises(_lib.CnxError):
+        ops.dwconv_ln_fwd(torch.zeros(1, 4, 4, 64, dtype=torch.bfloat16), torch.zeros(49, 64),
+                          torch.zeros(64))
+    with pytest.raises(_lib.CnxError):
+        ConvNeXtBlockB200(64)(torch.zeros(1, 64, 4, 4))
+    with pytest.raises(_lib.CnxError):
+        SoftTargetCrossEntropyB200(0.1)(torch.zeros(2, 5), torch.zeros(2, 5))
+
+
+def test_skeleton_matches_timm_attribute_contract():
+    """What the reference touches: stem, stages[i].blocks[-1].conv_dw.out_channels
+    (train_advanced_v4.py:106-111), head.{global_pool,norm,flatten,fc} (:140-143)."""
+    from image_classification_b200.convnext import create_convnext
+    from oracle.block_oracle import OracleConvNeXtBlock
+    m = create_convnext("convnext_tiny", 44, block_cls=OracleConvNeXtBlock)
+    assert [s.blocks[-1].conv_dw.out_channels for s in m.stages] == [96, 192, 384, 768]
+    assert [len(s.blocks) for s in m.stages] == [3, 3, 9, 3]
+    for attr in ("global_pool", "norm", "flatten", "fc"):
+        assert hasattr(m.head, attr)
+    x = torch.randn(2, 3, 64, 64)
+    feats = m.stages(m.stem(x))
+    out = m.head.fc(m.head.flatten(m.head.norm(m.head.global_pool(feats))))   # the :140-143 path
+    assert torch.allclose(out, m(x)) and out.shape == (2, 44)
+    n_params = sum(p.numel() for p in create_convnext("convnext_base", 44,
+                                                       block_cls=OracleConvNeXtBlock).parameters())
+    assert n_params == 87_611_564          # SURVEY.md §8 a1 (probe on the torchvision equivalent)
+
+
+def test_skeleton_equals_torchvision_convnext():
+    """The oracle model (skeleton + oracle block) reproduces torchvision's convnext_tiny."""
+    import torchvision
+    from image_classification_b200.convnext import create_convnext
+    from oracle.block_oracle import OracleConvNeXtBlock, convert_torchvision_convnext
+    torch.manual_seed(0)
+    tv = torchvision.models.convnext_tiny(num_classes=44, stochastic_depth_prob=0.0).eval()
+    m = create_convnext("convnext_tiny", 44, block_cls=OracleConvNeXtBlock).eval()
+    missing = m.load_state_dict(convert_torchvision_convnext(tv.state_dict()), strict=True)
+    assert not missing.missing_keys and not missing.unexpected_keys
+    x = torch.randn(2, 3, 64, 64)
+    with torch.no_grad():
+        assert torch.allclose(m(x), tv(x), atol=1e-5, rtol=1e-4)
+
+
+DDP_WORKER = r'''
+import os, sys, torch, torch.distributed as dist
+sys.path.insert(0, os.environ["CNX_ROOT"])
+from image_classification_b200.ddp import BucketedGradReducer
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+dist.init_process_group("gloo")
+torch.manual_seed(0)
+model = torch.nn.Sequential(torch.nn.Linear(16, 32), torch.nn.GELU(), torch.nn.Linear(32, 8))
+unused = torch.nn.Linear(4, 4)            # like the reference's discarded aux heads
+params = list(model.parameters()) + list(unused.parameters())
+red = BucketedGradReducer(params, bucket_bytes=1024)
+g = torch.Generator().manual_seed(7)
+X = torch.randn(2, 2, 6, 16, generator=g)      # [micro, rank, b, d]
+Y = torch.randn(2, 2, 6, 8, generator=g)
+def micro(i, r, m):
+    return ((m(X[i, r]) - Y[i, r]) ** 2).mean()
+# warm-up backward to discover the unused parameters
+red.set_sync(False); micro(0, rank, model).backward(); red.discover_unused(bucket_bytes=1024)
+for p in params: p.grad = None
+assert len(red.params) == 4 and len(red.buckets) >= 2
+# accumulate 2 micro-batches; exchange on the boundary only
+red.set_sync(False); micro(0, rank, model).backward()
+g_before = [p.grad.clone() for p in model.parameters()]
+red.set_sync(True); micro(1, rank, model).backward(); red.finish()
+# single-process truth: mean over ranks of (sum over micro-batches of local grads)
+ref = [torch.zeros_like(p) for p in model.parameters()]
+for r in range(world):
+    m2 = torch.nn.Sequential(torch.nn.Linear(16, 32), torch.nn.GELU(), torch.nn.Linear(32, 8))
+    m2.load_state_dict(model.state_dict())
+    (micro(0, r, m2) + micro(1, r, m2)).backward()
+    for a, p in zip(ref, m2.parameters()): a += p.grad / world
+for a, p in zip(ref, model.parameters()):
+    assert torch.allclose(a, p.grad, atol=1e-6), (rank, (a - p.grad).abs().max())
+assert all(p.grad is None for p in unused.parameters())
+dist.barrier(); dist.destroy_process_group()
+print("rank", rank, "ok")
+'''
+
+
+def test_bucketed_grad_reducer_world2_gloo(tmp_path):
+    script = tmp_path / "ddp_worker.py"
+    script.write_text(DDP_WORKER)
+    env = dict(os.environ, CNX_ROOT=ROOT, MASTER_ADDR="127.0.0.1", MASTER_PORT="29571",
+               WORLD_SIZE="2", OMP_NUM_THREADS="1")
+    procs = [subprocess.Popen([sys.executable, str(script)], env=dict(env, RANK=str(r)),
+                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+             for r in range(2)]
+    outs = [p.communicate(timeout=180)[0] for p in procs]
+    for r, (p, o) in enumerate(zip(procs, outs)):
+        assert p.returncode == 0, o
+        assert f"rank {r} ok" in o
+
+
+def test_bench_reference_arm_other_ranks_exit_quietly():
+    env = dict(os.environ, RANK="1", WORLD_SIZE="2", LOCAL_RANK="1")
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference",
+                          "--gpus", "2", "--steps", "1", "--warmup", "0"], env=env,
+                         capture_output=True, text=True, timeout=120)
+    assert res.returncode == 0 and res.stdout.strip() == ""
