@@ -34,6 +34,10 @@ class MixPlanEntry(ctypes.Structure):
     ]
 
 
+# cnx_op values (include/cnx_b200.h)
+(CNX_OP_DWCONV_LN_FWD, CNX_OP_DWCONV_LN_BWD, CNX_OP_MLP_FWD, CNX_OP_MLP_BWD, CNX_OP_MIX_BATCH,
+ CNX_OP_SOFTCE, CNX_OP_EMA) = range(7)
+
 P = c_void_p
 I = c_int
 I64 = c_int64
@@ -98,8 +102,8 @@ def check(rc: int, what: str) -> None:
 # kernels launched by one successful call of each entry point (bench.py's `gpu_launches` claim;
 # cudaMemsetAsync nodes are not counted)
 LAUNCHES_PER_CALL = {
-    "cnx_prep_block_weights": 4, "cnx_unfold_block_grads": 3, "cnx_dwconv_ln_fwd": 1,
-    "cnx_dwconv_ln_bwd": 1, "cnx_gemm_bf16": 1, "cnx_fc1_gelu_fwd": 1, "cnx_fc2_residual_fwd": 1,
+    "cnx_prep_block_weights": 4, "cnx_unfold_block_grads": 3, "cnx_dwconv_ln_fwd": 2,
+    "cnx_dwconv_ln_bwd": 2, "cnx_gemm_bf16": 1, "cnx_fc1_gelu_fwd": 1, "cnx_fc2_residual_fwd": 1,
     "cnx_mlp_bwd_dz": 1, "cnx_mlp_bwd_dxhat": 1, "cnx_mlp_bwd_wgrad": 2, "cnx_mix_batch": 1,
     "cnx_softce_fwd_bwd": 1, "cnx_ema_lerp_multi": 1, "cnx_nchw_f32_to_nhwc_bf16": 1,
     "cnx_nhwc_bf16_to_nchw_f32": 1,

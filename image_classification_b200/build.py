@@ -19,8 +19,8 @@ LIB_PATH = os.path.join(HERE, "libcnx_b200.so")
 SOURCES = [
     "cnx_util.cu",
     "cnx_api.cu",
-    "dwconv_ln_fwd.cu",
-    "dwconv_ln_bwd.cu",
+    "dwconv7.cu",
+    "ln_rows.cu",
     "mlp_gemm.cu",
     "elementwise.cu",
     "prep.cu",

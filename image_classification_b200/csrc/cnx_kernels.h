@@ -6,16 +6,20 @@
 
 namespace cnx {
 
-// ---- dwconv_ln_fwd.cu
+// ---- dwconv7.cu (conv engine) + ln_rows.cu (row LayerNorm)
 int dwconv_ln_fwd(const void* x, const float* wt, const float* bias, void* xhat, float* mean,
                   float* rstd, int B, int H, int W, int C, float eps, cudaStream_t stream);
 
-// ---- dwconv_ln_bwd.cu
 size_t dwconv_ln_bwd_workspace_bytes(int B, int H, int W, int C);
 int dwconv_ln_bwd(const void* dxhat, const void* xhat, const float* rstd, const void* x,
                   const void* dy, const float* wt, void* dx, float* dwt, float* dbias,
                   float* dy_colsum, int B, int H, int W, int C, void* workspace, size_t ws_bytes,
                   cudaStream_t stream);
+// pure depthwise-conv backward: dconv = dL/d(conv output) already formed (by ln_rows_bwd or by the
+// LN-backward epilogue of the fc1 data-gradient GEMM)
+int dwconv_bwd(const void* dconv, const void* x, const void* dy, const float* wt, void* dx,
+               float* dwt, float* dbias, float* dy_colsum, int B, int H, int W, int C,
+               cudaStream_t stream);
 
 // ---- mlp_gemm.cu  (tcgen05 / TMEM / TMA)
 enum GemmEpilogue : int {

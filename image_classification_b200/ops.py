@@ -110,8 +110,11 @@ def dwconv_ln_bwd(dxhat, xhat, rstd, x_nhwc, dy, wt_dw):
     dwt = torch.empty(49, C, device=dev, dtype=torch.float32)
     dbias = torch.empty(C, device=dev, dtype=torch.float32)
     dycs = torch.empty(C, device=dev, dtype=torch.float32)
+    # scratch for dconv = LN-backward(dxhat): sized by the library, owned by PyTorch's allocator
+    ws_bytes = int(_lib.load().cnx_workspace_bytes(_lib.CNX_OP_DWCONV_LN_BWD, B, H, W, C))
+    ws = torch.empty(ws_bytes, device=dev, dtype=torch.uint8)
     _lib.call("cnx_dwconv_ln_bwd", _p(dxhat), _p(xhat), _p(rstd), _p(x_nhwc), _p(dy), _p(wt_dw),
-              _p(dx), _p(dwt), _p(dbias), _p(dycs), B, H, W, C, None, 0, _stream(x_nhwc))
+              _p(dx), _p(dwt), _p(dbias), _p(dycs), B, H, W, C, _p(ws), ws_bytes, _stream(x_nhwc))
     return dx, dwt, dbias, dycs
 
 

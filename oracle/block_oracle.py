@@ -33,12 +33,18 @@ def block_forward_ref(x, conv_w, conv_b, norm_w, norm_b, fc1_w, fc1_b, fc2_w, fc
     return y + x
 
 
-def dwconv_ln_ref(x_nhwc, conv_w, conv_b, eps: float = LN_EPS):
+def dwconv_ln_ref(x_nhwc, conv_w, conv_b, eps: float = LN_EPS, amp_round=None):
     """Reference for cnx_dwconv_ln_fwd: x [B,H,W,C] -> (xhat, mean, rstd) in x's dtype,
-    LayerNorm WITHOUT affine (the affine is folded into fc1 in the product)."""
+    LayerNorm WITHOUT affine (the affine is folded into fc1 in the product).
+
+    amp_round=torch.bfloat16 restates the reference's autocast numerics: under
+    torch.amp.autocast (/root/reference/train_advanced_v4.py:217) conv2d returns the half type and
+    layer_norm then runs in fp32 ON THAT ROUNDED tensor."""
     B, H, W, C = x_nhwc.shape
     y = F.conv2d(x_nhwc.permute(0, 3, 1, 2), conv_w, conv_b, padding=3, groups=C)
     y = y.permute(0, 2, 3, 1)
+    if amp_round is not None:
+        y = y.to(amp_round).to(x_nhwc.dtype)
     mean = y.mean(-1)
     var = y.var(-1, unbiased=False)
     rstd = torch.rsqrt(var + eps)

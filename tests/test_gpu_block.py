@@ -48,14 +48,22 @@ def test_dwconv_ln_fwd_vs_oracle(cnx_lib, shape):
     w = torch.randn(C, 1, 7, 7, device=dev) * 0.15
     b = torch.randn(C, device=dev) * 0.5
     ref_xhat, ref_mean, ref_rstd = block_oracle.dwconv_ln_ref(x.double(), w.double(), b.double())
+    # statistics are taken over the bf16-rounded conv output, as under the reference's autocast
+    _, amp_mean, amp_rstd = block_oracle.dwconv_ln_ref(x.double(), w.double(), b.double(),
+                                                       amp_round=torch.bfloat16)
     wt = w.reshape(C, 49).t().contiguous()
     xhat, mean, rstd = ops.dwconv_ln_fwd(x.bfloat16(), wt, b)
     assert xhat.shape == (B, H, W, C) and xhat.dtype == torch.bfloat16
-    assert _rel(mean, ref_mean) < FP32_REL or (mean.double() - ref_mean).abs().max() < 1e-5
-    assert _rel(rstd, ref_rstd) < FP32_REL
+    # fp32 kernels vs the autocast-numerics oracle: 1e-4 (a conv sum within half a bf16 ulp of a
+    # rounding boundary may round the other way than fp64 does: allow it in the mean)
+    assert _rel(mean, amp_mean) < FP32_REL or (mean.double() - amp_mean).abs().max() < 2.0 ** -8 * 8 / C
+    assert _rel(rstd, amp_rstd) < FP32_REL + 0.1 / C
+    # and both stay within bf16 tolerance of the exact (un-rounded) statistics
+    assert _rel(mean, ref_mean) < BF16_REL and _rel(rstd, ref_rstd) < BF16_REL
     assert _rel(xhat, ref_xhat) < BF16_REL
-    # tighter: the only rounding left is the final bf16 store (2^-9 relative)
-    assert (xhat.double() - ref_xhat).abs().max() < 2.0 ** -8 * ref_xhat.abs().max() + 1e-3
+    # tighter: two roundings are left — the conv output is rounded to bf16 before LayerNorm (as
+    # under the reference's autocast, where conv2d returns half precision) and the final store
+    assert (xhat.double() - ref_xhat).abs().max() < 2.0 ** -7 * ref_xhat.abs().max() + 1e-3
 
 
 def test_dwconv_ln_fwd_rejects_bad_shapes(cnx_lib):
