@@ -22,6 +22,7 @@ SOURCES = [
     "dwconv7.cu",
     "ln_rows.cu",
     "mlp_gemm.cu",
+    "gemm2.cu",
     "elementwise.cu",
     "prep.cu",
     "layout.cu",

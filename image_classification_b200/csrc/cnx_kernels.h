@@ -42,7 +42,8 @@ struct GemmArgs {
   const void* R; int64_t ldr;   // residual (EPI_BIAS_RESIDUAL) or Z (EPI_GELU_GRAD), bf16
   float* colsum;                // [N] fp32, atomically accumulated (EPI_GELU_GRAD), may be null
 };
-int gemm_bf16(const GemmArgs& a, cudaStream_t stream);
+int gemm_bf16(const GemmArgs& a, cudaStream_t stream);      // gemm2.cu (persistent, warp-specialised)
+int gemm_bf16_v1(const GemmArgs& a, cudaStream_t stream);   // mlp_gemm.cu (round-1 v1, A/B debugging only)
 
 // ---- elementwise.cu
 struct MixPlanEntry {          // one per sample; integers are bit-exact vs the reference RNG order

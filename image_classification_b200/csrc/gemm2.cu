@@ -1,0 +1,674 @@
+// gemm2.cu — persistent, warp-specialised bf16 GEMM on 5th-gen tensor cores for the ConvNeXt MLP
+// (fc1 / fc2 and their data- and weight-gradients), with the block's elementwise work fused into
+// the epilogue.  Supersedes mlp_gemm.cu's one-tile-per-CTA kernel.
+//
+// Replaces mlp.fc1 -> act(GELU) -> mlp.fc2 -> *gamma -> +shortcut of timm's ConvNeXtBlock.forward
+// and their autograd backward (reached from
+// /root/reference/train_advanced_v4.py:134-135, backward from :223).
+//
+//   D[M,N] = epilogue( A[M,K] * B[N,K]^T )        fp32 accumulate in tensor memory
+//
+// One CTA per SM, 10 warps, looping over 128 x BN output tiles (BN = 256 or 128):
+//   warp 0 / lane 0 : TMA producer — cp.async.bulk.tensor into a ring of 128B-swizzled stages,
+//                     running ahead across tile boundaries
+//   warp 1          : TMEM allocator; lane 0 = MMA issuer — tcgen05.mma.cta_group::1.kind::f16
+//                     (128 x BN x 16), TWO accumulators of BN columns in tensor memory so tile
+//                     i+1's main loop overlaps tile i's epilogue; tcgen05.commit frees ring slots
+//                     and publishes the accumulator
+//   warps 2..9      : epilogue — tcgen05.ld (thread = accumulator row, two warps per TMEM lane
+//                     quarter, one per column half), fused math in registers, results staged in
+//                     128B-swizzled shared memory (conflict-free 16-byte stores) and written by TMA
+//                     (cp.async.bulk.tensor store: fully coalesced, clips ragged M / N edges);
+//                     residual / pre-activation operands arrive by TMA into the same staging
+//                     layout one chunk ahead of use.
+// A CTA keeps the same column block for its whole life whenever the tile grid allows it, so the
+// per-column sums of the GELU-gradient epilogue stay in registers (one atomic per column per CTA).
+// GELU and its derivative are degree-8/9 odd minimax polynomials evaluated with packed
+// fma.rn.f32x2 (|err| < 5e-5, far below the bf16 output resolution): the epilogue is issue-bound.
+// Operands may be K-major (row-major [rows,K]) or MN-major (stored [K,rows]); the latter is what
+// the weight-gradient GEMMs need (K = tokens), so no activation transpose ever touches HBM.
+#include "cnx_common.cuh"
+#include "cnx_kernels.h"
+
+namespace cnx {
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;                 // 64 bf16 = 128 B = one swizzle row
+constexpr int kThreads = 320;          // 10 warps
+constexpr int kEpiWarps = 8;
+constexpr int EPI_ATOMIC_F32 = 5;      // internal: split-K fp32 reduction
+constexpr uint32_t kChunkBytes = 32 * 128;   // staging chunk: 32 rows x 64 bf16, 128B swizzle
+
+template <int BN>
+struct Cfg {
+  static constexpr int kStages = (BN == 256) ? 3 : 4;
+  static constexpr uint32_t kABytes = BM * BK * 2;
+  static constexpr uint32_t kBBytes = BN * BK * 2;
+  static constexpr uint32_t kStageBytes = kABytes + kBBytes;
+  static constexpr uint32_t kEpiBytes = kEpiWarps * 2 * kChunkBytes;     // 64 KB
+  static constexpr uint32_t kBarBytes = 256;
+  static constexpr uint32_t kTotal = kStages * kStageBytes + kEpiBytes + kBarBytes + 1024;
+  static constexpr uint32_t kTmemCols = 2 * BN;
+};
+
+struct Gemm2Params {
+  int* timeout_flag;
+  int M, N, K;
+  int a_mn, b_mn;
+  int tiles_m, tiles_n, splits, kb_per_split, nkb_total, items;
+  float* D0f; int64_t ldd0;        // fp32 output (EPI_STORE_F32 / EPI_ATOMIC_F32)
+  const float* bias;
+  float* colsum;
+};
+
+// ---- packed-fp32 helpers (one issue slot, two lanes)
+__device__ __forceinline__ float2 fmul2(float2 a, float2 b) {
+  float2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;"
+      : "=l"(reinterpret_cast<uint64_t&>(d))
+      : "l"(reinterpret_cast<uint64_t&>(a)), "l"(reinterpret_cast<uint64_t&>(b)));
+  return d;
+}
+__device__ __forceinline__ float2 splat(float v) { return make_float2(v, v); }
+__device__ __forceinline__ float2 clamp4(float2 z) {
+  return make_float2(fminf(fmaxf(z.x, -4.0f), 4.0f), fminf(fmaxf(z.y, -4.0f), 4.0f));
+}
+// Phi(z) = 0.5 + zc * P(zc^2), zc = clamp(z, +-4): odd minimax fit of the normal CDF,
+// |err| < 5e-6 on [-4, 4] (Phi(4) = 1 - 3.2e-5 beyond)
+__device__ __forceinline__ float2 normcdf2(float2 z) {
+  const float2 zc = clamp4(z);
+  const float2 t = fmul2(zc, zc);
+  float2 p = splat(8.062970875e-11f);
+  p = ffma2(p, t, splat(-7.003161325e-09f));
+  p = ffma2(p, t, splat(2.716070385e-07f));
+  p = ffma2(p, t, splat(-6.294871603e-06f));
+  p = ffma2(p, t, splat(9.890699615e-05f));
+  p = ffma2(p, t, splat(-1.133916961e-03f));
+  p = ffma2(p, t, splat(9.877464146e-03f));
+  p = ffma2(p, t, splat(-6.641058180e-02f));
+  p = ffma2(p, t, splat(3.989227066e-01f));
+  return ffma2(zc, p, splat(0.5f));
+}
+__device__ __forceinline__ float2 gelu2(float2 z) { return fmul2(z, normcdf2(z)); }
+// d/dz [z Phi(z)] = Phi(z) + z phi(z) = 0.5 + zc * Q(zc^2): |err| < 5e-5 on [-4, 4]
+__device__ __forceinline__ float2 gelu_grad2(float2 z) {
+  const float2 zc = clamp4(z);
+  const float2 t = fmul2(zc, zc);
+  float2 p = splat(-5.247632696e-11f);
+  p = ffma2(p, t, splat(4.926839658e-09f));
+  p = ffma2(p, t, splat(-2.070275028e-07f));
+  p = ffma2(p, t, splat(5.183908664e-06f));
+  p = ffma2(p, t, splat(-8.703009122e-05f));
+  p = ffma2(p, t, splat(1.043571623e-03f));
+  p = ffma2(p, t, splat(-9.208667071e-03f));
+  p = ffma2(p, t, splat(5.941560108e-02f));
+  p = ffma2(p, t, splat(-2.656715040e-01f));
+  p = ffma2(p, t, splat(7.978260581e-01f));
+  return ffma2(zc, p, splat(0.5f));
+}
+
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c,
+                                             uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c),
+               "r"(d)
+               : "memory");
+}
+__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
+  uint4 r;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "r"(addr)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ uint32_t ld_shared_b32(uint32_t addr) {
+  uint32_t r;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(r) : "r"(addr) : "memory");
+  return r;
+}
+__device__ __forceinline__ void st_global_v4f(float* p, float a, float b, float c, float d) {
+  asm volatile("st.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+__device__ __forceinline__ void red_add_v4f(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c),
+               "f"(d)
+               : "memory");
+}
+
+struct ItemCoord { int m_blk, n_blk, kb_begin, kb_end; };
+__device__ __forceinline__ ItemCoord decode(const Gemm2Params& p, int w) {
+  ItemCoord c;
+  c.n_blk = w % p.tiles_n;
+  const int rest = w / p.tiles_n;
+  c.m_blk = rest % p.tiles_m;
+  const int split = rest / p.tiles_m;
+  c.kb_begin = split * p.kb_per_split;
+  c.kb_end = min(p.nkb_total, c.kb_begin + p.kb_per_split);
+  return c;
+}
+
+template <int BN, int EPI>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+             const __grid_constant__ CUtensorMap map_d0, const __grid_constant__ CUtensorMap map_d1,
+             const __grid_constant__ CUtensorMap map_r, const Gemm2Params p) {
+  using L = Cfg<BN>;
+  constexpr int kStages = L::kStages;
+  constexpr bool kHasR = (EPI == EPI_BIAS_RESIDUAL || EPI == EPI_GELU_GRAD);
+  constexpr bool kF32Out = (EPI == EPI_STORE_F32 || EPI == EPI_ATOMIC_F32);
+  constexpr int kChunks = BN / 2 / 64;         // 64-column chunks per epilogue warp per tile
+
+  extern __shared__ unsigned char smem_dyn[];
+  // 1024-byte alignment: the 128B swizzle pattern is a function of address bits [7,10)
+  const uint32_t raw = smem_u32(smem_dyn);
+  unsigned char* smem = smem_dyn + ((1024u - (raw & 1023u)) & 1023u);
+  unsigned char* epi_base = smem + kStages * L::kStageBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(epi_base + L::kEpiBytes);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full_bar = empty_bar + kStages;     // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;      // [2]
+  uint64_t* r_bar = tmem_empty_bar + 2;              // [kEpiWarps]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(r_bar + kEpiWarps);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+    if (!kF32Out) tma_prefetch_desc(&map_d0);
+    if (EPI == EPI_BIAS_GELU) tma_prefetch_desc(&map_d1);
+    if (kHasR) tma_prefetch_desc(&map_r);
+#pragma unroll
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tmem_full_bar[b], 1);
+      mbar_init(&tmem_empty_bar[b], kEpiWarps);
+    }
+#pragma unroll
+    for (int w = 0; w < kEpiWarps; ++w) mbar_init(&r_bar[w], 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, L::kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ------------------------------------------------------------ TMA producer
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int w = blockIdx.x; w < p.items; w += gridDim.x) {
+        const ItemCoord c = decode(p, w);
+        const int m0 = c.m_blk * BM, n0 = c.n_blk * BN;
+        for (int kb = c.kb_begin; kb < c.kb_end; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1, p.timeout_flag);
+          unsigned char* sa = smem + stage * L::kStageBytes;
+          unsigned char* sb = sa + L::kABytes;
+          mbar_arrive_expect_tx(&full_bar[stage], L::kStageBytes);
+          const int k0 = kb * BK;
+          if (!p.a_mn) {
+            tma_load_2d(sa, &map_a, &full_bar[stage], k0, m0);            // box [128 rows][64 k]
+          } else {
+#pragma unroll
+            for (int a = 0; a < BM / 64; ++a)                             // box [64 k][64 rows]
+              tma_load_2d(sa + a * (BK * 128), &map_a, &full_bar[stage], m0 + a * 64, k0);
+          }
+          if (!p.b_mn) {
+            tma_load_2d(sb, &map_b, &full_bar[stage], k0, n0);            // box [BN rows][64 k]
+          } else {
+#pragma unroll
+            for (int a = 0; a < BN / 64; ++a)
+              tma_load_2d(sb + a * (BK * 128), &map_b, &full_bar[stage], n0 + a * 64, k0);
+          }
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // -------------------------------------------------------------- MMA issuer
+      const uint32_t idesc = umma_idesc_bf16(BM, BN, p.a_mn, p.b_mn);
+      int stage = 0;
+      uint32_t phase = 0;
+      int i = 0;
+      for (int w = blockIdx.x; w < p.items; w += gridDim.x, ++i) {
+        const ItemCoord c = decode(p, w);
+        const int ab = i & 1;
+        mbar_wait(&tmem_empty_bar[ab], ((i >> 1) & 1) ^ 1, p.timeout_flag);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + ab * BN;
+        for (int kb = c.kb_begin; kb < c.kb_end; ++kb) {
+          mbar_wait(&full_bar[stage], phase, p.timeout_flag);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
+          const uint32_t sb = sa + L::kABytes;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            // K-major: 16 k-elements = 32 B inside the swizzled 128 B row; 8-row groups 1024 B
+            // apart.  MN-major: 16 k-rows = 2048 B; 8-k groups 1024 B apart (SBO), 64-wide MN
+            // atoms BK*128 B apart (LBO).
+            const uint64_t da = p.a_mn ? umma_desc_sw128(sa + k * 2048, BK * 128, 1024)
+                                       : umma_desc_sw128(sa + k * 32, 16, 1024);
+            const uint64_t db = p.b_mn ? umma_desc_sw128(sb + k * 2048, BK * 128, 1024)
+                                       : umma_desc_sw128(sb + k * 32, 16, 1024);
+            umma_bf16(tmem_d, da, db, idesc, (kb > c.kb_begin || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);      // slot reusable once these MMAs have read it
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tmem_full_bar[ab]);       // accumulator complete
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue warps
+    const int ew = warp - 2;
+    const int q = warp & 3;                    // TMEM lane quarter this warp may read
+    const int half = ew >> 2;                  // column half of the tile
+    unsigned char* buf0 = epi_base + ew * 2 * kChunkBytes;   // output staging (D0)
+    unsigned char* buf1 = buf0 + kChunkBytes;                // D1 staging or R landing zone
+    const uint32_t buf0_u = smem_u32(buf0), buf1_u = smem_u32(buf1);
+    const uint32_t row_off = static_cast<uint32_t>(lane) * 128u;
+    const uint32_t sw = static_cast<uint32_t>(lane & 7);
+    uint64_t* rbar = &r_bar[ew];
+    uint32_t r_jobs = 0;                       // R chunks consumed so far (phase of rbar)
+
+    auto chunk_n = [&](const ItemCoord& c, int ch) { return c.n_blk * BN + half * (BN / 2) + ch * 64; };
+    // first valid (n < N) chunk at or after (w, ch); w >= items when none is left
+    auto next_valid = [&](int& w, int& ch) {
+      while (w < p.items) {
+        const ItemCoord c = decode(p, w);
+        for (; ch < kChunks; ++ch)
+          if (chunk_n(c, ch) < p.N) return;
+        ch = 0;
+        w += gridDim.x;
+      }
+    };
+    auto issue_r = [&](int w, int ch) {
+      const ItemCoord c = decode(p, w);
+      mbar_arrive_expect_tx(rbar, kChunkBytes);
+      tma_load_2d(buf1, &map_r, rbar, chunk_n(c, ch), c.m_blk * BM + q * 32);
+    };
+    if (kHasR && lane == 0) {
+      int w = blockIdx.x, ch = 0;
+      next_valid(w, ch);
+      if (w < p.items) issue_r(w, ch);
+    }
+
+    float2 cs_acc[kChunks];                    // column sums (EPI_GELU_GRAD): lane -> cols 2l, 2l+1
+#pragma unroll
+    for (int ch = 0; ch < kChunks; ++ch) cs_acc[ch] = make_float2(0.f, 0.f);
+    int cs_nblk = -1;
+    auto flush_colsum = [&]() {
+      if (EPI == EPI_GELU_GRAD && p.colsum != nullptr && cs_nblk >= 0) {
+#pragma unroll
+        for (int ch = 0; ch < kChunks; ++ch) {
+          const int n = cs_nblk * BN + half * (BN / 2) + ch * 64 + 2 * lane;
+          if (n < p.N) {
+            atomicAdd(p.colsum + n, cs_acc[ch].x);
+            atomicAdd(p.colsum + n + 1, cs_acc[ch].y);
+          }
+          cs_acc[ch] = make_float2(0.f, 0.f);
+        }
+      }
+    };
+
+    int i = 0;
+    for (int w = blockIdx.x; w < p.items; w += gridDim.x, ++i) {
+      const ItemCoord c = decode(p, w);
+      const int ab = i & 1;
+      const int row0 = c.m_blk * BM + q * 32;
+      if (EPI == EPI_GELU_GRAD && c.n_blk != cs_nblk) {
+        flush_colsum();
+        cs_nblk = c.n_blk;
+      }
+      mbar_wait(&tmem_full_bar[ab], (i >> 1) & 1, p.timeout_flag);
+      tc_fence_after();
+      const uint32_t tmem_acc = tmem_base + ab * BN + (static_cast<uint32_t>(q * 32) << 16) +
+                                half * (BN / 2);
+
+#pragma unroll
+      for (int ch = 0; ch < kChunks; ++ch) {
+        const int n_g = chunk_n(c, ch);
+        if (n_g >= p.N) continue;                        // warp-uniform
+
+        if (kF32Out) {
+          const int row = row0 + lane;
+#pragma unroll
+          for (int sub = 0; sub < 2; ++sub) {
+            uint32_t v[32];
+            tmem_ld_32x32(tmem_acc + ch * 64 + sub * 32, v);
+            tmem_ld_wait();
+            const int n = n_g + sub * 32;
+            if (row < p.M) {
+              float* d = p.D0f + static_cast<int64_t>(row) * p.ldd0 + n;
+#pragma unroll
+              for (int j = 0; j < 32; j += 4) {
+                if (n + j < p.N) {
+                  if (EPI == EPI_ATOMIC_F32)
+                    red_add_v4f(d + j, __uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+                  else
+                    st_global_v4f(d + j, __uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                  __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+                }
+              }
+            }
+          }
+          continue;
+        }
+
+        // staging buffers must have been drained by the previous chunk's TMA stores
+        if (lane == 0) tma_store_wait_read();
+        __syncwarp();
+        if (kHasR) {
+          mbar_wait(rbar, r_jobs & 1, p.timeout_flag);
+          ++r_jobs;
+        }
+
+#pragma unroll
+        for (int sub = 0; sub < 2; ++sub) {
+          uint32_t v[32];
+          tmem_ld_32x32(tmem_acc + ch * 64 + sub * 32, v);
+          uint32_t rr[16];
+          if (kHasR) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const uint4 u = ld_shared_v4(buf1_u + row_off + (((sub * 4 + k) ^ sw) << 4));
+              rr[4 * k] = u.x; rr[4 * k + 1] = u.y; rr[4 * k + 2] = u.z; rr[4 * k + 3] = u.w;
+            }
+          }
+          tmem_ld_wait();
+          const int n = n_g + sub * 32;
+
+          float2 f[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            f[j] = make_float2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+
+          if (EPI == EPI_BIAS_GELU || EPI == EPI_BIAS_RESIDUAL) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              if (n + j < p.N) {
+                const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + n + j));
+                f[j / 2].x += b.x; f[j / 2].y += b.y;
+                f[j / 2 + 1].x += b.z; f[j / 2 + 1].y += b.w;
+              }
+            }
+          }
+          if (EPI == EPI_BIAS_RESIDUAL) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float2 r2 = bf16x2_to_f32x2(rr[j]);
+              f[j].x += r2.x;
+              f[j].y += r2.y;
+            }
+          }
+          if (EPI == EPI_GELU_GRAD) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) f[j] = fmul2(f[j], gelu_grad2(bf16x2_to_f32x2(rr[j])));
+          }
+
+          uint32_t pk[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) pk[j] = f32x2_to_bf16x2(f[j].x, f[j].y);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            st_shared_v4(buf0_u + row_off + (((sub * 4 + k) ^ sw) << 4), pk[4 * k], pk[4 * k + 1],
+                         pk[4 * k + 2], pk[4 * k + 3]);
+
+          if (EPI == EPI_BIAS_GELU) {
+            // activation of the ROUNDED pre-activation (what backward will see), second output
+            uint32_t hk[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float2 h2 = gelu2(bf16x2_to_f32x2(pk[j]));
+              hk[j] = f32x2_to_bf16x2(h2.x, h2.y);
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              st_shared_v4(buf1_u + row_off + (((sub * 4 + k) ^ sw) << 4), hk[4 * k],
+                           hk[4 * k + 1], hk[4 * k + 2], hk[4 * k + 3]);
+          }
+        }
+
+        if (ch == kChunks - 1) {
+          // last TMEM read of this tile is done: hand the accumulator back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty_bar[ab]);
+        }
+
+        fence_proxy_async();          // make this lane's st.shared visible to the TMA engine
+        __syncwarp();                 // all lanes stored (and finished reading R from buf1)
+        if (lane == 0) {
+          if (kHasR) {                // R of this chunk is consumed: fetch the next one
+            int w2 = w, ch2 = ch + 1;
+            next_valid(w2, ch2);
+            if (w2 < p.items) issue_r(w2, ch2);
+          }
+          tma_store_2d(&map_d0, buf0, n_g, row0);
+          if (EPI == EPI_BIAS_GELU) tma_store_2d(&map_d1, buf1, n_g, row0);
+          tma_store_commit();
+        }
+        if (EPI == EPI_GELU_GRAD) {
+          // column sums of the ROUNDED dz (what the weight-gradient GEMM will consume): lane l
+          // owns columns 2l, 2l+1 of this chunk; 32 conflict-free word reads down the rows
+          // (rows past M hold acc = 0 -> contribute nothing)
+          const uint32_t cchunk = static_cast<uint32_t>(lane >> 2), cword = static_cast<uint32_t>(lane & 3);
+          float2 s = cs_acc[ch];
+#pragma unroll
+          for (int r = 0; r < 32; ++r) {
+            const float2 t2 = bf16x2_to_f32x2(
+                ld_shared_b32(buf0_u + r * 128 + ((cchunk ^ (r & 7)) << 4) + (cword << 2)));
+            s.x += t2.x;
+            s.y += t2.y;
+          }
+          cs_acc[ch] = s;
+        }
+      }
+
+      if (kF32Out || chunk_n(c, kChunks - 1) >= p.N) {
+        // the last chunk was skipped (ragged N) or the fp32 path ran: release the accumulator here
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty_bar[ab]);
+      }
+    }
+    flush_colsum();
+    if (lane == 0) tma_store_wait_all();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, L::kTmemCols);
+}
+
+template <int BN, int EPI>
+int launch2(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md0,
+            const CUtensorMap& md1, const CUtensorMap& mr, const Gemm2Params& p, int grid,
+            cudaStream_t stream) {
+  using L = Cfg<BN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gemm2_kernel<BN, EPI>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
+    if (e != cudaSuccess) {
+      set_last_error("gemm_bf16: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+      return CNX_ERR_LAUNCH;
+    }
+    attr_set = true;
+  }
+  gemm2_kernel<BN, EPI><<<grid, kThreads, L::kTotal, stream>>>(ma, mb, md0, md1, mr, p);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_last_error("gemm_bf16 launch: %s", cudaGetErrorString(e));
+    return CNX_ERR_LAUNCH;
+  }
+  return CNX_OK;
+}
+
+template <int BN>
+int dispatch(int epi, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md0,
+             const CUtensorMap& md1, const CUtensorMap& mr, const Gemm2Params& p, int grid,
+             cudaStream_t stream) {
+  switch (epi) {
+    case EPI_STORE_BF16:    return launch2<BN, EPI_STORE_BF16>(ma, mb, md0, md1, mr, p, grid, stream);
+    case EPI_BIAS_GELU:     return launch2<BN, EPI_BIAS_GELU>(ma, mb, md0, md1, mr, p, grid, stream);
+    case EPI_BIAS_RESIDUAL: return launch2<BN, EPI_BIAS_RESIDUAL>(ma, mb, md0, md1, mr, p, grid, stream);
+    case EPI_GELU_GRAD:     return launch2<BN, EPI_GELU_GRAD>(ma, mb, md0, md1, mr, p, grid, stream);
+    case EPI_STORE_F32:     return launch2<BN, EPI_STORE_F32>(ma, mb, md0, md1, mr, p, grid, stream);
+    case EPI_ATOMIC_F32:    return launch2<BN, EPI_ATOMIC_F32>(ma, mb, md0, md1, mr, p, grid, stream);
+    default: break;
+  }
+  set_last_error("gemm_bf16: unsupported epilogue %d", epi);
+  return CNX_ERR_BAD_ARG;
+}
+
+// rounds of the persistent loop for a given column-tile width
+double tile_cost(int M, int N, int BN, int nsm, int* grid_out) {
+  const int tiles_m = (M + BM - 1) / BM, tiles_n = (N + BN - 1) / BN;
+  const int items = tiles_m * tiles_n;
+  int grid = nsm;
+  if (tiles_n <= nsm) grid = (nsm / tiles_n) * tiles_n;   // a CTA keeps its column block
+  if (grid > items) grid = items;
+  const int rounds = (items + grid - 1) / grid;
+  *grid_out = grid;
+  // BN=128 tiles pull 1.5x the operand bytes per MAC through L2/shared memory: charge 15 %
+  return static_cast<double>(rounds) * BN * (BN == 128 ? 1.15 : 1.0);
+}
+
+}  // namespace
+
+int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
+  if (a.M <= 0 || a.N <= 0 || a.K <= 0 || (a.N % 8) != 0 || (a.lda % 8) != 0 || (a.ldb % 8) != 0) {
+    set_last_error("gemm_bf16: bad shape M=%d N=%d K=%d lda=%lld ldb=%lld (N, lda, ldb must be "
+                   "multiples of 8)", a.M, a.N, a.K, (long long)a.lda, (long long)a.ldb);
+    return CNX_ERR_BAD_SHAPE;
+  }
+  if (!a.a_mn_major && (a.K % 8) != 0) {
+    set_last_error("gemm_bf16: K=%d must be a multiple of 8 for K-major operands", a.K);
+    return CNX_ERR_BAD_SHAPE;
+  }
+  auto misaligned = [](const void* q) { return q && (reinterpret_cast<uintptr_t>(q) & 15) != 0; };
+  if (misaligned(a.A) || misaligned(a.B) || misaligned(a.D0) || misaligned(a.D1) ||
+      misaligned(a.bias) || misaligned(a.R) || misaligned(a.colsum)) {
+    set_last_error("gemm_bf16: every operand pointer must be 16-byte aligned");
+    return CNX_ERR_BAD_ARG;
+  }
+  if ((a.ldd0 % 8) != 0 || (a.D1 && (a.ldd1 % 8) != 0) || (a.R && (a.ldr % 8) != 0)) {
+    set_last_error("gemm_bf16: output/residual leading dimensions must be multiples of 8");
+    return CNX_ERR_BAD_SHAPE;
+  }
+  int epi = a.epilogue;
+  const bool need_bias = (epi == EPI_BIAS_GELU || epi == EPI_BIAS_RESIDUAL);
+  const bool need_r = (epi == EPI_BIAS_RESIDUAL || epi == EPI_GELU_GRAD);
+  if (epi < 0 || epi > EPI_STORE_F32 || (need_bias && !a.bias) || (need_r && !a.R) ||
+      (epi == EPI_BIAS_GELU && !a.D1)) {
+    set_last_error("gemm_bf16: unsupported epilogue %d or missing operand", a.epilogue);
+    return CNX_ERR_BAD_ARG;
+  }
+
+  const int nsm = sm_count();
+  const int nkb = (a.K + BK - 1) / BK;
+  Gemm2Params p{};
+  p.timeout_flag = timeout_flag_ptr();
+  if (p.timeout_flag == nullptr) {
+    set_last_error("could not map the timeout flag (cudaHostAlloc failed)");
+    return CNX_ERR_DRIVER;
+  }
+  p.M = a.M; p.N = a.N; p.K = a.K;
+  p.a_mn = a.a_mn_major ? 1 : 0;
+  p.b_mn = a.b_mn_major ? 1 : 0;
+  p.bias = a.bias;
+  p.colsum = a.colsum;
+  p.D0f = static_cast<float*>(a.D0);
+  p.ldd0 = a.ldd0;
+  p.nkb_total = nkb;
+
+  // column-tile width: fewer persistent rounds wins; 256 preferred (less operand traffic per MAC)
+  int BN = 256, grid = 0;
+  {
+    int g256, g128;
+    const double c256 = tile_cost(a.M, a.N, 256, nsm, &g256);
+    const double c128 = tile_cost(a.M, a.N, 128, nsm, &g128);
+    if (a.N <= 128 || c128 < c256) { BN = 128; grid = g128; } else { BN = 256; grid = g256; }
+  }
+  p.tiles_m = (a.M + BM - 1) / BM;
+  p.tiles_n = (a.N + BN - 1) / BN;
+  int splits = 1;
+  if (epi == EPI_STORE_F32) {
+    // split-K so that the weight-gradient GEMMs (small M x N, K = tokens) fill the machine; the
+    // caller zero-fills D0 (fp32 vector reductions accumulate into it)
+    const int tiles = p.tiles_m * p.tiles_n;
+    splits = (nsm + tiles - 1) / tiles;
+    if (splits > nkb / 4) splits = nkb / 4;     // keep >= 4 k-blocks per item
+    if (splits < 1) splits = 1;
+  }
+  int kbps = (nkb + splits - 1) / splits;
+  splits = (nkb + kbps - 1) / kbps;             // no empty split
+  if (splits > 1) epi = EPI_ATOMIC_F32;
+  p.splits = splits;
+  p.kb_per_split = kbps;
+  p.items = p.tiles_m * p.tiles_n * splits;
+  if (splits > 1) grid = p.items < nsm ? p.items : nsm;
+
+  CUtensorMap ma, mb, md0, md1, mr;
+  int rc;
+  {
+    // K-major: stored [rows][K] -> dims (K, rows), box (64, tile rows).
+    // MN-major: stored [K][rows] -> dims (rows, K), box (64 rows, 64 k) per 64-wide atom.
+    const uint64_t dims_k[2] = {(uint64_t)a.K, (uint64_t)a.M};
+    const uint64_t dims_mn[2] = {(uint64_t)a.M, (uint64_t)a.K};
+    const uint64_t st[1] = {(uint64_t)a.lda * 2};
+    const uint32_t box_k[2] = {BK, BM};
+    const uint32_t box_mn[2] = {64, BK};
+    rc = make_tensor_map(&ma, a.A, 2, 2, a.a_mn_major ? dims_mn : dims_k, st,
+                         a.a_mn_major ? box_mn : box_k, 3);
+    if (rc != CNX_OK) return rc;
+  }
+  {
+    const uint64_t dims_k[2] = {(uint64_t)a.K, (uint64_t)a.N};
+    const uint64_t dims_mn[2] = {(uint64_t)a.N, (uint64_t)a.K};
+    const uint64_t st[1] = {(uint64_t)a.ldb * 2};
+    const uint32_t box_k[2] = {BK, (uint32_t)BN};
+    const uint32_t box_mn[2] = {64, BK};
+    rc = make_tensor_map(&mb, a.B, 2, 2, a.b_mn_major ? dims_mn : dims_k, st,
+                         a.b_mn_major ? box_mn : box_k, 3);
+    if (rc != CNX_OK) return rc;
+  }
+  // epilogue maps: [M][N] bf16 row-major, box 64 cols x 32 rows, 128B swizzle (staging layout)
+  auto mn_map = [&](CUtensorMap* m, const void* base, int64_t ld) {
+    const uint64_t dims[2] = {(uint64_t)a.N, (uint64_t)a.M};
+    const uint64_t st[1] = {(uint64_t)ld * 2};
+    const uint32_t box[2] = {64, 32};
+    return make_tensor_map(m, base, 2, 2, dims, st, box, 3);
+  };
+  const bool f32_out = (epi == EPI_STORE_F32 || epi == EPI_ATOMIC_F32);
+  md0 = ma; md1 = ma; mr = ma;    // placeholders for unused maps (never dereferenced)
+  if (!f32_out) {
+    rc = mn_map(&md0, a.D0, a.ldd0);
+    if (rc != CNX_OK) return rc;
+  }
+  if (epi == EPI_BIAS_GELU) {
+    rc = mn_map(&md1, a.D1, a.ldd1);
+    if (rc != CNX_OK) return rc;
+  }
+  if (need_r) {
+    rc = mn_map(&mr, a.R, a.ldr);
+    if (rc != CNX_OK) return rc;
+  }
+
+  return BN == 256 ? dispatch<256>(epi, ma, mb, md0, md1, mr, p, grid, stream)
+                   : dispatch<128>(epi, ma, mb, md0, md1, mr, p, grid, stream);
+}
+
+}  // namespace cnx

@@ -359,7 +359,7 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, in
 
 }  // namespace
 
-int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
+int gemm_bf16_v1(const GemmArgs& a, cudaStream_t stream) {
   if (a.M <= 0 || a.N <= 0 || a.K <= 0 || (a.N % 8) != 0 || (a.lda % 8) != 0 || (a.ldb % 8) != 0) {
     set_last_error("gemm_bf16: bad shape M=%d N=%d K=%d lda=%lld ldb=%lld (N, lda, ldb must be "
                    "multiples of 8)", a.M, a.N, a.K, (long long)a.lda, (long long)a.ldb);
