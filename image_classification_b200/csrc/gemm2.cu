@@ -607,11 +607,19 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   int splits = 1;
   if (epi == EPI_STORE_F32) {
     // split-K so that the weight-gradient GEMMs (small M x N, K = tokens) fill the machine; the
-    // caller zero-fills D0 (fp32 vector reductions accumulate into it)
+    // caller zero-fills D0 (fp32 vector reductions accumulate into it).  Pick the split count
+    // that minimises (persistent rounds) x (k-blocks per item), keeping >= 4 k-blocks per item.
     const int tiles = p.tiles_m * p.tiles_n;
-    splits = (nsm + tiles - 1) / tiles;
-    if (splits > nkb / 4) splits = nkb / 4;     // keep >= 4 k-blocks per item
-    if (splits < 1) splits = 1;
+    int max_splits = nkb / 4;
+    if (max_splits > 2 * nsm) max_splits = 2 * nsm;
+    long best = -1;
+    for (int s = 1; s <= max_splits; ++s) {
+      const int kb = (nkb + s - 1) / s;
+      const int eff = (nkb + kb - 1) / kb;
+      const long rounds = (static_cast<long>(tiles) * eff + nsm - 1) / nsm;
+      const long cost = rounds * (kb + 6);     // + ~6 k-blocks of prologue/epilogue per item
+      if (best < 0 || cost < best) { best = cost; splits = eff; }
+    }
   }
   int kbps = (nkb + splits - 1) / splits;
   splits = (nkb + kbps - 1) / kbps;             // no empty split
