@@ -13,6 +13,7 @@ import torch
 import torch.nn.functional as F
 from torch import nn
 
+from . import ops
 from .block import ConvNeXtBlockB200
 
 CONVNEXT_CFGS = {
@@ -23,10 +24,39 @@ CONVNEXT_CFGS = {
 }
 
 
+class _LayerNorm2dFn(torch.autograd.Function):
+    """x: [B,C,H,W] bf16 channels_last (physically NHWC rows) -> same layout, libcnx_b200 kernels."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, eps):
+        B, C, H, W = x.shape
+        x2d = x.permute(0, 2, 3, 1).reshape(B * H * W, C)
+        y, mean, rstd = ops.layernorm_fwd(x2d, weight.detach(), bias.detach(), eps)
+        ctx.save_for_backward(x2d, weight, mean, rstd)
+        return y.view(B, H, W, C).permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, g):
+        x2d, weight, mean, rstd = ctx.saved_tensors
+        B, C, H, W = g.shape
+        g = g.permute(0, 2, 3, 1)
+        if g.dtype != torch.bfloat16 or not g.is_contiguous():
+            g = g.to(torch.bfloat16).contiguous()
+        dx, dw, db = ops.layernorm_bwd(g.view(B * H * W, C), x2d, weight.detach(), mean, rstd)
+        return dx.view(B, H, W, C).permute(0, 3, 1, 2), dw, db, None
+
+
 class LayerNorm2d(nn.LayerNorm):
-    """LayerNorm over the channel dim of an NCHW tensor (timm's LayerNorm2d)."""
+    """LayerNorm over the channel dim of an NCHW tensor (timm's LayerNorm2d).  bf16 channels_last
+    CUDA activations (the stem / downsample stream of the B200 model) go through
+    cnx_layernorm_fwd/bwd; anything else (the oracle on CPU, the 1x1 head) takes the PyTorch op."""
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        C = x.shape[1]
+        if (x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 4 and C % 8 == 0 and C <= 1024
+                and x.shape[2] * x.shape[3] > 1 and x.permute(0, 2, 3, 1).is_contiguous()
+                and self.weight.dtype == torch.float32):
+            return _LayerNorm2dFn.apply(x, self.weight, self.bias, self.eps)
         y = x.permute(0, 2, 3, 1)
         y = F.layer_norm(y, self.normalized_shape, self.weight, self.bias, self.eps)
         # autocast runs layer_norm in fp32; hand the stream back in the dtype it came in so the

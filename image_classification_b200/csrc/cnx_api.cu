@@ -92,6 +92,23 @@ int cnx_dwconv_ln_bwd(const void* dxhat, const void* xhat, const float* rstd, co
                        workspace, workspace_bytes, as_stream(stream));
 }
 
+int cnx_layernorm_fwd(const void* x, const float* weight, const float* bias, void* y, float* mean,
+                      float* rstd, int64_t M, int C, float eps, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(weight); CNX_REQUIRE_PTR(bias); CNX_REQUIRE_PTR(y);
+  CNX_REQUIRE_PTR(mean); CNX_REQUIRE_PTR(rstd);
+  return ln_affine_fwd(x, weight, bias, y, mean, rstd, M, C, eps, as_stream(stream));
+}
+
+int cnx_layernorm_bwd(const void* dy, const void* x, const float* weight, const float* mean,
+                      const float* rstd, void* dx, float* dweight, float* dbias, int64_t M, int C,
+                      void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(dy); CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(weight); CNX_REQUIRE_PTR(mean);
+  CNX_REQUIRE_PTR(rstd); CNX_REQUIRE_PTR(dx); CNX_REQUIRE_PTR(dweight); CNX_REQUIRE_PTR(dbias);
+  return ln_affine_bwd(dy, x, weight, mean, rstd, dx, dweight, dbias, M, C, as_stream(stream));
+}
+
 int cnx_gemm_bf16(const void* A, int64_t lda, int a_mn_major, const void* B, int64_t ldb,
                   int b_mn_major, int M, int N, int K, int epilogue, void* D0, int64_t ldd0,
                   void* D1, int64_t ldd1, const float* bias, const void* R, int64_t ldr,

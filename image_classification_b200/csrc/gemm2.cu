@@ -600,7 +600,9 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
     int g256, g128;
     const double c256 = tile_cost(a.M, a.N, 256, nsm, &g256);
     const double c128 = tile_cost(a.M, a.N, 128, nsm, &g128);
-    if (a.N <= 128 || c128 < c256) { BN = 128; grid = g128; } else { BN = 256; grid = g256; }
+    // split-K weight gradients are one long main loop per item: the wide tile always wins there
+    const bool wide = (epi == EPI_STORE_F32) ? (a.N > 128) : !(a.N <= 128 || c128 < c256);
+    if (wide) { BN = 256; grid = g256; } else { BN = 128; grid = g128; }
   }
   p.tiles_m = (a.M + BM - 1) / BM;
   p.tiles_n = (a.N + BN - 1) / BN;

@@ -151,6 +151,168 @@ ln_rows_bwd_kernel(const __nv_bfloat16* __restrict__ dxhat, const __nv_bfloat16*
   }
 }
 
+
+// ---- LayerNorm WITH affine over [M, C] bf16 rows (timm LayerNorm2d of the stem and of the stage
+// `downsample` modules): y = (x - mean) * rstd * w + b; mean / rstd saved.
+template <int LPR, int NV>
+__global__ void __launch_bounds__(kRowThreads)
+ln_affine_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
+                     const float* __restrict__ b, __nv_bfloat16* __restrict__ y,
+                     float* __restrict__ mean_out, float* __restrict__ rstd_out, int64_t M, int C,
+                     float eps) {
+  const int lane_in_row = threadIdx.x % LPR;
+  const int64_t row = static_cast<int64_t>(blockIdx.x) * (kRowThreads / LPR) + threadIdx.x / LPR;
+  const bool row_ok = row < M;
+  const int nvec = C >> 3;
+  const int64_t off = (row_ok ? row : 0) * C;
+  float f[NV][8];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int v = lane_in_row + i * LPR;
+    if (row_ok && v < nvec) {
+      unpack8(ld_v4(x + off + v * 8), f[i]);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) s += f[i][k];
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f[i][k] = 0.f;
+    }
+  }
+  const float inv_c = 1.0f / static_cast<float>(C);
+  const float mean = group_sum<LPR>(s) * inv_c;
+  float m2 = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int v = lane_in_row + i * LPR;
+    if (v < nvec) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float d = f[i][k] - mean;
+        m2 = fmaf(d, d, m2);
+      }
+    }
+  }
+  const float rstd = rsqrtf(group_sum<LPR>(m2) * inv_c + eps);
+  if (!row_ok) return;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int v = lane_in_row + i * LPR;
+    if (v < nvec) {
+      const float4 w0 = __ldg(reinterpret_cast<const float4*>(w + v * 8));
+      const float4 w1 = __ldg(reinterpret_cast<const float4*>(w + v * 8 + 4));
+      const float4 b0 = __ldg(reinterpret_cast<const float4*>(b + v * 8));
+      const float4 b1 = __ldg(reinterpret_cast<const float4*>(b + v * 8 + 4));
+      const float wv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+      const float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+      float o[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o[k] = fmaf((f[i][k] - mean) * rstd, wv[k], bv[k]);
+      st_v4(y + off + v * 8, pack8(o));
+    }
+  }
+  if (lane_in_row == 0) {
+    mean_out[row] = mean;
+    rstd_out[row] = rstd;
+  }
+}
+
+// backward: dx = rstd * (g*w - mean_c(g*w) - xhat * mean_c(g*w*xhat)), dw += sum_rows g*xhat,
+// db += sum_rows g.  A CTA walks `rows_per_cta` rows keeping the per-channel sums in registers,
+// then reduces them through shared-memory atomics and issues one global atomic per channel.
+template <int LPR, int NV>
+__global__ void __launch_bounds__(kRowThreads)
+ln_affine_bwd_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ x,
+                     const float* __restrict__ w, const float* __restrict__ mean_in,
+                     const float* __restrict__ rstd_in, __nv_bfloat16* __restrict__ dx,
+                     float* __restrict__ dw, float* __restrict__ db, int64_t M, int C,
+                     int rows_per_cta) {
+  __shared__ float s_dw[1024];
+  __shared__ float s_db[1024];
+  for (int i = threadIdx.x; i < C; i += kRowThreads) {
+    s_dw[i] = 0.f;
+    s_db[i] = 0.f;
+  }
+  __syncthreads();
+  const int lane_in_row = threadIdx.x % LPR;
+  const int slot = threadIdx.x / LPR;
+  constexpr int kSlots = kRowThreads / LPR;
+  const int nvec = C >> 3;
+  const float inv_c = 1.0f / static_cast<float>(C);
+  float wv[NV][8], dwa[NV][8], dba[NV][8];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int v = lane_in_row + i * LPR;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      wv[i][k] = (v < nvec) ? __ldg(w + v * 8 + k) : 0.f;
+      dwa[i][k] = 0.f;
+      dba[i][k] = 0.f;
+    }
+  }
+  const int64_t row_begin = static_cast<int64_t>(blockIdx.x) * rows_per_cta;
+  for (int r = slot; r < rows_per_cta; r += kSlots) {
+    const int64_t row = row_begin + r;
+    const bool row_ok = row < M;            // uniform across the lanes sharing the row
+    const int64_t off = (row_ok ? row : 0) * C;
+    const float mu = row_ok ? mean_in[row] : 0.f;
+    const float rs = row_ok ? rstd_in[row] : 0.f;
+    float gw[NV][8], xh[NV][8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int v = lane_in_row + i * LPR;
+      if (row_ok && v < nvec) {
+        float gg[8], xx[8];
+        unpack8(ld_v4(g + off + v * 8), gg);
+        unpack8(ld_v4(x + off + v * 8), xx);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          xh[i][k] = (xx[k] - mu) * rs;
+          dwa[i][k] = fmaf(gg[k], xh[i][k], dwa[i][k]);
+          dba[i][k] += gg[k];
+          gw[i][k] = gg[k] * wv[i][k];
+          s1 += gw[i][k];
+          s2 = fmaf(gw[i][k], xh[i][k], s2);
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) gw[i][k] = xh[i][k] = 0.f;
+      }
+    }
+    const float m1 = group_sum<LPR>(s1) * inv_c;
+    const float m2 = group_sum<LPR>(s2) * inv_c;
+    if (row_ok) {
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int v = lane_in_row + i * LPR;
+        if (v < nvec) {
+          float o[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) o[k] = rs * (gw[i][k] - m1 - xh[i][k] * m2);
+          st_v4(dx + off + v * 8, pack8(o));
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int v = lane_in_row + i * LPR;
+    if (v < nvec) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        atomicAdd(&s_dw[v * 8 + k], dwa[i][k]);
+        atomicAdd(&s_db[v * 8 + k], dba[i][k]);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += kRowThreads) {
+    atomicAdd(dw + i, s_dw[i]);
+    atomicAdd(db + i, s_db[i]);
+  }
+}
+
 struct RowCfg { int lpr, nv; };
 bool pick_cfg(int C, RowCfg* cfg) {
   const int nvec = C / 8;
@@ -212,6 +374,44 @@ int ln_rows_bwd(const void* dxhat, const void* xhat, const float* rstd, void* dc
                    static_cast<const __nv_bfloat16*>(xhat), rstd,
                    static_cast<__nv_bfloat16*>(dconv), M, C);
   return launch_status("ln_rows_bwd");
+}
+
+int ln_affine_fwd(const void* x, const float* w, const float* b, void* y, float* mean, float* rstd,
+                  int64_t M, int C, float eps, cudaStream_t stream) {
+  RowCfg cfg;
+  int rc = check_rows("ln_affine_fwd", M, C, &cfg);
+  if (rc != CNX_OK) return rc;
+  CNX_ROW_DISPATCH(ln_affine_fwd_kernel, static_cast<const __nv_bfloat16*>(x), w, b,
+                   static_cast<__nv_bfloat16*>(y), mean, rstd, M, C, eps);
+  return launch_status("ln_affine_fwd");
+}
+
+int ln_affine_bwd(const void* g, const void* x, const float* w, const float* mean,
+                  const float* rstd, void* dx, float* dw, float* db, int64_t M, int C,
+                  cudaStream_t stream) {
+  RowCfg cfg;
+  int rc = check_rows("ln_affine_bwd", M, C, &cfg);
+  if (rc != CNX_OK) return rc;
+  cudaMemsetAsync(dw, 0, sizeof(float) * C, stream);
+  cudaMemsetAsync(db, 0, sizeof(float) * C, stream);
+  // ~4 CTAs per SM, each walking a contiguous run of rows (multiple of the rows in flight)
+  const int slots = kRowThreads / cfg.lpr;
+  int64_t rpc = (M + 4 * sm_count() - 1) / (4 * sm_count());
+  rpc = (rpc + slots - 1) / slots * slots;
+  if (rpc < slots) rpc = slots;
+  const int rows_per_cta = static_cast<int>(rpc);
+  const unsigned grid = static_cast<unsigned>((M + rpc - 1) / rpc);
+#define CNX_LNB(LPR_, NV_)                                                                      \
+  ln_affine_bwd_kernel<LPR_, NV_><<<grid, kRowThreads, 0, stream>>>(                            \
+      static_cast<const __nv_bfloat16*>(g), static_cast<const __nv_bfloat16*>(x), w, mean, rstd, \
+      static_cast<__nv_bfloat16*>(dx), dw, db, M, C, rows_per_cta)
+  if (cfg.lpr == 8) CNX_LNB(8, 1);
+  else if (cfg.lpr == 16) CNX_LNB(16, 1);
+  else if (cfg.nv == 1) CNX_LNB(32, 1);
+  else if (cfg.nv == 2) CNX_LNB(32, 2);
+  else CNX_LNB(32, 4);
+#undef CNX_LNB
+  return launch_status("ln_affine_bwd");
 }
 
 }  // namespace cnx

@@ -118,6 +118,34 @@ def dwconv_ln_bwd(dxhat, xhat, rstd, x_nhwc, dy, wt_dw):
     return dx, dwt, dbias, dycs
 
 
+# ------------------------------------------------------------------ LayerNorm2d (stem / downsample)
+def layernorm_fwd(x2d, weight, bias, eps: float = LN_EPS):
+    """x [M,C] bf16 -> (y [M,C] bf16, mean [M] f32, rstd [M] f32); affine LayerNorm over C."""
+    _chk(x2d, torch.bfloat16, "x")
+    _chk(weight, torch.float32, "weight")
+    _chk(bias, torch.float32, "bias")
+    M, C = x2d.shape
+    y = torch.empty_like(x2d)
+    mean = torch.empty(M, device=x2d.device, dtype=torch.float32)
+    rstd = torch.empty_like(mean)
+    _lib.call("cnx_layernorm_fwd", _p(x2d), _p(weight), _p(bias), _p(y), _p(mean), _p(rstd), M, C,
+              eps, _stream(x2d))
+    return y, mean, rstd
+
+
+def layernorm_bwd(dy2d, x2d, weight, mean, rstd):
+    """-> (dx [M,C] bf16, dweight [C] f32, dbias [C] f32)."""
+    _chk(dy2d, torch.bfloat16, "dy")
+    _chk(x2d, torch.bfloat16, "x")
+    M, C = x2d.shape
+    dx = torch.empty_like(x2d)
+    dw = torch.empty(C, device=x2d.device, dtype=torch.float32)
+    db = torch.empty_like(dw)
+    _lib.call("cnx_layernorm_bwd", _p(dy2d), _p(x2d), _p(_chk(weight, torch.float32, "weight")),
+              _p(mean), _p(rstd), _p(dx), _p(dw), _p(db), M, C, _stream(x2d))
+    return dx, dw, db
+
+
 # ------------------------------------------------------------------ MLP GEMMs
 EPI_STORE_BF16, EPI_BIAS_GELU, EPI_BIAS_RESIDUAL, EPI_GELU_GRAD, EPI_STORE_F32 = range(5)
 

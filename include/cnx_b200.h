@@ -107,6 +107,17 @@ int cnx_dwconv_ln_bwd(const void* dxhat, const void* xhat, const float* rstd, co
                       float* dy_colsum, int B, int H, int W, int C, void* workspace,
                       size_t workspace_bytes, void* stream);
 
+/* timm LayerNorm2d (channels-last LayerNorm WITH affine) of the stem and of every stage's
+ * `downsample` (un-vendored timm; reached from /root/reference/train_advanced_v4.py:131,134-135;
+ * SURVEY.md §8 f-1): x, y [M, C] bf16 rows (NHWC), weight / bias [C] fp32, mean / rstd [M] fp32
+ * saved for the backward.  C multiple of 8, <= 1024. */
+int cnx_layernorm_fwd(const void* x, const float* weight, const float* bias, void* y, float* mean,
+                      float* rstd, int64_t M, int C, float eps, void* stream);
+/* Its backward: dx [M, C] bf16; dweight, dbias [C] fp32 are overwritten. */
+int cnx_layernorm_bwd(const void* dy, const void* x, const float* weight, const float* mean,
+                      const float* rstd, void* dx, float* dweight, float* dbias, int64_t M, int C,
+                      void* stream);
+
 /* Generic tensor-core GEMM: D[M,N] = epilogue(A[M,K] * B[N,K]^T), bf16 in, fp32 accumulate.
  * a_mn_major / b_mn_major != 0: the operand is stored [K, rows] (row-major) instead. */
 int cnx_gemm_bf16(const void* A, int64_t lda, int a_mn_major, const void* B, int64_t ldb,

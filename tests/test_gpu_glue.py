@@ -202,3 +202,56 @@ def test_unfold_block_grads_is_adjoint_of_prep(cnx_lib, C):
         ref = p[key].grad.float()
         err = (got - ref).abs().max() / ref.abs().max()
         assert err < 1e-4, (key, float(err))
+
+
+# ---------------------------------------------------------------- LayerNorm2d (stem / downsample)
+@pytest.mark.parametrize("shape", [(301, 64), (1000, 128), (77, 96), (513, 256), (260, 512),
+                                   (130, 1024), (5, 8)])
+def test_layernorm_affine_fwd_bwd_vs_torch_fp64(cnx_lib, shape):
+    """cnx_layernorm_fwd/bwd vs F.layer_norm in fp64 on the same bf16-representable inputs."""
+    import torch.nn.functional as F
+    from image_classification_b200 import ops
+    M, C = shape
+    dev = torch.device("cuda:0")
+    torch.manual_seed(M + C)
+    x = (torch.randn(M, C, device=dev) * 1.7 + 0.4).bfloat16()
+    g = torch.randn(M, C, device=dev).bfloat16()
+    w = (1 + 0.3 * torch.randn(C, device=dev))
+    b = 0.2 * torch.randn(C, device=dev)
+    xr = x.double().requires_grad_()
+    wr, br = w.double().requires_grad_(), b.double().requires_grad_()
+    yr = F.layer_norm(xr, (C,), wr, br, 1e-6)
+    yr.backward(g.double())
+    y, mean, rstd = ops.layernorm_fwd(x, w, b, 1e-6)
+    dx, dw, db = ops.layernorm_bwd(g, x, w, mean, rstd)
+    rel = lambda a, r: float((a.double() - r).abs().max() / r.abs().max().clamp_min(1e-30))
+    assert rel(mean, x.double().mean(1)) < 1e-4 or (mean.double() - x.double().mean(1)).abs().max() < 1e-5
+    assert rel(rstd, torch.rsqrt(x.double().var(1, unbiased=False) + 1e-6)) < 1e-4
+    assert rel(y, yr.detach()) < 2e-2
+    assert (y.double() - yr.detach()).abs().max() < 2.0 ** -8 * yr.abs().max() + 1e-3
+    assert rel(dx, xr.grad) < 2e-2
+    assert rel(dw, wr.grad) < 1e-3 and rel(db, br.grad) < 1e-3
+
+
+def test_layernorm2d_module_uses_library_and_matches_torch(cnx_lib):
+    from image_classification_b200 import _lib
+    from image_classification_b200.convnext import LayerNorm2d
+    dev = torch.device("cuda:0")
+    torch.manual_seed(3)
+    ln = LayerNorm2d(128, eps=1e-6).to(dev)
+    with torch.no_grad():
+        ln.weight.normal_(1, 0.2)
+        ln.bias.normal_(0, 0.2)
+    x = torch.randn(2, 128, 9, 7, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    xa = x.clone().requires_grad_()
+    n0 = _lib.launch_count
+    y = ln(xa)
+    y.float().square().sum().backward()
+    assert _lib.launch_count - n0 == 2                       # fwd + bwd kernels of libcnx_b200
+    xb = x.double().requires_grad_()
+    yb = torch.nn.functional.layer_norm(xb.permute(0, 2, 3, 1), (128,), ln.weight.double(),
+                                        ln.bias.double(), 1e-6).permute(0, 3, 1, 2)
+    yb.square().sum().backward()
+    rel = lambda a, r: float((a.double() - r).abs().max() / r.abs().max())
+    assert y.dtype == torch.bfloat16 and rel(y, yb.detach()) < 2e-2
+    assert rel(xa.grad, xb.grad) < 2e-2
