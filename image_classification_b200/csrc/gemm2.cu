@@ -29,6 +29,7 @@
 // the weight-gradient GEMMs need (K = tokens), so no activation transpose ever touches HBM.
 #include "cnx_common.cuh"
 #include "cnx_kernels.h"
+#include <stdlib.h>
 
 namespace cnx {
 
@@ -41,11 +42,17 @@ constexpr int kEpiWarps = 8;
 constexpr int EPI_ATOMIC_F32 = 5;      // internal: split-K fp32 reduction
 constexpr uint32_t kChunkBytes = 32 * 128;   // staging chunk: 32 rows x 64 bf16, 128B swizzle
 
-template <int BN>
+// PAIR: two CTAs (a cluster of 2 on one TPC) share a 256 x BN tile through cta_group::2 MMAs; each
+// stages its own 128 rows of A and HALF of B, which halves the B bytes written into and read out
+// of every SM's shared memory (ncu on the single-CTA kernel: tensor pipe capped near 63 % because
+// TMA writes + MMA operand reads exceed the 128 B/clk shared-memory port).
+template <int BN, bool PAIR>
 struct Cfg {
-  static constexpr int kStages = (BN == 256) ? 3 : 4;
+  static constexpr int kStages = PAIR ? 4 : ((BN == 256) ? 3 : 4);
+  static constexpr int kTileM = PAIR ? 2 * BM : BM;
+  static constexpr int kBRows = PAIR ? BN / 2 : BN;      // rows of B staged by one CTA
   static constexpr uint32_t kABytes = BM * BK * 2;
-  static constexpr uint32_t kBBytes = BN * BK * 2;
+  static constexpr uint32_t kBBytes = kBRows * BK * 2;
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
   static constexpr uint32_t kEpiBytes = kEpiWarps * 2 * kChunkBytes;     // 64 KB
   static constexpr uint32_t kBarBytes = 256;
@@ -150,13 +157,14 @@ __device__ __forceinline__ ItemCoord decode(const Gemm2Params& p, int w) {
   return c;
 }
 
-template <int BN, int EPI>
+template <int BN, int EPI, bool PAIR>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
              const __grid_constant__ CUtensorMap map_d0, const __grid_constant__ CUtensorMap map_d1,
              const __grid_constant__ CUtensorMap map_r, const Gemm2Params p) {
-  using L = Cfg<BN>;
+  using L = Cfg<BN, PAIR>;
   constexpr int kStages = L::kStages;
+  constexpr int kTileM = L::kTileM;
   constexpr bool kHasR = (EPI == EPI_BIAS_RESIDUAL || EPI == EPI_GELU_GRAD);
   constexpr bool kF32Out = (EPI == EPI_STORE_F32 || EPI == EPI_ATOMIC_F32);
   constexpr int kChunks = BN / 2 / 64;         // 64-column chunks per epilogue warp per tile
@@ -174,6 +182,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(r_bar + kEpiWarps);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = PAIR ? cluster_ctarank() : 0u;       // 0 = leader of the CTA pair
+  const int w_first = PAIR ? (blockIdx.x >> 1) : blockIdx.x; // both CTAs of a pair walk the same items
+  const int w_stride = PAIR ? (gridDim.x >> 1) : gridDim.x;
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&map_a);
@@ -189,15 +200,19 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
 #pragma unroll
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tmem_full_bar[b], 1);
-      mbar_init(&tmem_empty_bar[b], kEpiWarps);
+      mbar_init(&tmem_empty_bar[b], PAIR ? 2 * kEpiWarps : kEpiWarps);
     }
 #pragma unroll
     for (int w = 0; w < kEpiWarps; ++w) mbar_init(&r_bar[w], 1);
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, L::kTmemCols);
+  if (warp == 1) {
+    if (PAIR) tmem_alloc_pair(tmem_slot, L::kTmemCols);
+    else tmem_alloc(tmem_slot, L::kTmemCols);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all();    // the peer's barriers must exist before anything signals them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -206,41 +221,62 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
       // ------------------------------------------------------------ TMA producer
       int stage = 0;
       uint32_t phase = 0;
-      for (int w = blockIdx.x; w < p.items; w += gridDim.x) {
+      for (int w = w_first; w < p.items; w += w_stride) {
         const ItemCoord c = decode(p, w);
-        const int m0 = c.m_blk * BM, n0 = c.n_blk * BN;
+        const int m0 = c.m_blk * kTileM + static_cast<int>(rank) * BM;
+        const int n0 = c.n_blk * BN + static_cast<int>(rank) * (BN - L::kBRows);   // pair: own half of B
         for (int kb = c.kb_begin; kb < c.kb_end; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1, p.timeout_flag);
           unsigned char* sa = smem + stage * L::kStageBytes;
           unsigned char* sb = sa + L::kABytes;
-          mbar_arrive_expect_tx(&full_bar[stage], L::kStageBytes);
           const int k0 = kb * BK;
-          if (!p.a_mn) {
-            tma_load_2d(sa, &map_a, &full_bar[stage], k0, m0);            // box [128 rows][64 k]
-          } else {
+          if (PAIR) {
+            // both CTAs' bytes are credited to the LEADER's full barrier, which it arms for both
+            if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * L::kStageBytes);
+            const uint32_t fb = dsmem_map(smem_u32(&full_bar[stage]), 0);
+            if (!p.a_mn) {
+              tma_load_2d_pair(sa, &map_a, fb, k0, m0);
+            } else {
 #pragma unroll
-            for (int a = 0; a < BM / 64; ++a)                             // box [64 k][64 rows]
-              tma_load_2d(sa + a * (BK * 128), &map_a, &full_bar[stage], m0 + a * 64, k0);
-          }
-          if (!p.b_mn) {
-            tma_load_2d(sb, &map_b, &full_bar[stage], k0, n0);            // box [BN rows][64 k]
-          } else {
+              for (int a = 0; a < BM / 64; ++a)
+                tma_load_2d_pair(sa + a * (BK * 128), &map_a, fb, m0 + a * 64, k0);
+            }
+            if (!p.b_mn) {
+              tma_load_2d_pair(sb, &map_b, fb, k0, n0);                   // box [BN/2 rows][64 k]
+            } else {
 #pragma unroll
-            for (int a = 0; a < BN / 64; ++a)
-              tma_load_2d(sb + a * (BK * 128), &map_b, &full_bar[stage], n0 + a * 64, k0);
+              for (int a = 0; a < L::kBRows / 64; ++a)
+                tma_load_2d_pair(sb + a * (BK * 128), &map_b, fb, n0 + a * 64, k0);
+            }
+          } else {
+            mbar_arrive_expect_tx(&full_bar[stage], L::kStageBytes);
+            if (!p.a_mn) {
+              tma_load_2d(sa, &map_a, &full_bar[stage], k0, m0);          // box [128 rows][64 k]
+            } else {
+#pragma unroll
+              for (int a = 0; a < BM / 64; ++a)                           // box [64 k][64 rows]
+                tma_load_2d(sa + a * (BK * 128), &map_a, &full_bar[stage], m0 + a * 64, k0);
+            }
+            if (!p.b_mn) {
+              tma_load_2d(sb, &map_b, &full_bar[stage], k0, n0);          // box [BN rows][64 k]
+            } else {
+#pragma unroll
+              for (int a = 0; a < BN / 64; ++a)
+                tma_load_2d(sb + a * (BK * 128), &map_b, &full_bar[stage], n0 + a * 64, k0);
+            }
           }
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (lane == 0 && rank == 0) {
       // -------------------------------------------------------------- MMA issuer
-      const uint32_t idesc = umma_idesc_bf16(BM, BN, p.a_mn, p.b_mn);
+      const uint32_t idesc = umma_idesc_bf16(kTileM, BN, p.a_mn, p.b_mn);
       int stage = 0;
       uint32_t phase = 0;
       int i = 0;
-      for (int w = blockIdx.x; w < p.items; w += gridDim.x, ++i) {
+      for (int w = w_first; w < p.items; w += w_stride, ++i) {
         const ItemCoord c = decode(p, w);
         const int ab = i & 1;
         mbar_wait(&tmem_empty_bar[ab], ((i >> 1) & 1) ^ 1, p.timeout_flag);
@@ -260,12 +296,16 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
                                        : umma_desc_sw128(sa + k * 32, 16, 1024);
             const uint64_t db = p.b_mn ? umma_desc_sw128(sb + k * 2048, BK * 128, 1024)
                                        : umma_desc_sw128(sb + k * 32, 16, 1024);
-            umma_bf16(tmem_d, da, db, idesc, (kb > c.kb_begin || k > 0) ? 1u : 0u);
+            if (PAIR) umma_bf16_pair(tmem_d, da, db, idesc, (kb > c.kb_begin || k > 0) ? 1u : 0u);
+            else umma_bf16(tmem_d, da, db, idesc, (kb > c.kb_begin || k > 0) ? 1u : 0u);
           }
-          umma_commit(&empty_bar[stage]);      // slot reusable once these MMAs have read it
+          // slot reusable (in both CTAs of a pair) once these MMAs have read it
+          if (PAIR) umma_commit_pair(&empty_bar[stage], 3);
+          else umma_commit(&empty_bar[stage]);
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tmem_full_bar[ab]);       // accumulator complete
+        if (PAIR) umma_commit_pair(&tmem_full_bar[ab], 3);   // accumulator complete (both CTAs)
+        else umma_commit(&tmem_full_bar[ab]);
       }
     }
   } else {
@@ -289,16 +329,17 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
         for (; ch < kChunks; ++ch)
           if (chunk_n(c, ch) < p.N) return;
         ch = 0;
-        w += gridDim.x;
+        w += w_stride;
       }
     };
     auto issue_r = [&](int w, int ch) {
       const ItemCoord c = decode(p, w);
       mbar_arrive_expect_tx(rbar, kChunkBytes);
-      tma_load_2d(buf1, &map_r, rbar, chunk_n(c, ch), c.m_blk * BM + q * 32);
+      tma_load_2d(buf1, &map_r, rbar, chunk_n(c, ch),
+                  c.m_blk * kTileM + static_cast<int>(rank) * BM + q * 32);
     };
     if (kHasR && lane == 0) {
-      int w = blockIdx.x, ch = 0;
+      int w = w_first, ch = 0;
       next_valid(w, ch);
       if (w < p.items) issue_r(w, ch);
     }
@@ -322,10 +363,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
     };
 
     int i = 0;
-    for (int w = blockIdx.x; w < p.items; w += gridDim.x, ++i) {
+    for (int w = w_first; w < p.items; w += w_stride, ++i) {
       const ItemCoord c = decode(p, w);
       const int ab = i & 1;
-      const int row0 = c.m_blk * BM + q * 32;
+      const int row0 = c.m_blk * kTileM + static_cast<int>(rank) * BM + q * 32;
       if (EPI == EPI_GELU_GRAD && c.n_blk != cs_nblk) {
         flush_colsum();
         cs_nblk = c.n_blk;
@@ -444,7 +485,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
           // last TMEM read of this tile is done: hand the accumulator back to the MMA warp
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&tmem_empty_bar[ab]);
+          if (lane == 0) {
+            if (PAIR) mbar_arrive_cluster(dsmem_map(smem_u32(&tmem_empty_bar[ab]), 0));
+            else mbar_arrive(&tmem_empty_bar[ab]);
+          }
         }
 
         fence_proxy_async();          // make this lane's st.shared visible to the TMA engine
@@ -480,7 +524,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
         // the last chunk was skipped (ragged N) or the fp32 path ran: release the accumulator here
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty_bar[ab]);
+        if (lane == 0) {
+          if (PAIR) mbar_arrive_cluster(dsmem_map(smem_u32(&tmem_empty_bar[ab]), 0));
+          else mbar_arrive(&tmem_empty_bar[ab]);
+        }
       }
     }
     flush_colsum();
@@ -488,18 +535,22 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
   }
 
   tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, L::kTmemCols);
+  if (PAIR) cluster_sync_all();    // the leader's MMAs read the peer's shared memory until the end
+  else __syncthreads();
+  if (warp == 1) {
+    if (PAIR) tmem_dealloc_pair(tmem_base, L::kTmemCols);
+    else tmem_dealloc(tmem_base, L::kTmemCols);
+  }
 }
 
-template <int BN, int EPI>
+template <int BN, int EPI, bool PAIR>
 int launch2(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md0,
             const CUtensorMap& md1, const CUtensorMap& mr, const Gemm2Params& p, int grid,
             cudaStream_t stream) {
-  using L = Cfg<BN>;
+  using L = Cfg<BN, PAIR>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm2_kernel<BN, EPI>,
+    cudaError_t e = cudaFuncSetAttribute(gemm2_kernel<BN, EPI, PAIR>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
     if (e != cudaSuccess) {
       set_last_error("gemm_bf16: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
@@ -507,8 +558,19 @@ int launch2(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md0
     }
     attr_set = true;
   }
-  gemm2_kernel<BN, EPI><<<grid, kThreads, L::kTotal, stream>>>(ma, mb, md0, md1, mr, p);
-  cudaError_t e = cudaGetLastError();
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = L::kTotal;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = PAIR ? 2 : 1;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm2_kernel<BN, EPI, PAIR>, ma, mb, md0, md1, mr, p);
   if (e != cudaSuccess) {
     set_last_error("gemm_bf16 launch: %s", cudaGetErrorString(e));
     return CNX_ERR_LAUNCH;
@@ -516,32 +578,37 @@ int launch2(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md0
   return CNX_OK;
 }
 
-template <int BN>
+template <int BN, bool PAIR>
 int dispatch(int epi, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md0,
              const CUtensorMap& md1, const CUtensorMap& mr, const Gemm2Params& p, int grid,
              cudaStream_t stream) {
   switch (epi) {
-    case EPI_STORE_BF16:    return launch2<BN, EPI_STORE_BF16>(ma, mb, md0, md1, mr, p, grid, stream);
-    case EPI_BIAS_GELU:     return launch2<BN, EPI_BIAS_GELU>(ma, mb, md0, md1, mr, p, grid, stream);
-    case EPI_BIAS_RESIDUAL: return launch2<BN, EPI_BIAS_RESIDUAL>(ma, mb, md0, md1, mr, p, grid, stream);
-    case EPI_GELU_GRAD:     return launch2<BN, EPI_GELU_GRAD>(ma, mb, md0, md1, mr, p, grid, stream);
-    case EPI_STORE_F32:     return launch2<BN, EPI_STORE_F32>(ma, mb, md0, md1, mr, p, grid, stream);
-    case EPI_ATOMIC_F32:    return launch2<BN, EPI_ATOMIC_F32>(ma, mb, md0, md1, mr, p, grid, stream);
+    case EPI_STORE_BF16:    return launch2<BN, EPI_STORE_BF16, PAIR>(ma, mb, md0, md1, mr, p, grid, stream);
+    case EPI_BIAS_GELU:     return launch2<BN, EPI_BIAS_GELU, PAIR>(ma, mb, md0, md1, mr, p, grid, stream);
+    case EPI_BIAS_RESIDUAL: return launch2<BN, EPI_BIAS_RESIDUAL, PAIR>(ma, mb, md0, md1, mr, p, grid, stream);
+    case EPI_GELU_GRAD:     return launch2<BN, EPI_GELU_GRAD, PAIR>(ma, mb, md0, md1, mr, p, grid, stream);
+    case EPI_STORE_F32:     return launch2<BN, EPI_STORE_F32, PAIR>(ma, mb, md0, md1, mr, p, grid, stream);
+    case EPI_ATOMIC_F32:    return launch2<BN, EPI_ATOMIC_F32, PAIR>(ma, mb, md0, md1, mr, p, grid, stream);
     default: break;
   }
   set_last_error("gemm_bf16: unsupported epilogue %d", epi);
   return CNX_ERR_BAD_ARG;
 }
 
-// rounds of the persistent loop for a given column-tile width
-double tile_cost(int M, int N, int BN, int nsm, int* grid_out) {
-  const int tiles_m = (M + BM - 1) / BM, tiles_n = (N + BN - 1) / BN;
+// Persistent-loop cost of a tiling: (rounds) x (tile width), for `units` workers (SMs, or CTA
+// pairs) over tiles of tile_m rows.  `workers_out` = workers to launch.
+double tile_cost(int M, int N, int BN, int tile_m, int units, int* workers_out) {
+  const int tiles_m = (M + tile_m - 1) / tile_m, tiles_n = (N + BN - 1) / BN;
   const int items = tiles_m * tiles_n;
-  int grid = nsm;
-  if (tiles_n <= nsm) grid = (nsm / tiles_n) * tiles_n;   // a CTA keeps its column block
-  if (grid > items) grid = items;
-  const int rounds = (items + grid - 1) / grid;
-  *grid_out = grid;
+  // option 1: every worker keeps one column block for its whole life (column sums stay in
+  // registers); option 2: all workers, column block changes from item to item
+  int w1 = (tiles_n <= units) ? (units / tiles_n) * tiles_n : units;
+  if (w1 > items) w1 = items;
+  int w2 = units < items ? units : items;
+  const int r1 = (items + w1 - 1) / w1, r2 = (items + w2 - 1) / w2;
+  int workers = w1, rounds = r1;
+  if (r2 < r1) { workers = w2; rounds = r2; }
+  *workers_out = workers;
   // BN=128 tiles pull 1.5x the operand bytes per MAC through L2/shared memory: charge 15 %
   return static_cast<double>(rounds) * BN * (BN == 128 ? 1.15 : 1.0);
 }
@@ -594,17 +661,29 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   p.ldd0 = a.ldd0;
   p.nkb_total = nkb;
 
+  // CTA pairs (256-row tiles through cta_group::2) whenever there are at least two row tiles
+  // (CNX_GEMM_NO_PAIR=1 forces the single-CTA kernel: A/B debugging switch)
+  static const bool no_pair = getenv("CNX_GEMM_NO_PAIR") != nullptr;
+  // measured (profiles/r01_microbench_v4_pair.json): pairs win on the long-K GEMMs (weight gradients
+  // +6 %, fc2 / dxhat at K >= 1024 +3 %) and lose on the short-K GELU epilogues, where the two
+  // CTAs' epilogues gate each other's next tile
+  const bool long_k_plain = (epi == EPI_STORE_BF16 || epi == EPI_BIAS_RESIDUAL) && a.K >= 1024 &&
+                            a.M >= 16384;
+  const bool pair = !no_pair && a.M > BM && nsm >= 2 && (epi == EPI_STORE_F32 || long_k_plain);
+  const int tile_m = pair ? 2 * BM : BM;
+  const int units = pair ? nsm / 2 : nsm;
+
   // column-tile width: fewer persistent rounds wins; 256 preferred (less operand traffic per MAC)
-  int BN = 256, grid = 0;
+  int BN = 256, workers = 0;
   {
-    int g256, g128;
-    const double c256 = tile_cost(a.M, a.N, 256, nsm, &g256);
-    const double c128 = tile_cost(a.M, a.N, 128, nsm, &g128);
+    int w256, w128;
+    const double c256 = tile_cost(a.M, a.N, 256, tile_m, units, &w256);
+    const double c128 = tile_cost(a.M, a.N, 128, tile_m, units, &w128);
     // split-K weight gradients are one long main loop per item: the wide tile always wins there
     const bool wide = (epi == EPI_STORE_F32) ? (a.N > 128) : !(a.N <= 128 || c128 < c256);
-    if (wide) { BN = 256; grid = g256; } else { BN = 128; grid = g128; }
+    if (wide) { BN = 256; workers = w256; } else { BN = 128; workers = w128; }
   }
-  p.tiles_m = (a.M + BM - 1) / BM;
+  p.tiles_m = (a.M + tile_m - 1) / tile_m;
   p.tiles_n = (a.N + BN - 1) / BN;
   int splits = 1;
   if (epi == EPI_STORE_F32) {
@@ -613,12 +692,12 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
     // that minimises (persistent rounds) x (k-blocks per item), keeping >= 4 k-blocks per item.
     const int tiles = p.tiles_m * p.tiles_n;
     int max_splits = nkb / 4;
-    if (max_splits > 2 * nsm) max_splits = 2 * nsm;
+    if (max_splits > 2 * units) max_splits = 2 * units;
     long best = -1;
     for (int s = 1; s <= max_splits; ++s) {
       const int kb = (nkb + s - 1) / s;
       const int eff = (nkb + kb - 1) / kb;
-      const long rounds = (static_cast<long>(tiles) * eff + nsm - 1) / nsm;
+      const long rounds = (static_cast<long>(tiles) * eff + units - 1) / units;
       const long cost = rounds * (kb + 6);     // + ~6 k-blocks of prologue/epilogue per item
       if (best < 0 || cost < best) { best = cost; splits = eff; }
     }
@@ -629,7 +708,8 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   p.splits = splits;
   p.kb_per_split = kbps;
   p.items = p.tiles_m * p.tiles_n * splits;
-  if (splits > 1) grid = p.items < nsm ? p.items : nsm;
+  if (splits > 1) workers = p.items < units ? p.items : units;
+  const int grid = pair ? 2 * workers : workers;
 
   CUtensorMap ma, mb, md0, md1, mr;
   int rc;
@@ -649,7 +729,7 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
     const uint64_t dims_k[2] = {(uint64_t)a.K, (uint64_t)a.N};
     const uint64_t dims_mn[2] = {(uint64_t)a.N, (uint64_t)a.K};
     const uint64_t st[1] = {(uint64_t)a.ldb * 2};
-    const uint32_t box_k[2] = {BK, (uint32_t)BN};
+    const uint32_t box_k[2] = {BK, (uint32_t)(pair ? BN / 2 : BN)};   // a pair member stages half of B
     const uint32_t box_mn[2] = {64, BK};
     rc = make_tensor_map(&mb, a.B, 2, 2, a.b_mn_major ? dims_mn : dims_k, st,
                          a.b_mn_major ? box_mn : box_k, 3);
@@ -677,8 +757,11 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
     if (rc != CNX_OK) return rc;
   }
 
-  return BN == 256 ? dispatch<256>(epi, ma, mb, md0, md1, mr, p, grid, stream)
-                   : dispatch<128>(epi, ma, mb, md0, md1, mr, p, grid, stream);
+  if (pair)
+    return BN == 256 ? dispatch<256, true>(epi, ma, mb, md0, md1, mr, p, grid, stream)
+                     : dispatch<128, true>(epi, ma, mb, md0, md1, mr, p, grid, stream);
+  return BN == 256 ? dispatch<256, false>(epi, ma, mb, md0, md1, mr, p, grid, stream)
+                   : dispatch<128, false>(epi, ma, mb, md0, md1, mr, p, grid, stream);
 }
 
 }  // namespace cnx
