@@ -283,6 +283,7 @@ def _work_table():
     return {
         "cnx_dwconv_ln_fwd": ("dwconv_ln_fwd", "hbm", dw_fwd),
         "cnx_dwconv_ln_bwd": ("dwconv_ln_bwd", "hbm", dw_bwd),
+        "cnx_dwconv_ln_bwd_acc": ("dwconv_ln_bwd", "hbm", dw_bwd),
         "cnx_fc1_gelu_fwd": ("mlp_gemm", "tensor", lambda a: mlp(a, 5, 6)),
         "cnx_fc2_residual_fwd": ("mlp_gemm", "tensor", lambda a: mlp(a, 5, 6)),
         "cnx_mlp_bwd_dz": ("mlp_gemm", "tensor", lambda a: mlp(a, 5, 6)),

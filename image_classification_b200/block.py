@@ -41,6 +41,7 @@ class _BlockFn(torch.autograd.Function):
         y = ops.fc2_residual_fwd(h, fw.w2f, fw.b2f, x_nhwc.reshape(M, C))
         ctx.save_for_backward(x, xhat, rstd, z, h, norm_w, norm_b, fc1_w, fc2_w, fc2_b, gamma)
         ctx.fw = fw
+        ctx.module = module
         return y.view(B, H, W, C).permute(0, 3, 1, 2)
 
     @staticmethod
@@ -53,14 +54,25 @@ class _BlockFn(torch.autograd.Function):
         if dy_nhwc.dtype != torch.bfloat16 or not dy_nhwc.is_contiguous():
             dy_nhwc = dy_nhwc.to(torch.bfloat16).contiguous()
         dy2d = dy_nhwc.view(M, C)
-        dz, db1f = ops.mlp_bwd_dz(dy2d, fw.w2fT, z)
+        win = ctx.module._window          # GradWindow slot of this block, or None
+        a = win.acc if win is not None and win.owner.active else None
+        dz, db1f = ops.mlp_bwd_dz(dy2d, fw.w2fT, z, None if a is None else a["db1f"])
         dxhat = ops.mlp_bwd_dxhat(dz, fw.w1fT)
-        dw2f, dw1f = ops.mlp_bwd_wgrad(dy2d, h, dz, xhat.view(M, C))
-        dx, dwt, dbias, db2f = ops.dwconv_ln_bwd(dxhat.view(B, H, W, C), xhat, rstd,
-                                                 x.permute(0, 2, 3, 1), dy_nhwc, fw.wt_dw)
+        dw2f, dw1f = ops.mlp_bwd_wgrad(dy2d, h, dz, xhat.view(M, C),
+                                       None if a is None else (a["dw2f"], a["dw1f"]))
+        dx, dwt, dbias, db2f = ops.dwconv_ln_bwd(
+            dxhat.view(B, H, W, C), xhat, rstd, x.permute(0, 2, 3, 1), dy_nhwc, fw.wt_dw,
+            None if a is None else (a["dwt"], a["dbias"], a["db2f"]))
+        if a is not None and not win.owner.boundary:
+            # inside an accumulation window: the folded-parameter gradients stay in the window's
+            # fp32 accumulators; parameter gradients are produced on the boundary micro-batch only
+            return (dx.permute(0, 3, 1, 2),) + (None,) * 10
         d_conv_w, d_norm_w, d_norm_b, d_fc1_w, d_fc2_w, d_fc2_b, d_gamma = ops.unfold_block_grads(
             dw1f, db1f, dw2f, db2f, dwt, norm_w.detach(), norm_b.detach(), fc1_w.detach(),
             fc2_w.detach(), fc2_b.detach(), gamma.detach())
+        if a is not None:
+            # the two pass-through gradients alias the window's accumulators: hand out copies
+            dbias, db1f = dbias.clone(), db1f.clone()
         return (dx.permute(0, 3, 1, 2), d_conv_w, dbias, d_norm_w, d_norm_b, d_fc1_w, db1f,
                 d_fc2_w, d_fc2_b, d_gamma, None)
 
@@ -113,6 +125,7 @@ class ConvNeXtBlockB200(nn.Module):
         self.drop_path = nn.Identity()   # create_model passes no drop_path_rate (:488-492)
         self._fold_key = None
         self._fold = None
+        self._window = None              # set by GradWindow
 
     # -- folded bf16 weights, cached per weight version -------------------------------------
     def _folded(self, *params) -> ops.FoldedWeights:
@@ -160,6 +173,80 @@ class ConvNeXtBlockB200(nn.Module):
         if getattr(other, "gamma", None) is not None:
             self.gamma.copy_(other.gamma.reshape(-1))
         return self
+
+
+class _WindowSlot:
+    __slots__ = ("owner", "acc")
+
+    def __init__(self, owner, acc):
+        self.owner, self.acc = owner, acc
+
+
+class GradWindow:
+    """Gradient-accumulation window for every ConvNeXtBlockB200 of `model`.
+
+    The reference accumulates 2 micro-batches per optimizer step
+    (/root/reference/train_advanced_v4.py:225, config.py:37).  Autograd would run the adjoint of the
+    weight folding (cnx_unfold_block_grads) and an `AccumulateGrad` add per parameter on every
+    micro-batch.  Inside a window the blocks instead accumulate the gradients of their FOLDED
+    parameters (fp32, one flat buffer for the whole model, zeroed by one memset) across
+    micro-batches through the kernels' += outputs, and emit parameter gradients only on the
+    boundary micro-batch.  The sum is the same; only the summation order differs.
+
+        win = GradWindow(model)
+        win.begin(); win.set_boundary(False); loss1.backward()
+        win.set_boundary(True); loss2.backward()      # .grad of the block parameters appears here
+    """
+
+    def __init__(self, model: nn.Module):
+        self.blocks = [m for m in model.modules() if isinstance(m, ConvNeXtBlockB200)]
+        self.active = False
+        self.boundary = True
+        self.flat = None
+        if not self.blocks:
+            return
+        dev = self.blocks[0].gamma.device
+        shapes = lambda C: (("dw1f", (4 * C, C)), ("dw2f", (C, 4 * C)), ("db1f", (4 * C,)),
+                            ("dwt", (49, C)), ("dbias", (C,)), ("db2f", (C,)))
+        total = 0
+        for b in self.blocks:
+            C = b.gamma.numel()
+            total += sum((_numel(sh) + 3) // 4 * 4 for _, sh in shapes(C))
+        self.flat = torch.zeros(total, device=dev, dtype=torch.float32)
+        off = 0
+        for b in self.blocks:
+            acc = {}
+            for name, sh in shapes(b.gamma.numel()):
+                n = _numel(sh)
+                acc[name] = self.flat[off:off + n].view(sh)
+                off += (n + 3) // 4 * 4          # keep every slice 16-byte aligned
+            b._window = _WindowSlot(self, acc)
+
+    def begin(self):
+        """Start a window: zero all accumulators (one memset)."""
+        if self.flat is not None:
+            self.flat.zero_()
+            self.active = True
+            self.boundary = False
+
+    def set_boundary(self, boundary: bool):
+        self.boundary = bool(boundary)
+
+    def end(self):
+        self.active = False
+        self.boundary = True
+
+    def detach(self):
+        for b in self.blocks:
+            b._window = None
+        self.active = False
+
+
+def _numel(shape):
+    n = 1
+    for d in shape:
+        n *= d
+    return n
 
 
 def swap_blocks(model: nn.Module) -> int:

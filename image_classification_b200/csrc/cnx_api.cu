@@ -89,7 +89,19 @@ int cnx_dwconv_ln_bwd(const void* dxhat, const void* xhat, const float* rstd, co
   CNX_REQUIRE_PTR(dy); CNX_REQUIRE_PTR(wt_dw); CNX_REQUIRE_PTR(dx); CNX_REQUIRE_PTR(dwt);
   CNX_REQUIRE_PTR(dbias); CNX_REQUIRE_PTR(dy_colsum);
   return dwconv_ln_bwd(dxhat, xhat, rstd, x, dy, wt_dw, dx, dwt, dbias, dy_colsum, B, H, W, C,
-                       workspace, workspace_bytes, as_stream(stream));
+                       workspace, workspace_bytes, 0, as_stream(stream));
+}
+
+int cnx_dwconv_ln_bwd_acc(const void* dxhat, const void* xhat, const float* rstd, const void* x,
+                      const void* dy, const float* wt_dw, void* dx, float* dwt, float* dbias,
+                      float* dy_colsum, int B, int H, int W, int C, void* workspace,
+                      size_t workspace_bytes, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(dxhat); CNX_REQUIRE_PTR(xhat); CNX_REQUIRE_PTR(rstd); CNX_REQUIRE_PTR(x);
+  CNX_REQUIRE_PTR(dy); CNX_REQUIRE_PTR(wt_dw); CNX_REQUIRE_PTR(dx); CNX_REQUIRE_PTR(dwt);
+  CNX_REQUIRE_PTR(dbias); CNX_REQUIRE_PTR(dy_colsum);
+  return dwconv_ln_bwd(dxhat, xhat, rstd, x, dy, wt_dw, dx, dwt, dbias, dy_colsum, B, H, W, C,
+                       workspace, workspace_bytes, 1, as_stream(stream));
 }
 
 int cnx_layernorm_fwd(const void* x, const float* weight, const float* bias, void* y, float* mean,

@@ -14,12 +14,12 @@ size_t dwconv_ln_bwd_workspace_bytes(int B, int H, int W, int C);
 int dwconv_ln_bwd(const void* dxhat, const void* xhat, const float* rstd, const void* x,
                   const void* dy, const float* wt, void* dx, float* dwt, float* dbias,
                   float* dy_colsum, int B, int H, int W, int C, void* workspace, size_t ws_bytes,
-                  cudaStream_t stream);
+                  int accumulate, cudaStream_t stream);
 // pure depthwise-conv backward: dconv = dL/d(conv output) already formed (by ln_rows_bwd or by the
 // LN-backward epilogue of the fc1 data-gradient GEMM)
 int dwconv_bwd(const void* dconv, const void* x, const void* dy, const float* wt, void* dx,
                float* dwt, float* dbias, float* dy_colsum, int B, int H, int W, int C,
-               cudaStream_t stream);
+               int accumulate, cudaStream_t stream);
 
 // ---- ln_rows.cu : LayerNorm with affine over [M, C] bf16 rows (stem / downsample LayerNorm2d)
 int ln_affine_fwd(const void* x, const float* w, const float* b, void* y, float* mean, float* rstd,

@@ -483,7 +483,7 @@ size_t dwconv_ln_bwd_workspace_bytes(int B, int H, int W, int C) {
 int dwconv_ln_bwd(const void* dxhat, const void* xhat, const float* rstd, const void* x,
                   const void* dy, const float* wt, void* dx, float* dwt, float* dbias,
                   float* dy_colsum, int B, int H, int W, int C, void* workspace, size_t ws_bytes,
-                  cudaStream_t stream) {
+                  int accumulate, cudaStream_t stream) {
   int rc = check_shape("dwconv_ln_bwd", B, H, W, C);
   if (rc != CNX_OK) return rc;
   const size_t need = dwconv_ln_bwd_workspace_bytes(B, H, W, C);
@@ -495,12 +495,13 @@ int dwconv_ln_bwd(const void* dxhat, const void* xhat, const float* rstd, const 
   }
   rc = ln_rows_bwd(dxhat, xhat, rstd, workspace, static_cast<int64_t>(B) * H * W, C, stream);
   if (rc != CNX_OK) return rc;
-  return dwconv_bwd(workspace, x, dy, wt, dx, dwt, dbias, dy_colsum, B, H, W, C, stream);
+  return dwconv_bwd(workspace, x, dy, wt, dx, dwt, dbias, dy_colsum, B, H, W, C, accumulate,
+                    stream);
 }
 
 int dwconv_bwd(const void* dconv, const void* x, const void* dy, const float* wt, void* dx,
                float* dwt, float* dbias, float* dy_colsum, int B, int H, int W, int C,
-               cudaStream_t stream) {
+               int accumulate, cudaStream_t stream) {
   int rc = check_shape("dwconv_bwd", B, H, W, C);
   if (rc != CNX_OK) return rc;
   ConvParams p{};
@@ -513,9 +514,11 @@ int dwconv_bwd(const void* dconv, const void* x, const void* dy, const float* wt
   p.out = static_cast<__nv_bfloat16*>(dx);
   p.dy = static_cast<const __nv_bfloat16*>(dy);
   p.dwt = dwt; p.dbias = dbias; p.dy_colsum = dy_colsum;
-  cudaMemsetAsync(dwt, 0, sizeof(float) * 49 * C, stream);
-  cudaMemsetAsync(dbias, 0, sizeof(float) * C, stream);
-  cudaMemsetAsync(dy_colsum, 0, sizeof(float) * C, stream);
+  if (!accumulate) {
+    cudaMemsetAsync(dwt, 0, sizeof(float) * 49 * C, stream);
+    cudaMemsetAsync(dbias, 0, sizeof(float) * C, stream);
+    cudaMemsetAsync(dy_colsum, 0, sizeof(float) * C, stream);
+  }
   return (W > 7) ? launch_bwd<14>(dconv, x, p, B, H, W, C, stream)
                  : launch_bwd<7>(dconv, x, p, B, H, W, C, stream);
 }

@@ -704,7 +704,9 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   }
   int kbps = (nkb + splits - 1) / splits;
   splits = (nkb + kbps - 1) / kbps;             // no empty split
-  if (splits > 1) epi = EPI_ATOMIC_F32;
+  // D0 += acc in every case (the header's contract): callers may accumulate several launches
+  // (gradient-accumulation windows) into one buffer
+  if (epi == EPI_STORE_F32) epi = EPI_ATOMIC_F32;
   p.splits = splits;
   p.kb_per_split = kbps;
   p.items = p.tiles_m * p.tiles_n * splits;

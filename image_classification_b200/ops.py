@@ -98,8 +98,11 @@ def dwconv_ln_fwd(x_nhwc: torch.Tensor, wt_dw: torch.Tensor, bias: torch.Tensor,
     return xhat, mean, rstd
 
 
-def dwconv_ln_bwd(dxhat, xhat, rstd, x_nhwc, dy, wt_dw):
-    """-> (dx [B,H,W,C] bf16, dwt [49,C] f32, dbias [C] f32, dy_colsum [C] f32)."""
+def dwconv_ln_bwd(dxhat, xhat, rstd, x_nhwc, dy, wt_dw, acc=None):
+    """-> (dx [B,H,W,C] bf16, dwt [49,C] f32, dbias [C] f32, dy_colsum [C] f32).
+
+    acc=(dwt, dbias, dy_colsum): accumulate (+=) into these existing fp32 buffers instead of
+    overwriting fresh ones (gradient-accumulation window, see block.GradWindow)."""
     for n, t in (("dxhat", dxhat), ("xhat", xhat), ("x", x_nhwc), ("dy", dy)):
         _chk(t, torch.bfloat16, n)
     _chk(rstd, torch.float32, "rstd")
@@ -107,13 +110,18 @@ def dwconv_ln_bwd(dxhat, xhat, rstd, x_nhwc, dy, wt_dw):
     B, H, W, C = x_nhwc.shape
     dev = x_nhwc.device
     dx = torch.empty_like(x_nhwc)
-    dwt = torch.empty(49, C, device=dev, dtype=torch.float32)
-    dbias = torch.empty(C, device=dev, dtype=torch.float32)
-    dycs = torch.empty(C, device=dev, dtype=torch.float32)
+    if acc is None:
+        dwt = torch.empty(49, C, device=dev, dtype=torch.float32)
+        dbias = torch.empty(C, device=dev, dtype=torch.float32)
+        dycs = torch.empty(C, device=dev, dtype=torch.float32)
+        entry = "cnx_dwconv_ln_bwd"
+    else:
+        dwt, dbias, dycs = (_chk(t, torch.float32, "acc") for t in acc)
+        entry = "cnx_dwconv_ln_bwd_acc"
     # scratch for dconv = LN-backward(dxhat): sized by the library, owned by PyTorch's allocator
     ws_bytes = int(_lib.load().cnx_workspace_bytes(_lib.CNX_OP_DWCONV_LN_BWD, B, H, W, C))
     ws = torch.empty(ws_bytes, device=dev, dtype=torch.uint8)
-    _lib.call("cnx_dwconv_ln_bwd", _p(dxhat), _p(xhat), _p(rstd), _p(x_nhwc), _p(dy), _p(wt_dw),
+    _lib.call(entry, _p(dxhat), _p(xhat), _p(rstd), _p(x_nhwc), _p(dy), _p(wt_dw),
               _p(dx), _p(dwt), _p(dbias), _p(dycs), B, H, W, C, _p(ws), ws_bytes, _stream(x_nhwc))
     return dx, dwt, dbias, dycs
 
@@ -203,10 +211,12 @@ def fc2_residual_fwd(h, w2f, b2f, x2d):
     return y
 
 
-def mlp_bwd_dz(dy2d, w2fT, z):
+def mlp_bwd_dz(dy2d, w2fT, z, db1f=None):
+    """db1f: existing fp32 [4C] accumulator (+=) or None for a fresh zero-filled one."""
     M, C = dy2d.shape
     dz = torch.empty_like(z)
-    db1f = torch.zeros(4 * C, device=z.device, dtype=torch.float32)
+    if db1f is None:
+        db1f = torch.zeros(4 * C, device=z.device, dtype=torch.float32)
     _lib.call("cnx_mlp_bwd_dz", _p(_chk(dy2d, torch.bfloat16, "dy")),
               _p(_chk(w2fT, torch.bfloat16, "w2fT")), _p(_chk(z, torch.bfloat16, "z")), _p(dz),
               _p(db1f), M, C, _stream(z))
@@ -222,10 +232,14 @@ def mlp_bwd_dxhat(dz, w1fT):
     return dxhat
 
 
-def mlp_bwd_wgrad(dy2d, h, dz, xhat2d):
+def mlp_bwd_wgrad(dy2d, h, dz, xhat2d, acc=None):
+    """acc=(dw2f, dw1f): existing fp32 accumulators (+=) or None for fresh zero-filled ones."""
     M, C = dy2d.shape
-    dw2f = torch.zeros(C, 4 * C, device=h.device, dtype=torch.float32)
-    dw1f = torch.zeros(4 * C, C, device=h.device, dtype=torch.float32)
+    if acc is None:
+        dw2f = torch.zeros(C, 4 * C, device=h.device, dtype=torch.float32)
+        dw1f = torch.zeros(4 * C, C, device=h.device, dtype=torch.float32)
+    else:
+        dw2f, dw1f = (_chk(t, torch.float32, "acc") for t in acc)
     _lib.call("cnx_mlp_bwd_wgrad", _p(_chk(dy2d, torch.bfloat16, "dy")),
               _p(_chk(h, torch.bfloat16, "h")), _p(_chk(dz, torch.bfloat16, "dz")),
               _p(_chk(xhat2d, torch.bfloat16, "xhat")), _p(dw2f), _p(dw1f), M, C, _stream(h))

@@ -50,18 +50,30 @@ class TrainStep:
     every batch, exactly like the body of the reference's `for batch_idx, ...` loop."""
 
     def __init__(self, model, criterion, optimizer, scheduler=None, scaler=None, ema=None,
-                 cfg: StepConfig | None = None, grad_reducer=None):
+                 cfg: StepConfig | None = None, grad_reducer=None, use_grad_window: bool = True):
         self.model, self.criterion, self.optimizer = model, criterion, optimizer
         self.scheduler, self.scaler, self.ema = scheduler, scaler, ema
         self.cfg = cfg or StepConfig()
         self.grad_reducer = grad_reducer          # ddp.BucketedGradReducer or None
         self.params = [p for p in model.parameters() if p.requires_grad]
+        # with accumulation > 1 the B200 blocks keep folded-parameter gradients in one fp32 window
+        # and run the fold adjoint once per optimizer step (block.GradWindow); GradScaler's scale is
+        # constant inside a window (it only changes in scaler.update(), :230)
+        self.window = None
+        if self.cfg.gradient_accumulation_steps > 1 and use_grad_window:
+            from .block import GradWindow
+            w = GradWindow(model)
+            self.window = w if w.blocks else None
 
     def micro_step(self, images: torch.Tensor, labels: torch.Tensor, batch_idx: int) -> torch.Tensor:
         cfg = self.cfg
         boundary = (batch_idx + 1) % cfg.gradient_accumulation_steps == 0     # :225
         if self.grad_reducer is not None:
             self.grad_reducer.set_sync(boundary)       # all-reduce only on the boundary micro-step
+        if self.window is not None:
+            if batch_idx % cfg.gradient_accumulation_steps == 0:
+                self.window.begin()
+            self.window.set_boundary(boundary)
         if self.scaler is not None:
             with torch.autocast("cuda", dtype=cfg.amp_dtype):                 # :217
                 outputs = self.model(images)                                   # :218

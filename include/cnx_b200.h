@@ -107,6 +107,14 @@ int cnx_dwconv_ln_bwd(const void* dxhat, const void* xhat, const float* rstd, co
                       float* dy_colsum, int B, int H, int W, int C, void* workspace,
                       size_t workspace_bytes, void* stream);
 
+/* Same, but dwt / dbias / dy_colsum are ACCUMULATED into (+=): used inside a gradient-accumulation
+ * window (/root/reference/train_advanced_v4.py:225, accumulate 2) so that the adjoint of the
+ * weight folding runs once per optimizer step instead of once per micro-batch. */
+int cnx_dwconv_ln_bwd_acc(const void* dxhat, const void* xhat, const float* rstd, const void* x,
+                          const void* dy, const float* wt_dw, void* dx, float* dwt, float* dbias,
+                          float* dy_colsum, int B, int H, int W, int C, void* workspace,
+                          size_t workspace_bytes, void* stream);
+
 /* timm LayerNorm2d (channels-last LayerNorm WITH affine) of the stem and of every stage's
  * `downsample` (un-vendored timm; reached from /root/reference/train_advanced_v4.py:131,134-135;
  * SURVEY.md §8 f-1): x, y [M, C] bf16 rows (NHWC), weight / bias [C] fp32, mean / rstd [M] fp32
@@ -136,7 +144,8 @@ int cnx_mlp_bwd_dz(const void* dy, const void* w2fT, const void* z, void* dz, fl
                    int C, void* stream);
 /* dxhat = dz @ w1f   ([M,C] bf16). */
 int cnx_mlp_bwd_dxhat(const void* dz, const void* w1fT, void* dxhat, int M, int C, void* stream);
-/* dw2f[C,4C] += dy^T @ h ; dw1f[4C,C] += dz^T @ xhat   (fp32, zero-filled by caller). */
+/* dw2f[C,4C] += dy^T @ h ; dw1f[4C,C] += dz^T @ xhat   (fp32; always accumulated: zero-fill or keep
+ * accumulating across micro-batches). */
 int cnx_mlp_bwd_wgrad(const void* dy, const void* h, const void* dz, const void* xhat, float* dw2f,
                       float* dw1f, int M, int C, void* stream);
 

@@ -131,3 +131,48 @@ def test_loop_mirror_matches_oracle_loop_on_first_steps(cnx_lib):
     lp = [step.micro_step(x[i].to(dev), t[i].to(dev), i).item() for i in range(2)]
     for a, b in zip(lp, lo):
         assert abs(a - b) < BF16_REL * abs(b), (lp, lo)
+
+
+def test_grad_window_matches_per_microbatch_accumulation(cnx_lib):
+    """block.GradWindow (folded-gradient accumulation, fold adjoint once per optimizer step) gives
+    the same parameter gradients as autograd's per-micro-batch accumulation."""
+    from image_classification_b200.block import GradWindow
+    from image_classification_b200.convnext import ConvNeXtTimmLike
+    dev = _dev()
+    torch.manual_seed(11)
+    model = ConvNeXtTimmLike(depths=(1, 1, 2, 1), dims=(64, 128, 256, 512), num_classes=44).to(dev)
+    with torch.no_grad():
+        for n, p in model.named_parameters():
+            if n.endswith("gamma"):
+                p.copy_(torch.rand_like(p) * 0.9 + 0.1)
+    xs = [torch.randn(4, 3, 64, 64, device=dev) for _ in range(2)]
+    ts = [torch.softmax(torch.randn(4, 44, device=dev), 1) for _ in range(2)]
+
+    def run(window):
+        model.zero_grad(set_to_none=True)
+        for i in range(2):
+            if window is not None:
+                if i == 0:
+                    window.begin()
+                window.set_boundary(i == 1)
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                out = model(xs[i].contiguous(memory_format=torch.channels_last))
+                loss = -(ts[i] * torch.log_softmax(out.float(), 1)).sum(1).mean()
+            loss.backward()
+            if window is not None and i == 0:      # block parameters have no .grad yet
+                blk = model.stages[0].blocks[0]
+                assert blk.mlp.fc1.weight.grad is None and blk.gamma.grad is None
+        return {n: p.grad.clone() for n, p in model.named_parameters()}
+
+    ref = run(None)
+    win = GradWindow(model)
+    assert len(win.blocks) == 5
+    got = run(win)
+    win.detach()
+    for n in ref:
+        d = float((got[n].double() - ref[n].double()).abs().max())
+        s = float(ref[n].double().abs().max())
+        assert d <= 2e-5 * s + 1e-7, (n, d, s)       # same sums, different summation order
+    again = run(None)                                   # detached: back to the plain path
+    for n in ref:
+        assert torch.allclose(again[n], ref[n], rtol=1e-4, atol=1e-6), n
