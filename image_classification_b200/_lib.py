@@ -49,6 +49,7 @@ SIGNATURES = {
     "cnx_last_error_string": (c_char_p, []),
     "cnx_check_device": (I, []),
     "cnx_debug_timeout_flag": (I, []),
+    "cnx_debug_gemm_tuning": (None, [I, I, I, I]),
     "cnx_workspace_bytes": (c_size_t, [I, I, I, I, I]),
     "cnx_prep_block_weights": (I, [P] * 8 + [P] * 7 + [I, P]),
     "cnx_unfold_block_grads": (I, [P] * 11 + [P] * 7 + [I, P]),

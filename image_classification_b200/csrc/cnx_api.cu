@@ -33,6 +33,9 @@ const char* cnx_last_error_string(void) { return last_error(); }
 int cnx_check_device(void) { return check_device_sm100(); }
 
 int cnx_debug_timeout_flag(void) { return read_and_clear_timeout_flag(); }
+void cnx_debug_gemm_tuning(int stages, int pair, int bn, int splits) {
+  gemm_debug_tuning(stages, pair, bn, splits);
+}
 
 size_t cnx_workspace_bytes(int op, int B, int H, int W, int C) {
   if (op == CNX_OP_DWCONV_LN_BWD) return dwconv_ln_bwd_workspace_bytes(B, H, W, C);

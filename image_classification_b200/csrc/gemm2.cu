@@ -46,25 +46,34 @@ constexpr uint32_t kChunkBytes = 32 * 128;   // staging chunk: 32 rows x 64 bf16
 // stages its own 128 rows of A and HALF of B, which halves the B bytes written into and read out
 // of every SM's shared memory (ncu on the single-CTA kernel: tensor pipe capped near 63 % because
 // TMA writes + MMA operand reads exceed the 128 B/clk shared-memory port).
-template <int BN, bool PAIR>
+template <int BN, bool PAIR, bool STAGED>
 struct Cfg {
-  static constexpr int kStages = PAIR ? 4 : ((BN == 256) ? 3 : 4);
   static constexpr int kTileM = PAIR ? 2 * BM : BM;
   static constexpr int kBRows = PAIR ? BN / 2 : BN;      // rows of B staged by one CTA
   static constexpr uint32_t kABytes = BM * BK * 2;
   static constexpr uint32_t kBBytes = kBRows * BK * 2;
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
-  static constexpr uint32_t kEpiBytes = kEpiWarps * 2 * kChunkBytes;     // 64 KB
-  static constexpr uint32_t kBarBytes = 256;
+  // bf16 epilogues stage through shared memory (64 KB); the fp32 reduction epilogue does not
+  static constexpr uint32_t kEpiBytes = STAGED ? kEpiWarps * 2 * kChunkBytes : 0;
+  static constexpr uint32_t kBarBytes = 512;
+  static constexpr uint32_t kSmemMax = 232448;           // 227 KB opt-in limit per CTA
+  // as many operand stages as fit: the main loop is bound by bytes in flight towards L2
+  static constexpr int kFit = (kSmemMax - 1024 - kBarBytes - kEpiBytes) / kStageBytes;
+  static constexpr int kStages = kFit > 8 ? 8 : kFit;
   static constexpr uint32_t kTotal = kStages * kStageBytes + kEpiBytes + kBarBytes + 1024;
   static constexpr uint32_t kTmemCols = 2 * BN;
+  static_assert(kStages >= 3, "operand ring too shallow");
 };
+
+struct GemmTuning { int stages = -1, pair = -1, bn = -1, splits = -1; };
+GemmTuning g_tune;                 // development overrides (cnx_debug_gemm_tuning)
 
 struct Gemm2Params {
   int* timeout_flag;
   int M, N, K;
   int a_mn, b_mn;
   int tiles_m, tiles_n, splits, kb_per_split, nkb_total, items;
+  int stages;                      // operand-ring depth in use (<= Cfg::kStages)
   float* D0f; int64_t ldd0;        // fp32 output (EPI_STORE_F32 / EPI_ATOMIC_F32)
   const float* bias;
   float* colsum;
@@ -162,7 +171,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
              const __grid_constant__ CUtensorMap map_d0, const __grid_constant__ CUtensorMap map_d1,
              const __grid_constant__ CUtensorMap map_r, const Gemm2Params p) {
-  using L = Cfg<BN, PAIR>;
+  using L = Cfg<BN, PAIR, !(EPI == EPI_STORE_F32 || EPI == EPI_ATOMIC_F32)>;
   constexpr int kStages = L::kStages;
   constexpr int kTileM = L::kTileM;
   constexpr bool kHasR = (EPI == EPI_BIAS_RESIDUAL || EPI == EPI_GELU_GRAD);
@@ -265,7 +274,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
                 tma_load_2d(sb + a * (BK * 128), &map_b, &full_bar[stage], n0 + a * 64, k0);
             }
           }
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
       }
     }
@@ -302,7 +311,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
           // slot reusable (in both CTAs of a pair) once these MMAs have read it
           if (PAIR) umma_commit_pair(&empty_bar[stage], 3);
           else umma_commit(&empty_bar[stage]);
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
         if (PAIR) umma_commit_pair(&tmem_full_bar[ab], 3);   // accumulator complete (both CTAs)
         else umma_commit(&tmem_full_bar[ab]);
@@ -545,9 +554,11 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
 
 template <int BN, int EPI, bool PAIR>
 int launch2(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md0,
-            const CUtensorMap& md1, const CUtensorMap& mr, const Gemm2Params& p, int grid,
+            const CUtensorMap& md1, const CUtensorMap& mr, const Gemm2Params& p_in, int grid,
             cudaStream_t stream) {
-  using L = Cfg<BN, PAIR>;
+  using L = Cfg<BN, PAIR, !(EPI == EPI_STORE_F32 || EPI == EPI_ATOMIC_F32)>;
+  Gemm2Params p = p_in;
+  p.stages = (g_tune.stages >= 2 && g_tune.stages < L::kStages) ? g_tune.stages : L::kStages;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(gemm2_kernel<BN, EPI, PAIR>,
@@ -609,11 +620,17 @@ double tile_cost(int M, int N, int BN, int tile_m, int units, int* workers_out) 
   int workers = w1, rounds = r1;
   if (r2 < r1) { workers = w2; rounds = r2; }
   *workers_out = workers;
-  // BN=128 tiles pull 1.5x the operand bytes per MAC through L2/shared memory: charge 15 %
-  return static_cast<double>(rounds) * BN * (BN == 128 ? 1.15 : 1.0);
+  // the main loop is bound by operand bytes pulled from L2 (tools/gemm_sweep.py): an item costs
+  // the rows of A plus the rows of B one CTA stages per k-block
+  const int b_rows = (tile_m > BM) ? BN / 2 : BN;
+  return static_cast<double>(rounds) * (BM + b_rows);
 }
 
 }  // namespace
+
+void gemm_debug_tuning(int stages, int pair, int bn, int splits) {
+  g_tune.stages = stages; g_tune.pair = pair; g_tune.bn = bn; g_tune.splits = splits;
+}
 
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   if (a.M <= 0 || a.N <= 0 || a.K <= 0 || (a.N % 8) != 0 || (a.lda % 8) != 0 || (a.ldb % 8) != 0) {
@@ -664,12 +681,21 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   // CTA pairs (256-row tiles through cta_group::2) whenever there are at least two row tiles
   // (CNX_GEMM_NO_PAIR=1 forces the single-CTA kernel: A/B debugging switch)
   static const bool no_pair = getenv("CNX_GEMM_NO_PAIR") != nullptr;
-  // measured (profiles/r01_microbench_v4_pair.json): pairs win on the long-K GEMMs (weight gradients
-  // +6 %, fc2 / dxhat at K >= 1024 +3 %) and lose on the short-K GELU epilogues, where the two
-  // CTAs' epilogues gate each other's next tile
-  const bool long_k_plain = (epi == EPI_STORE_BF16 || epi == EPI_BIAS_RESIDUAL) && a.K >= 1024 &&
-                            a.M >= 16384;
-  const bool pair = !no_pair && a.M > BM && nsm >= 2 && (epi == EPI_STORE_F32 || long_k_plain);
+  // measured with tools/gemm_sweep.py (profiles/r01_gemm_sweep.txt), same process A/B: every one of
+  // these GEMMs is bound by operand bytes pulled from L2 (~8 TB/s chip-wide), so the pair tile
+  // (2/3 of the operand bytes per MAC) wins wherever the main loop dominates; with short K the
+  // two CTAs' heavy epilogues gate each other's next tile and the single-CTA kernel stays ahead
+  bool pair = false;
+  switch (epi) {
+    case EPI_STORE_F32:     pair = true; break;
+    case EPI_STORE_BF16:
+    case EPI_BIAS_RESIDUAL: pair = a.K >= 1024 || (a.K >= 512 && a.N >= 1024); break;
+    case EPI_BIAS_GELU:     pair = a.K >= 512; break;
+    case EPI_GELU_GRAD:     pair = a.K >= 1024; break;
+    default: break;
+  }
+  pair = pair && !no_pair && a.M > BM && nsm >= 2;
+  if (g_tune.pair >= 0) pair = g_tune.pair != 0 && a.M > BM && nsm >= 2;
   const int tile_m = pair ? 2 * BM : BM;
   const int units = pair ? nsm / 2 : nsm;
 
@@ -680,8 +706,13 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
     const double c256 = tile_cost(a.M, a.N, 256, tile_m, units, &w256);
     const double c128 = tile_cost(a.M, a.N, 128, tile_m, units, &w128);
     // split-K weight gradients are one long main loop per item: the wide tile always wins there
-    const bool wide = (epi == EPI_STORE_F32) ? (a.N > 128) : !(a.N <= 128 || c128 < c256);
-    if (wide) { BN = 256; workers = w256; } else { BN = 128; workers = w128; }
+    const bool wide = (epi == EPI_STORE_F32) ? (a.N > 128) : !(a.N <= 128 || c128 < 0.95 * c256);
+    bool use256 = wide;
+    // fc1 of the first stage (K = 128: two k-blocks per tile): the narrow tile's shorter epilogue
+    // turns around faster (measured 172 vs 188 us)
+    if (epi == EPI_BIAS_GELU && a.K <= 128 && a.N > 128) use256 = false;
+    if (g_tune.bn == 128 || g_tune.bn == 256) use256 = g_tune.bn == 256;
+    if (use256) { BN = 256; workers = w256; } else { BN = 128; workers = w128; }
   }
   p.tiles_m = (a.M + tile_m - 1) / tile_m;
   p.tiles_n = (a.N + BN - 1) / BN;
@@ -702,6 +733,7 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
       if (best < 0 || cost < best) { best = cost; splits = eff; }
     }
   }
+  if (epi == EPI_STORE_F32 && g_tune.splits >= 1) splits = g_tune.splits < nkb ? g_tune.splits : nkb;
   int kbps = (nkb + splits - 1) / splits;
   splits = (nkb + kbps - 1) / kbps;             // no empty split
   // D0 += acc in every case (the header's contract): callers may accumulate several launches

@@ -70,7 +70,12 @@ int cnx_check_device(void);
 /* Debug: 1 if a kernel gave up waiting on an mbarrier since the last call (then that launch's
  * results are garbage), 0 otherwise; clears the flag.  Call after synchronising the stream. */
 int cnx_debug_timeout_flag(void);
-/* Scratch bytes an op needs for the given problem (currently 0 for every op). */
+/* Debug / tuning: override the GEMM's tiling heuristics for the following calls (development tool
+ * behind tools/gemm_sweep.py; -1 = automatic).  stages: operand-ring depth actually used (<= the
+ * compiled depth); pair: 0/1 CTA-pair kernel; bn: 128/256 column tile; splits: split-K count of the
+ * fp32 reduction epilogue. */
+void cnx_debug_gemm_tuning(int stages, int pair, int bn, int splits);
+/* Scratch bytes an op needs for the given problem (B*H*W*C*2 for CNX_OP_DWCONV_LN_BWD, else 0). */
 size_t cnx_workspace_bytes(int op, int B, int H, int W, int C);
 
 /* Fold LN affine into fc1 and layer-scale into fc2, cast to bf16 in both orientations, and

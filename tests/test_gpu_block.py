@@ -147,6 +147,47 @@ def test_gemm_epilogues(cnx_lib):
     assert _rel(colsum, dz.double().sum(0)) < 1e-4      # sums of the rounded dz
 
 
+@pytest.mark.parametrize("tuning", [(2, 0, 256, -1), (-1, 0, 128, -1), (-1, 1, 256, -1), (3, 1, 128, 3),
+                                    (2, 1, 256, 5)])
+def test_gemm_forced_tilings(cnx_lib, tuning):
+    """Every kernel instantiation (single CTA / CTA pair, 128- and 256-wide tiles, shallow operand
+    ring, forced split-K) gives the same results: ragged M, N and K, several tiles per CTA."""
+    from image_classification_b200 import ops, _lib
+    dev = _dev()
+    torch.manual_seed(11)
+    M, N, K = 1000, 520, 200
+    A = (torch.randn(M, K, device=dev) * 0.3).bfloat16()
+    Bm = (torch.randn(N, K, device=dev) * 0.3).bfloat16()
+    bias = torch.randn(N, device=dev)
+    R = torch.randn(M, N, device=dev).bfloat16()
+    acc = A.double() @ Bm.double().t()
+    lib = _lib.load()
+    lib.cnx_debug_gemm_tuning(*tuning)
+    try:
+        D = ops.gemm_bf16(A, Bm)
+        z, h = ops.gemm_bf16(A, Bm, epilogue=ops.EPI_BIAS_GELU, bias=bias)
+        y = ops.gemm_bf16(A, Bm, epilogue=ops.EPI_BIAS_RESIDUAL, bias=bias, R=R)
+        colsum = torch.zeros(N, device=dev)
+        dz = ops.gemm_bf16(A, Bm, epilogue=ops.EPI_GELU_GRAD, R=R, colsum=colsum)
+        D32 = ops.gemm_bf16(A, Bm, epilogue=ops.EPI_STORE_F32)
+        Dw = ops.gemm_bf16(A.t().contiguous(), Bm.t().contiguous(), a_mn_major=True,
+                           b_mn_major=True, epilogue=ops.EPI_STORE_F32)
+        torch.cuda.synchronize()
+    finally:
+        lib.cnx_debug_gemm_tuning(-1, -1, -1, -1)
+    assert lib.cnx_debug_timeout_flag() == 0
+    assert _rel(D, acc) < BF16_REL
+    assert _rel(z, acc + bias.double()) < BF16_REL
+    assert _rel(h, F.gelu(z.double())) < BF16_REL
+    assert _rel(y, acc + bias.double() + R.double()) < BF16_REL
+    Rd = R.double().requires_grad_()
+    F.gelu(Rd).sum().backward()
+    assert _rel(dz, acc * Rd.grad) < BF16_REL
+    assert _rel(colsum, dz.double().sum(0)) < 1e-4
+    assert _rel(D32, acc) < 1e-4
+    assert _rel(Dw, acc) < 1e-4
+
+
 # ---------------------------------------------------------------------------- dwconv + LN bwd
 @pytest.mark.parametrize("shape", [(2, 7, 7, 64), (1, 14, 14, 128), (2, 9, 11, 96), (1, 12, 12, 256),
                                    (2, 14, 14, 512), (1, 7, 7, 1024), (1, 28, 28, 128),
