@@ -19,6 +19,7 @@ int* timeout_flag_ptr();             // device-visible mapped host int set by a 
 int read_and_clear_timeout_flag();   // host side; call after synchronising the stream
 int  check_device_sm100();           // CNX_OK or CNX_ERR_NOT_SM100 (cached per device)
 int  sm_count();
+bool pdl_enabled();                // false when CNX_NO_PDL is set (A/B switch)
 
 // Host-side TMA descriptor encoder (driver entry point fetched at run time so the
 // library links without libcuda).  dims/strides are innermost-first; strides in
@@ -28,6 +29,36 @@ int make_tensor_map(CUtensorMap* map, const void* base, int elem_bytes, int rank
                     const uint32_t* box, int swizzle);
 
 #ifdef __CUDACC__
+// Launch with an optional cluster width and, unless CNX_NO_PDL is set, programmatic stream
+// serialization (see pdl_wait() below): only for kernels that call pdl_wait() before their first
+// global-memory access.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), unsigned grid, unsigned block, size_t smem,
+                              cudaStream_t stream, unsigned cluster_x, Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  unsigned n = 0;
+  if (cluster_x > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = cluster_x;
+    attr[n].val.clusterDim.y = 1;
+    attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  if (pdl_enabled()) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // ------------------------------------------------------------------ small math
 __device__ __forceinline__ float2 bf16x2_to_f32x2(uint32_t v) {
   float2 r;
@@ -126,6 +157,18 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int* t
 // ------------------------------------------------------------------------ TMA
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
+}
+
+// Programmatic dependent launch: a kernel launched with launch_pdl() may be scheduled while the
+// previous kernel on the stream is still draining (its CTAs exit at different times, and a
+// persistent kernel leaves SMs idle during its tail).  Everything before pdl_wait() must not touch
+// global memory; pdl_wait() returns once every prerequisite grid has completed and its writes are
+// visible.  pdl_launch_dependents() lets the NEXT kernel start its own prologue early: call it
+// AFTER pdl_wait() (otherwise a chain of kernels cascades onto the SMs) and only from persistent
+// single-wave grids (a multi-wave grid would lose SM slots to the blocked CTAs of its successor).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m, uint64_t* bar,
                                             int c0, int c1) {

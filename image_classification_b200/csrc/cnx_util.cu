@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstring>
 #include <mutex>
+#include <stdlib.h>
 
 namespace cnx {
 
@@ -76,6 +77,11 @@ int check_device_sm100() {
     return CNX_ERR_NOT_SM100;
   }
   return CNX_OK;
+}
+
+bool pdl_enabled() {
+  static const bool on = getenv("CNX_NO_PDL") == nullptr;
+  return on;
 }
 
 int sm_count() {

@@ -102,6 +102,8 @@ dwconv7_fwd_kernel(const __grid_constant__ CUtensorMap x_map, const ConvParams p
     fence_mbar_init();
   }
   __syncthreads();
+  pdl_wait();                 // first global access (taps, TMA) comes after the previous kernel
+  pdl_launch_dependents();    // persistent single-wave grid: the next kernel may stage its prologue
 
   auto issue = [&](int item, int b) {
     const Item it = decode_item(p, item, TW);
@@ -219,6 +221,8 @@ dwconv7_bwd_kernel(const __grid_constant__ CUtensorMap dconv_map,
     mbar_init(&full_bar[1], 1);
     fence_mbar_init();
   }
+  pdl_wait();
+  pdl_launch_dependents();    // persistent single-wave grid: the next kernel may stage its prologue
   // taps of this slab -> shared memory (zero for channels past C)
   for (int i = tid; i < 49 * kWords; i += kThreads) {
     const int t = i >> 6, l = i & 63;
@@ -421,8 +425,7 @@ int launch_fwd(const void* x, ConvParams& p, int B, int H, int W, int C, cudaStr
     if (rc != CNX_OK) return rc;
     attr_set = true;
   }
-  dwconv7_fwd_kernel<TW><<<grid_size(p), kThreads, smem, stream>>>(map, p);
-  cudaError_t e = cudaGetLastError();
+  cudaError_t e = launch_pdl(dwconv7_fwd_kernel<TW>, grid_size(p), kThreads, smem, stream, 1u, map, p);
   if (e != cudaSuccess) {
     set_last_error("dwconv7_fwd launch: %s", cudaGetErrorString(e));
     return CNX_ERR_LAUNCH;
@@ -446,8 +449,8 @@ int launch_bwd(const void* dconv, const void* x, ConvParams& p, int B, int H, in
     if (rc != CNX_OK) return rc;
     attr_set = true;
   }
-  dwconv7_bwd_kernel<TW><<<grid_size(p), kThreads, smem, stream>>>(map_d, map_x, p);
-  cudaError_t e = cudaGetLastError();
+  cudaError_t e = launch_pdl(dwconv7_bwd_kernel<TW>, grid_size(p), kThreads, smem, stream, 1u, map_d,
+                             map_x, p);
   if (e != cudaSuccess) {
     set_last_error("dwconv7_bwd launch: %s", cudaGetErrorString(e));
     return CNX_ERR_LAUNCH;

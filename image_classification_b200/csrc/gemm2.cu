@@ -224,6 +224,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
   else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // the prologue above overlapped the previous kernel's tail; from here on global memory is touched
+  pdl_wait();
+  pdl_launch_dependents();    // persistent single-wave grid: the next kernel may stage its prologue
 
   if (warp == 0) {
     if (lane == 0) {
@@ -569,19 +572,8 @@ int launch2(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md0
     }
     attr_set = true;
   }
-  cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(kThreads);
-  cfg.dynamicSmemBytes = L::kTotal;
-  cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = PAIR ? 2 : 1;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm2_kernel<BN, EPI, PAIR>, ma, mb, md0, md1, mr, p);
+  cudaError_t e = launch_pdl(gemm2_kernel<BN, EPI, PAIR>, grid, kThreads, L::kTotal, stream,
+                             PAIR ? 2u : 1u, ma, mb, md0, md1, mr, p);
   if (e != cudaSuccess) {
     set_last_error("gemm_bf16 launch: %s", cudaGetErrorString(e));
     return CNX_ERR_LAUNCH;

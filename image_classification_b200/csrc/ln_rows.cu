@@ -55,6 +55,7 @@ template <int LPR, int NV>
 __global__ void __launch_bounds__(kRowThreads)
 ln_rows_fwd_kernel(__nv_bfloat16* __restrict__ u, float* __restrict__ mean_out,
                    float* __restrict__ rstd_out, int64_t M, int C, float eps) {
+  pdl_wait();                 // launched with launch_pdl: scheduled while the conv kernel drains
   const int lane_in_row = threadIdx.x % LPR;
   const int64_t row = static_cast<int64_t>(blockIdx.x) * (kRowThreads / LPR) + threadIdx.x / LPR;
   const bool row_ok = row < M;
@@ -111,6 +112,7 @@ __global__ void __launch_bounds__(kRowThreads)
 ln_rows_bwd_kernel(const __nv_bfloat16* __restrict__ dxhat, const __nv_bfloat16* __restrict__ xhat,
                    const float* __restrict__ rstd_in, __nv_bfloat16* __restrict__ dconv, int64_t M,
                    int C) {
+  pdl_wait();
   const int lane_in_row = threadIdx.x % LPR;
   const int64_t row = static_cast<int64_t>(blockIdx.x) * (kRowThreads / LPR) + threadIdx.x / LPR;
   const bool row_ok = row < M;
@@ -356,12 +358,24 @@ int launch_status(const char* who) {
     else KERNEL<32, 4><<<grid, kRowThreads, 0, stream>>>(__VA_ARGS__);                         \
   } while (0)
 
+// same, through launch_pdl (kernels that begin with pdl_wait())
+#define CNX_ROW_DISPATCH_PDL(KERNEL, ...)                                                      \
+  do {                                                                                         \
+    const unsigned grid = static_cast<unsigned>((M + (kRowThreads / cfg.lpr) - 1) /            \
+                                                (kRowThreads / cfg.lpr));                      \
+    if (cfg.lpr == 8) launch_pdl(KERNEL<8, 1>, grid, kRowThreads, 0, stream, 1u, __VA_ARGS__);  \
+    else if (cfg.lpr == 16) launch_pdl(KERNEL<16, 1>, grid, kRowThreads, 0, stream, 1u, __VA_ARGS__); \
+    else if (cfg.nv == 1) launch_pdl(KERNEL<32, 1>, grid, kRowThreads, 0, stream, 1u, __VA_ARGS__); \
+    else if (cfg.nv == 2) launch_pdl(KERNEL<32, 2>, grid, kRowThreads, 0, stream, 1u, __VA_ARGS__); \
+    else launch_pdl(KERNEL<32, 4>, grid, kRowThreads, 0, stream, 1u, __VA_ARGS__);              \
+  } while (0)
+
 int ln_rows_fwd(void* u_inout, float* mean, float* rstd, int64_t M, int C, float eps,
                 cudaStream_t stream) {
   RowCfg cfg;
   int rc = check_rows("ln_rows_fwd", M, C, &cfg);
   if (rc != CNX_OK) return rc;
-  CNX_ROW_DISPATCH(ln_rows_fwd_kernel, static_cast<__nv_bfloat16*>(u_inout), mean, rstd, M, C, eps);
+  CNX_ROW_DISPATCH_PDL(ln_rows_fwd_kernel, static_cast<__nv_bfloat16*>(u_inout), mean, rstd, M, C, eps);
   return launch_status("ln_rows_fwd");
 }
 
@@ -370,7 +384,7 @@ int ln_rows_bwd(const void* dxhat, const void* xhat, const float* rstd, void* dc
   RowCfg cfg;
   int rc = check_rows("ln_rows_bwd", M, C, &cfg);
   if (rc != CNX_OK) return rc;
-  CNX_ROW_DISPATCH(ln_rows_bwd_kernel, static_cast<const __nv_bfloat16*>(dxhat),
+  CNX_ROW_DISPATCH_PDL(ln_rows_bwd_kernel, static_cast<const __nv_bfloat16*>(dxhat),
                    static_cast<const __nv_bfloat16*>(xhat), rstd,
                    static_cast<__nv_bfloat16*>(dconv), M, C);
   return launch_status("ln_rows_bwd");

@@ -33,5 +33,5 @@ for n, us in win:
     a[0] += us; a[1] += 1
 tot = sum(a[0] for a in agg.values())
 print(f"window = launches [{lo},{hi}) of {len(rows)} captured: one optimizer step; total {tot:.1f} us over {len(win)} launches")
-for k, (us, n) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:40]:
+for k, (us, n) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:int(sys.argv[2]) if len(sys.argv) > 2 else 40]:
     print(f"{us:10.1f} us {100*us/tot:5.1f}% n={n:4d} avg={us/n:8.1f} us  {k}")
