@@ -21,7 +21,6 @@ SOURCES = [
     "cnx_api.cu",
     "dwconv7.cu",
     "ln_rows.cu",
-    "mlp_gemm.cu",
     "gemm2.cu",
     "elementwise.cu",
     "prep.cu",

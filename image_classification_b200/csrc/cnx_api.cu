@@ -137,8 +137,7 @@ int cnx_gemm_bf16(const void* A, int64_t lda, int a_mn_major, const void* B, int
   a.epilogue = epilogue;
   a.D0 = D0; a.ldd0 = ldd0; a.D1 = D1; a.ldd1 = ldd1;
   a.bias = bias; a.R = R; a.ldr = ldr; a.colsum = colsum;
-  static const bool use_v1 = getenv("CNX_GEMM_V1") != nullptr;   // A/B debugging switch
-  return use_v1 ? gemm_bf16_v1(a, as_stream(stream)) : gemm_bf16(a, as_stream(stream));
+  return gemm_bf16(a, as_stream(stream));
 }
 
 int cnx_fc1_gelu_fwd(const void* xhat, const void* w1f, const float* b1f, void* z, void* h, int M,

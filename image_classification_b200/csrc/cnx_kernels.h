@@ -51,7 +51,6 @@ struct GemmArgs {
 };
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream);      // gemm2.cu (persistent, warp-specialised)
 void gemm_debug_tuning(int stages, int pair, int bn, int splits);   // gemm2.cu, -1 = automatic
-int gemm_bf16_v1(const GemmArgs& a, cudaStream_t stream);   // mlp_gemm.cu (round-1 v1, A/B debugging only)
 
 // ---- elementwise.cu
 struct MixPlanEntry {          // one per sample; integers are bit-exact vs the reference RNG order
