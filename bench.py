@@ -191,6 +191,16 @@ def main_reference(args):
 # ---------------------------------------------------------------------------------------------
 # B200 arm
 # ---------------------------------------------------------------------------------------------
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture
+# (profiles/r01_ncu_gemm2_v6_summary.txt): mean over the six GEMM launches of one stage-3 block
+# (C=512, M=25088: fc1 173.5, fc2 141.4, dz 195.6, dxhat 113.4, wgrad 139.8 + 137.0 MB), the shape
+# 27 of the 36 blocks run.  Algorithmic operand+result bytes of the same six launches: 171 MB mean (part of the results is
+# still dirty in the 126 MB L2 when a kernel ends, so DRAM traffic can sit below that).
+NCU_TRAFFIC = {"mlp_gemm": 150.1e6}
+NCU_TRAFFIC_NOTE = ("bytes per launch, mean of the 6 GEMMs of a stage-3 block, ncu --set full "
+                    "(profiles/r01_ncu_gemm2_v6_summary.txt); algorithmic bytes of the same launches 171e6")
+
+
 class B200Trainer:
     """Everything one rank needs to run optimizer steps through the repo's public API."""
 
@@ -397,7 +407,8 @@ def main_b200(args):
     dom = max((n for n in kernels if "frac" in kernels[n]), key=lambda n: kernels[n]["ms_per_step"])
     roof = {"kernel": dom, "bound": kernels[dom]["bound"], "achieved": kernels[dom]["achieved"],
             "peak": kernels[dom]["peak"], "unit": kernels[dom]["unit"], "frac": kernels[dom]["frac"],
-            "traffic": None, "peak_source": pk["source"] +
+            "traffic": NCU_TRAFFIC.get(dom), "traffic_note": NCU_TRAFFIC_NOTE if dom in NCU_TRAFFIC else None,
+            "peak_source": pk["source"] +
             (" sustained bf16" if kernels[dom]["bound"] == "tensor" else " copy bandwidth"),
             "how": "sum of algorithmic work over this family's launches in one optimizer step / "
                    "sum of their CUDA-event durations (instrumented step after the timed region)"}

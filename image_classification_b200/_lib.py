@@ -50,6 +50,7 @@ SIGNATURES = {
     "cnx_check_device": (I, []),
     "cnx_debug_timeout_flag": (I, []),
     "cnx_debug_gemm_tuning": (None, [I, I, I, I]),
+    "cnx_debug_max_clusters": (I, [I]),
     "cnx_workspace_bytes": (c_size_t, [I, I, I, I, I]),
     "cnx_prep_block_weights": (I, [P] * 8 + [P] * 7 + [I, P]),
     "cnx_unfold_block_grads": (I, [P] * 11 + [P] * 7 + [I, P]),

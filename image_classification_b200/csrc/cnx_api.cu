@@ -33,6 +33,7 @@ const char* cnx_last_error_string(void) { return last_error(); }
 int cnx_check_device(void) { return check_device_sm100(); }
 
 int cnx_debug_timeout_flag(void) { return read_and_clear_timeout_flag(); }
+int cnx_debug_max_clusters(int cluster_size) { return gemm_debug_max_clusters(cluster_size); }
 void cnx_debug_gemm_tuning(int stages, int pair, int bn, int splits) {
   gemm_debug_tuning(stages, pair, bn, splits);
 }

@@ -50,6 +50,7 @@ struct GemmArgs {
   float* colsum;                // [N] fp32, atomically accumulated (EPI_GELU_GRAD), may be null
 };
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream);      // gemm2.cu (persistent, warp-specialised)
+int gemm_debug_max_clusters(int cluster_size);                      // gemm2.cu, occupancy probe
 void gemm_debug_tuning(int stages, int pair, int bn, int splits);   // gemm2.cu, -1 = automatic
 
 // ---- elementwise.cu

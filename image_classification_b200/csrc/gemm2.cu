@@ -620,6 +620,30 @@ double tile_cost(int M, int N, int BN, int tile_m, int units, int* workers_out) 
 
 }  // namespace
 
+int gemm_debug_max_clusters(int cluster_size) {
+  // how many clusters of `cluster_size` pair-kernel CTAs (full shared-memory footprint) the device
+  // can hold at once: GPC fragmentation shows up here (development probe)
+  using L = Cfg<256, true, true>;
+  auto kern = gemm2_kernel<256, EPI_STORE_BF16, true>;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
+  if (cluster_size > 8) cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(sm_count() / cluster_size * cluster_size);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = L::kTotal;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = cluster_size;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int n = -1;
+  cudaError_t e = cudaOccupancyMaxActiveClusters(&n, kern, &cfg);
+  if (e != cudaSuccess) { cudaGetLastError(); return -1; }
+  return n;
+}
+
 void gemm_debug_tuning(int stages, int pair, int bn, int splits) {
   g_tune.stages = stages; g_tune.pair = pair; g_tune.bn = bn; g_tune.splits = splits;
 }

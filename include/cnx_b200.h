@@ -75,6 +75,8 @@ int cnx_debug_timeout_flag(void);
  * compiled depth); pair: 0/1 CTA-pair kernel; bn: 128/256 column tile; splits: split-K count of the
  * fp32 reduction epilogue. */
 void cnx_debug_gemm_tuning(int stages, int pair, int bn, int splits);
+/* Debug: clusters of `cluster_size` GEMM CTAs the device can hold at once (occupancy probe). */
+int cnx_debug_max_clusters(int cluster_size);
 /* Scratch bytes an op needs for the given problem (B*H*W*C*2 for CNX_OP_DWCONV_LN_BWD, else 0). */
 size_t cnx_workspace_bytes(int op, int B, int H, int W, int C);
 
