@@ -225,8 +225,11 @@ class B200Trainer:
         self.reducer = ddp.BucketedGradReducer(self.params) if world > 1 else None
         cfg = train_step.StepConfig(gradient_accumulation_steps=ACCUM, gradient_clip_val=1.0,
                                     num_classes=NUM_CLASSES)
+        # CNX_NO_FUSED_OPTIM=1: torch's unscale_/clip/AdamW/update + EMAB200.update (A/B switch)
+        fused = False if os.environ.get("CNX_NO_FUSED_OPTIM") else None
         self.step_obj = train_step.TrainStep(self.model, self.criterion, self.opt, self.sched,
-                                             self.scaler, self.ema, cfg, self.reducer)
+                                             self.scaler, self.ema, cfg, self.reducer,
+                                             use_fused_optim=fused)
         g = torch.Generator().manual_seed(100 + rank)
         # synthetic "normalised pixels" (dataset.py:233-236) and hard labels, pinned on the host
         self.host_images = [torch.randn(micro_batch, 3, res, res, generator=g).pin_memory()
@@ -283,7 +286,7 @@ def timed_region(fn, steps, world, device):
 
 
 # per entry point: (family, bound, work(args) in bytes or flops) — SURVEY.md §8(d) accounting
-def _work_table():
+def _work_table(nparams=0):
     def dw_fwd(a):   # (x, wt, b, xhat, mean, rstd, B, H, W, C, eps, stream)
         return 2.0 * a[6] * a[7] * a[8] * a[9] * 2
     def dw_bwd(a):   # (dxhat, xhat, rstd, x, dy, wt, dx, dwt, dbias, dycs, B, H, W, C, ...)
@@ -299,6 +302,9 @@ def _work_table():
         "cnx_mlp_bwd_dz": ("mlp_gemm", "tensor", lambda a: mlp(a, 5, 6)),
         "cnx_mlp_bwd_dxhat": ("mlp_gemm", "tensor", lambda a: mlp(a, 3, 4)),
         "cnx_mlp_bwd_wgrad": ("mlp_gemm", "tensor", lambda a: mlp(a, 6, 7, 2.0)),
+        # optimizer step: 4 B/param (read g) + 36 B/param (read p,g,m,v,shadow; write p,m,v,shadow)
+        "cnx_optim_grad_norm": ("optim_step", "hbm", lambda a: 4.0 * nparams),
+        "cnx_optim_adamw_ema": ("optim_step", "hbm", lambda a: 36.0 * nparams),
     }
 
 
@@ -306,7 +312,7 @@ def profile_kernels(trainer, device):
     """One extra optimizer step with a CUDA-event pair around every library call (after the
     timed region, so the events do not perturb `value`).  -> {family: stats}, launches/step."""
     from image_classification_b200 import _lib
-    table = _work_table()
+    table = _work_table(sum(p.numel() for p in trainer.params))
     recs, open_ev = [], {}
 
     def hook(name, phase, args):

@@ -23,6 +23,7 @@ SOURCES = [
     "ln_rows.cu",
     "gemm2.cu",
     "elementwise.cu",
+    "optim.cu",
     "prep.cu",
     "layout.cu",
 ]

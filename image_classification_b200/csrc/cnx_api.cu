@@ -205,6 +205,32 @@ int cnx_ema_lerp_multi(const void* const* param_ptrs, void* const* shadow_ptrs,
 
 int cnx_ema_chunk_elems(void) { return kEmaChunkElems; }
 
+int cnx_optim_grad_norm(const void* const* grad_ptrs, const int64_t* numels,
+                        const int64_t* chunk_prefix, int num_tensors, int64_t total_chunks,
+                        const float* scale, float max_norm, float* partials, float* state,
+                        void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(grad_ptrs); CNX_REQUIRE_PTR(numels); CNX_REQUIRE_PTR(chunk_prefix);
+  CNX_REQUIRE_PTR(partials); CNX_REQUIRE_PTR(state);
+  return optim_grad_norm(grad_ptrs, numels, chunk_prefix, num_tensors, total_chunks, scale,
+                         max_norm, partials, state, as_stream(stream));
+}
+
+int cnx_optim_adamw_ema(void* const* param_ptrs, const void* const* grad_ptrs, void* const* m_ptrs,
+                        void* const* v_ptrs, void* const* shadow_ptrs, const int64_t* numels,
+                        const int64_t* chunk_prefix, int num_tensors, int64_t total_chunks,
+                        float lr, float beta1, float beta2, float eps, float weight_decay,
+                        float ema_one_minus_decay, float ema_decay, const float* state,
+                        void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(param_ptrs); CNX_REQUIRE_PTR(grad_ptrs); CNX_REQUIRE_PTR(m_ptrs);
+  CNX_REQUIRE_PTR(v_ptrs); CNX_REQUIRE_PTR(numels); CNX_REQUIRE_PTR(chunk_prefix);
+  CNX_REQUIRE_PTR(state);
+  return optim_adamw_ema(param_ptrs, grad_ptrs, m_ptrs, v_ptrs, shadow_ptrs, numels, chunk_prefix,
+                         num_tensors, total_chunks, lr, beta1, beta2, eps, weight_decay,
+                         ema_one_minus_decay, ema_decay, state, as_stream(stream));
+}
+
 int cnx_nchw_f32_to_nhwc_bf16(const float* src, void* dst, int B, int C, int H, int W,
                               void* stream) {
   CNX_REQUIRE_DEVICE();

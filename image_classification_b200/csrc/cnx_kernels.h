@@ -70,6 +70,18 @@ int ema_lerp_multi(const void* const* param_ptrs, void* const* shadow_ptrs,
                    int64_t total_chunks, float one_minus_decay, float decay, cudaStream_t stream);
 constexpr int kEmaChunkElems = 8192;
 
+// ---- optim.cu : unscale + clip-norm + AdamW + EMA over pointer tables
+int optim_grad_norm(const void* const* grad_ptrs, const int64_t* numels,
+                    const int64_t* chunk_prefix, int num_tensors, int64_t total_chunks,
+                    const float* scale, float max_norm, float* partials, float* state,
+                    cudaStream_t stream);
+int optim_adamw_ema(void* const* param_ptrs, const void* const* grad_ptrs, void* const* m_ptrs,
+                    void* const* v_ptrs, void* const* shadow_ptrs, const int64_t* numels,
+                    const int64_t* chunk_prefix, int num_tensors, int64_t total_chunks, float lr,
+                    float beta1, float beta2, float eps, float weight_decay,
+                    float ema_one_minus_decay, float ema_decay, const float* state,
+                    cudaStream_t stream);
+
 // ---- prep.cu : weight folding before the GEMMs and its adjoint after them
 int prep_block_weights(const float* dw_w, const float* ln_w, const float* ln_b, const float* fc1_w,
                        const float* fc1_b, const float* fc2_w, const float* fc2_b,

@@ -50,7 +50,8 @@ class TrainStep:
     every batch, exactly like the body of the reference's `for batch_idx, ...` loop."""
 
     def __init__(self, model, criterion, optimizer, scheduler=None, scaler=None, ema=None,
-                 cfg: StepConfig | None = None, grad_reducer=None, use_grad_window: bool = True):
+                 cfg: StepConfig | None = None, grad_reducer=None, use_grad_window: bool = True,
+                 use_fused_optim: bool | None = None):
         self.model, self.criterion, self.optimizer = model, criterion, optimizer
         self.scheduler, self.scaler, self.ema = scheduler, scaler, ema
         self.cfg = cfg or StepConfig()
@@ -59,6 +60,17 @@ class TrainStep:
         # with accumulation > 1 the B200 blocks keep folded-parameter gradients in one fp32 window
         # and run the fold adjoint once per optimizer step (block.GradWindow); GradScaler's scale is
         # constant inside a window (it only changes in scaler.update(), :230)
+        # lines :226-230 and :236-237 as two launches (optim_step.FusedOptimStep) whenever the
+        # optimizer is the reference's AdamW over CUDA fp32 parameters; otherwise torch's own calls
+        self.fused = None
+        if use_fused_optim is None:
+            use_fused_optim = (isinstance(optimizer, torch.optim.AdamW) and len(self.params) > 0 and
+                               all(p.is_cuda and p.dtype == torch.float32 for p in self.params) and
+                               not any(g.get("amsgrad") or g.get("maximize")
+                                       for g in optimizer.param_groups))
+        if use_fused_optim:
+            from .optim_step import FusedOptimStep
+            self.fused = FusedOptimStep(model, optimizer, scaler, ema, self.cfg.gradient_clip_val)
         self.window = None
         if self.cfg.gradient_accumulation_steps > 1 and use_grad_window:
             from .block import GradWindow
@@ -84,15 +96,18 @@ class TrainStep:
             if boundary:
                 if self.grad_reducer is not None:
                     self.grad_reducer.finish()
-                self.scaler.unscale_(self.optimizer)                           # :226
-                if cfg.gradient_clip_val > 0:
-                    torch.nn.utils.clip_grad_norm_(self.params, cfg.gradient_clip_val)   # :228
-                self.scaler.step(self.optimizer)                               # :229
-                self.scaler.update()                                           # :230
+                if self.fused is not None:
+                    self.fused.step()                                          # :226-230, :236-237
+                else:
+                    self.scaler.unscale_(self.optimizer)                       # :226
+                    if cfg.gradient_clip_val > 0:
+                        torch.nn.utils.clip_grad_norm_(self.params, cfg.gradient_clip_val)   # :228
+                    self.scaler.step(self.optimizer)                           # :229
+                    self.scaler.update()                                       # :230
                 self.optimizer.zero_grad()                                     # :231
                 if self.scheduler is not None:
                     self.scheduler.step()                                      # :233-234
-                if self.ema is not None:
+                if self.ema is not None and self.fused is None:
                     self.ema.update()                                          # :236-237
         else:
             outputs = self.model(images)
@@ -104,13 +119,16 @@ class TrainStep:
             if boundary:
                 if self.grad_reducer is not None:
                     self.grad_reducer.finish()
-                if cfg.gradient_clip_val > 0:
-                    torch.nn.utils.clip_grad_norm_(self.params, cfg.gradient_clip_val)
-                self.optimizer.step()
+                if self.fused is not None:
+                    self.fused.step()
+                else:
+                    if cfg.gradient_clip_val > 0:
+                        torch.nn.utils.clip_grad_norm_(self.params, cfg.gradient_clip_val)
+                    self.optimizer.step()
                 self.optimizer.zero_grad()
                 if self.scheduler is not None:
                     self.scheduler.step()
-                if self.ema is not None:
+                if self.ema is not None and self.fused is None:
                     self.ema.update()
         return loss.detach()
 

@@ -177,6 +177,29 @@ int cnx_ema_lerp_multi(const void* const* param_ptrs, void* const* shadow_ptrs,
                        int64_t total_chunks, float one_minus_decay, float decay, void* stream);
 int cnx_ema_chunk_elems(void);
 
+/* The optimizer step of the loop (/root/reference/train_advanced_v4.py:226-237) as two launches over
+ * device pointer tables (same chunking as cnx_ema_lerp_multi; fp32 tensors only).
+ * cnx_optim_grad_norm  = GradScaler.unscale_ (inf/nan check) + the norm of clip_grad_norm_:
+ *   reads every gradient once.  scale: device float (GradScaler's scale) or NULL (= 1);
+ *   partials: device float[total_chunks] scratch; state: device float[8], zero-initialised ONCE by
+ *   the caller and then owned by these two calls:
+ *     [0] total gradient norm (unscaled)   [1] gradient multiplier = clip_coef / scale
+ *     [2] found_inf (1.0 when any gradient is non-finite: the AdamW update is skipped)
+ *     [3] AdamW step count (incremented here unless found_inf)   [4] internal   [5] clip_coef
+ * cnx_optim_adamw_ema  = AdamW.step (torch.optim.AdamW arithmetic, one parameter group) with the
+ *   multiplier applied to the gradient on the fly, then EMA.update of the new parameter
+ *   (shadow_ptrs may be NULL: no EMA).  Must follow cnx_optim_grad_norm on the same stream. */
+int cnx_optim_grad_norm(const void* const* grad_ptrs, const int64_t* numels,
+                        const int64_t* chunk_prefix, int num_tensors, int64_t total_chunks,
+                        const float* scale, float max_norm, float* partials, float* state,
+                        void* stream);
+int cnx_optim_adamw_ema(void* const* param_ptrs, const void* const* grad_ptrs, void* const* m_ptrs,
+                        void* const* v_ptrs, void* const* shadow_ptrs, const int64_t* numels,
+                        const int64_t* chunk_prefix, int num_tensors, int64_t total_chunks,
+                        float lr, float beta1, float beta2, float eps, float weight_decay,
+                        float ema_one_minus_decay, float ema_decay, const float* state,
+                        void* stream);
+
 /* Module-boundary layout conversion (timm blocks are NCHW): [B,C,H,W] fp32 <-> [B,H,W,C] bf16. */
 int cnx_nchw_f32_to_nhwc_bf16(const float* src, void* dst, int B, int C, int H, int W, void* stream);
 int cnx_nhwc_bf16_to_nchw_f32(const void* src, float* dst, int B, int C, int H, int W, void* stream);

@@ -255,3 +255,109 @@ def test_layernorm2d_module_uses_library_and_matches_torch(cnx_lib):
     rel = lambda a, r: float((a.double() - r).abs().max() / r.abs().max())
     assert y.dtype == torch.bfloat16 and rel(y, yb.detach()) < 2e-2
     assert rel(xa.grad, xb.grad) < 2e-2
+
+
+# ------------------------------------------------------------------- fused optimizer step
+class _RefEMA:
+    """The reference's EMA.update expression (train_advanced_v4.py:75-80) in plain torch."""
+
+    def __init__(self, model, decay):
+        self.model, self.decay = model, decay
+        self.shadow = {n: p.data.clone() for n, p in model.named_parameters() if p.requires_grad}
+
+    def update(self):
+        for n, p in self.model.named_parameters():
+            if p.requires_grad:
+                self.shadow[n] = (1.0 - self.decay) * p.data + self.decay * self.shadow[n]
+
+
+class _Toy(torch.nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.body = torch.nn.Sequential(torch.nn.Conv2d(3, 16, 3), torch.nn.GELU(), torch.nn.Flatten(),
+                                        torch.nn.Linear(16 * 6 * 6, 37), torch.nn.Linear(37, 5))
+        self.unused = torch.nn.Linear(7, 3)      # never receives a gradient (the aux heads)
+
+    def forward(self, x):
+        return self.body(x)
+
+    def __getitem__(self, i):
+        return self.body[i]
+
+
+def _toy_model(dev, seed):
+    torch.manual_seed(seed)
+    m = _Toy().to(dev)
+    m[0].to(memory_format=torch.channels_last)              # a channels_last parameter
+    return m
+
+
+@pytest.mark.parametrize("use_scaler", [True, False])
+def test_fused_optim_step_matches_reference_sequence(cnx_lib, use_scaler):
+    """unscale_ + clip_grad_norm_ + AdamW.step + scaler.update + EMA.update (reference loop
+    :226-237) against FusedOptimStep on identical gradients, including a step with an inf gradient
+    (skipped update, halved scale) — 12 optimizer steps."""
+    from image_classification_b200 import ema as ema_mod
+    from image_classification_b200.optim_step import FusedOptimStep
+    dev = _dev()
+    ref, mine = _toy_model(dev, 3), _toy_model(dev, 3)
+    opt_r = torch.optim.AdamW(ref.parameters(), lr=3e-3, weight_decay=1e-2)
+    opt_m = torch.optim.AdamW(mine.parameters(), lr=3e-3, weight_decay=1e-2)
+    sc_r = torch.amp.GradScaler("cuda", init_scale=1024.0, growth_interval=4) if use_scaler else None
+    sc_m = torch.amp.GradScaler("cuda", init_scale=1024.0, growth_interval=4) if use_scaler else None
+    ema_r, ema_m = _RefEMA(ref, 0.97), ema_mod.EMAB200(mine, 0.97)
+    fused = FusedOptimStep(mine, opt_m, sc_m, ema_m, max_norm=0.05)      # small: clipping is active
+    sched_r = torch.optim.lr_scheduler.LambdaLR(opt_r, lambda s: 1.0 / (1 + s))
+    sched_m = torch.optim.lr_scheduler.LambdaLR(opt_m, lambda s: 1.0 / (1 + s))
+    gen = torch.Generator(device="cpu").manual_seed(0)
+    for step in range(12):
+        x = torch.randn(4, 3, 8, 8, generator=gen).to(dev)
+        y = torch.randn(4, 5, generator=gen).to(dev)
+        for model, sc in ((ref, sc_r), (mine, sc_m)):
+            loss = ((model(x) - y) ** 2).mean()
+            (sc.scale(loss) if sc is not None else loss).backward()
+        if step == 5:                       # overflow: both paths must skip and back off
+            for model in (ref, mine):
+                model[3].weight.grad[2, 3] = float("inf")
+        # reference order
+        if sc_r is not None:
+            sc_r.unscale_(opt_r)
+        norm_r = torch.nn.utils.clip_grad_norm_(ref.parameters(), 0.05)
+        if sc_r is not None:
+            sc_r.step(opt_r)
+            sc_r.update()
+        else:
+            if step != 5:
+                opt_r.step()                # (without a scaler the reference would take a NaN step)
+        opt_r.zero_grad()
+        sched_r.step()
+        ema_r.update()
+        # fused
+        fused.step()
+        opt_m.zero_grad()
+        sched_m.step()
+        if step != 5:
+            assert torch.allclose(fused.total_norm, norm_r, rtol=1e-5), (step, fused.total_norm, norm_r)
+        assert float(fused.found_inf) == (1.0 if step == 5 else 0.0)
+        if use_scaler:
+            assert sc_m.get_scale() == sc_r.get_scale(), step
+        for (n, pr), (_, pm) in zip(ref.named_parameters(), mine.named_parameters()):
+            assert torch.allclose(pm, pr, rtol=2e-5, atol=1e-7), (step, n, (pm - pr).abs().max())
+            assert torch.allclose(ema_m.shadow[n], ema_r.shadow[n], rtol=2e-5, atol=1e-7), (step, n)
+    # optimizer state stays torch-shaped: step count, moments
+    for pr, pm in zip(ref.parameters(), mine.parameters()):
+        if pr in opt_r.state:
+            assert float(opt_m.state[pm]["step"]) == float(opt_r.state[pr]["step"]) == 11.0
+            assert torch.allclose(opt_m.state[pm]["exp_avg"], opt_r.state[pr]["exp_avg"], rtol=1e-4, atol=1e-8)
+            assert torch.allclose(opt_m.state[pm]["exp_avg_sq"], opt_r.state[pr]["exp_avg_sq"], rtol=1e-4, atol=1e-10)
+    opt_m.state_dict()                      # still serialisable
+
+
+def test_fused_optim_step_rejects_unsupported(cnx_lib):
+    from image_classification_b200 import _lib
+    from image_classification_b200.optim_step import FusedOptimStep
+    m = _toy_model(_dev(), 0)
+    with pytest.raises(_lib.CnxError):
+        FusedOptimStep(m, torch.optim.SGD(m.parameters(), lr=0.1))
+    with pytest.raises(_lib.CnxError):
+        FusedOptimStep(m, torch.optim.AdamW(m.parameters(), amsgrad=True))
