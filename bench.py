@@ -432,7 +432,9 @@ def main_b200(args):
         "data": "synthetic",
         "config": {"workload": f"ConvNeXt-Base 44-class {args.res}x{args.res} bf16 AMP training "
                                f"step, micro-batch {args.micro_batch} x accumulation {ACCUM} per "
-                               "GPU (BASELINE config 2; config 3 layout for N>1)",
+                               "GPU " + ("(BASELINE config 2; config 3 layout for N>1)"
+                                         if args.res == 224 else "(BASELINE config 4 shape)"
+                                         if args.res == 384 else "(non-BASELINE shape)"),
                    "global_batch": imgs_per_step, "micro_batch_per_gpu": args.micro_batch,
                    "accumulation": ACCUM, "parallelism": f"dp{world}",
                    "step": "mixup/cutmix + fwd + soft-CE + bwd (x2) + unscale + clip 1.0 + "
