@@ -64,13 +64,60 @@ class LayerNorm2d(nn.LayerNorm):
         return y.to(x.dtype).permute(0, 3, 1, 2)
 
 
+class _PatchConvFn(torch.autograd.Function):
+    """conv2d(kernel = stride, no padding) + bias on bf16 channels_last activations.  Forward and
+    the input / weight gradients are cuDNN's; the bias gradient (sum of grad_output over batch and
+    space, which PyTorch computes with a slow strided reduction over NHWC: 73 us per layer measured)
+    is one cnx_colsum_bf16 launch."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, stride):
+        wq = weight.to(torch.bfloat16)          # what autocast would hand to conv2d
+        ctx.save_for_backward(x, wq)
+        ctx.stride = stride
+        ctx.w_like = weight.detach()
+        return F.conv2d(x, wq, bias.to(torch.bfloat16), stride=stride)
+
+    @staticmethod
+    def backward(ctx, g):
+        x, wq = ctx.saved_tensors
+        s = ctx.stride
+        if not g.is_contiguous(memory_format=torch.channels_last):
+            g = g.contiguous(memory_format=torch.channels_last)
+        dx, dw, _ = torch.ops.aten.convolution_backward(
+            g, x, wq, None, [s, s], [0, 0], [1, 1], False, [0, 0], 1,
+            [ctx.needs_input_grad[0], True, False])
+        B, C, H, W = g.shape
+        db = ops.colsum_bf16(g.permute(0, 2, 3, 1).reshape(B * H * W, C))
+        dw32 = torch.empty_like(ctx.w_like, dtype=torch.float32)     # the parameter's own layout
+        dw32.copy_(dw)
+        return dx, dw32, db, None
+
+
+class PatchConv2d(nn.Conv2d):
+    """The stem (4x4 stride 4) and downsample (2x2 stride 2) convolutions of timm's ConvNeXt:
+    an `nn.Conv2d` (same parameters, same state_dict keys) whose bf16 channels_last CUDA path takes
+    its bias gradient from libcnx_b200; any other input goes through `nn.Conv2d.forward`."""
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        k = self.kernel_size[0]
+        if (x.is_cuda and x.dim() == 4 and self.bias is not None and self.groups == 1
+                and self.kernel_size == (k, k) and self.stride == (k, k) and self.padding == (0, 0)
+                and self.dilation == (1, 1) and self.out_channels % 8 == 0
+                and self.out_channels <= 2048 and torch.is_autocast_enabled()
+                and torch.get_autocast_dtype("cuda") == torch.bfloat16
+                and x.is_contiguous(memory_format=torch.channels_last)):
+            return _PatchConvFn.apply(x.to(torch.bfloat16), self.weight, self.bias, k)
+        return super().forward(x)
+
+
 class ConvNeXtStage(nn.Module):
     def __init__(self, in_chs: int, out_chs: int, depth: int, stride: int, block_cls, ls_init_value):
         super().__init__()
         if in_chs != out_chs or stride > 1:
             self.downsample = nn.Sequential(
                 LayerNorm2d(in_chs, eps=1e-6),
-                nn.Conv2d(in_chs, out_chs, kernel_size=stride, stride=stride),
+                PatchConv2d(in_chs, out_chs, kernel_size=stride, stride=stride),
             )
         else:
             self.downsample = nn.Identity()
@@ -101,7 +148,7 @@ class ConvNeXtTimmLike(nn.Module):
                  in_chans: int = 3, ls_init_value: float = 1e-6, block_cls=ConvNeXtBlockB200):
         super().__init__()
         self.num_classes = num_classes
-        self.stem = nn.Sequential(nn.Conv2d(in_chans, dims[0], kernel_size=4, stride=4),
+        self.stem = nn.Sequential(PatchConv2d(in_chans, dims[0], kernel_size=4, stride=4),
                                   LayerNorm2d(dims[0], eps=1e-6))
         stages, prev = [], dims[0]
         for i, (d, c) in enumerate(zip(depths, dims)):

@@ -116,6 +116,12 @@ int cnx_layernorm_fwd(const void* x, const float* weight, const float* bias, voi
   return ln_affine_fwd(x, weight, bias, y, mean, rstd, M, C, eps, as_stream(stream));
 }
 
+int cnx_colsum_bf16(const void* x, float* out, int64_t M, int C, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(out);
+  return colsum_bf16(x, out, M, C, as_stream(stream));
+}
+
 int cnx_layernorm_bwd(const void* dy, const void* x, const float* weight, const float* mean,
                       const float* rstd, void* dx, float* dweight, float* dbias, int64_t M, int C,
                       void* stream) {

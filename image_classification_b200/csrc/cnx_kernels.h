@@ -24,6 +24,7 @@ int dwconv_bwd(const void* dconv, const void* x, const void* dy, const float* wt
 // ---- ln_rows.cu : LayerNorm with affine over [M, C] bf16 rows (stem / downsample LayerNorm2d)
 int ln_affine_fwd(const void* x, const float* w, const float* b, void* y, float* mean, float* rstd,
                   int64_t M, int C, float eps, cudaStream_t stream);
+int colsum_bf16(const void* x, float* out, int64_t M, int C, cudaStream_t stream);   // ln_rows.cu
 int ln_affine_bwd(const void* g, const void* x, const float* w, const float* mean,
                   const float* rstd, void* dx, float* dw, float* db, int64_t M, int C,
                   cudaStream_t stream);

@@ -336,6 +336,36 @@ int check_rows(const char* who, int64_t M, int C, RowCfg* cfg) {
   return CNX_OK;
 }
 
+// Column sums of an [M, C] bf16 matrix (the bias gradient of the stem / downsample convolutions:
+// sum of grad_output over batch and space).  A thread owns one 8-channel vector of the row and
+// walks rows; lanes of different rows meet in shared memory, one atomic per channel per CTA.
+constexpr int kColsumThreads = 256;
+__global__ void __launch_bounds__(kColsumThreads)
+colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, int64_t M, int C,
+                   int rows_per_cta) {
+  extern __shared__ float s_cs[];                       // [C]
+  const int nvec = C >> 3;
+  const int rows_in_flight = kColsumThreads / nvec;     // host guarantees nvec <= 256
+  const int v = threadIdx.x % nvec, rl = threadIdx.x / nvec;
+  for (int i = threadIdx.x; i < C; i += kColsumThreads) s_cs[i] = 0.f;
+  __syncthreads();
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  const int64_t r0 = static_cast<int64_t>(blockIdx.x) * rows_per_cta;
+  const int64_t r1 = min(r0 + rows_per_cta, M);
+  if (rl < rows_in_flight) {
+    for (int64_t r = r0 + rl; r < r1; r += rows_in_flight) {
+      float f[8];
+      unpack8(ld_v4(x + r * C + v * 8), f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += f[k];
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) atomicAdd(&s_cs[v * 8 + k], acc[k]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += kColsumThreads) atomicAdd(out + i, s_cs[i]);
+}
+
 int launch_status(const char* who) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
@@ -426,6 +456,22 @@ int ln_affine_bwd(const void* g, const void* x, const float* w, const float* mea
   else CNX_LNB(32, 4);
 #undef CNX_LNB
   return launch_status("ln_affine_bwd");
+}
+
+int colsum_bf16(const void* x, float* out, int64_t M, int C, cudaStream_t stream) {
+  if (M <= 0 || C <= 0 || (C % 8) != 0 || C > 2048) {
+    set_last_error("colsum_bf16: bad shape M=%lld C=%d (C must be a multiple of 8, <= 2048)",
+                   (long long)M, C);
+    return CNX_ERR_BAD_SHAPE;
+  }
+  cudaMemsetAsync(out, 0, sizeof(float) * C, stream);
+  const int rows_in_flight = kColsumThreads / (C >> 3);
+  int64_t rpc = (M + 8 * sm_count() - 1) / (8 * sm_count());     // ~8 CTAs per SM
+  rpc = (rpc + rows_in_flight - 1) / rows_in_flight * rows_in_flight;
+  const unsigned grid = static_cast<unsigned>((M + rpc - 1) / rpc);
+  colsum_bf16_kernel<<<grid, kColsumThreads, sizeof(float) * C, stream>>>(
+      static_cast<const __nv_bfloat16*>(x), out, M, C, static_cast<int>(rpc));
+  return launch_status("colsum_bf16");
 }
 
 }  // namespace cnx

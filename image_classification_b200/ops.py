@@ -154,6 +154,15 @@ def layernorm_bwd(dy2d, x2d, weight, mean, rstd):
     return dx, dw, db
 
 
+def colsum_bf16(x2d: torch.Tensor) -> torch.Tensor:
+    """[M, C] bf16 -> [C] fp32 column sums."""
+    _chk(x2d, torch.bfloat16, "x")
+    M, C = x2d.shape
+    out = torch.empty(C, device=x2d.device, dtype=torch.float32)
+    _lib.call("cnx_colsum_bf16", _p(x2d), _p(out), M, C, _stream(x2d))
+    return out
+
+
 # ------------------------------------------------------------------ MLP GEMMs
 EPI_STORE_BF16, EPI_BIAS_GELU, EPI_BIAS_RESIDUAL, EPI_GELU_GRAD, EPI_STORE_F32 = range(5)
 

@@ -132,6 +132,9 @@ int cnx_layernorm_fwd(const void* x, const float* weight, const float* bias, voi
 int cnx_layernorm_bwd(const void* dy, const void* x, const float* weight, const float* mean,
                       const float* rstd, void* dx, float* dweight, float* dbias, int64_t M, int C,
                       void* stream);
+/* out[c] = sum_m x[m,c] for a bf16 [M,C] matrix (fp32 result, overwritten): the bias gradient of the
+ * stem / downsample convolutions (sum of grad_output over batch and space in NHWC). */
+int cnx_colsum_bf16(const void* x, float* out, int64_t M, int C, void* stream);
 
 /* Generic tensor-core GEMM: D[M,N] = epilogue(A[M,K] * B[N,K]^T), bf16 in, fp32 accumulate.
  * a_mn_major / b_mn_major != 0: the operand is stored [K, rows] (row-major) instead. */

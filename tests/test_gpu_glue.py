@@ -361,3 +361,35 @@ def test_fused_optim_step_rejects_unsupported(cnx_lib):
         FusedOptimStep(m, torch.optim.SGD(m.parameters(), lr=0.1))
     with pytest.raises(_lib.CnxError):
         FusedOptimStep(m, torch.optim.AdamW(m.parameters(), amsgrad=True))
+
+
+# ----------------------------------------------------------------- stem / downsample conv
+@pytest.mark.parametrize("cfg", [(3, 128, 4, 32), (128, 256, 2, 28), (512, 1024, 2, 14)])
+def test_patch_conv_bias_grad_from_library(cnx_lib, cfg):
+    """PatchConv2d (cuDNN conv + cnx_colsum_bf16 bias gradient) vs nn.Conv2d under the same
+    autocast; column sums also against fp64."""
+    from image_classification_b200 import ops
+    from image_classification_b200.convnext import PatchConv2d
+    cin, cout, k, hw = cfg
+    dev = _dev()
+    torch.manual_seed(cin + cout)
+    mine = PatchConv2d(cin, cout, kernel_size=k, stride=k).to(dev).to(memory_format=torch.channels_last)
+    ref = torch.nn.Conv2d(cin, cout, kernel_size=k, stride=k).to(dev).to(memory_format=torch.channels_last)
+    ref.load_state_dict(mine.state_dict())
+    x = torch.randn(4, cin, hw, hw, device=dev).contiguous(memory_format=torch.channels_last)
+    xm, xr = x.clone().requires_grad_(), x.clone().requires_grad_()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        ym, yr = mine(xm), ref(xr)
+    assert ym.dtype == torch.bfloat16 and torch.equal(ym, yr)
+    g = torch.randn_like(ym)
+    ym.backward(g)
+    yr.backward(g)
+    assert mine.weight.grad.stride() == mine.weight.stride()
+    assert torch.allclose(mine.weight.grad, ref.weight.grad, rtol=2e-2, atol=1e-3)
+    assert torch.allclose(xm.grad, xr.grad, rtol=2e-2, atol=1e-3)
+    exact = g.double().sum((0, 2, 3))
+    assert float((mine.bias.grad.double() - exact).abs().max() / exact.abs().max()) < 1e-5
+    # the kernel alone, ragged channel count
+    t = torch.randn(1000, 96, device=dev).bfloat16()
+    cs = ops.colsum_bf16(t)
+    assert float((cs.double() - t.double().sum(0)).abs().max()) < 1e-3
