@@ -8,7 +8,8 @@ One "step" = one optimizer step of the reference loop (/root/reference/train_adv
 ConvNeXt-Base forward (36 libcnx_b200 blocks) -> label-smoothed soft-target CE -> backward; then
 unscale / clip 1.0 / AdamW / scheduler / EMA.  `value` = images all ranks processed / max-over-
 ranks device time with the raw batch already in HBM; `e2e` = same loop fed from pinned host
-buffers through the public API (H2D copy of every micro-batch and a D2H read of the loss inside
+buffers through the public API (`prefetch.DevicePrefetcher`: H2D copy of every micro-batch on a
+second stream, one batch ahead; D2H read of every step's loss through pinned memory — all inside
 the timed region).  Weak scaling: per-GPU work is fixed, global batch = 256 * N.
 
 `--impl reference` times the reference's CPU PyTorch path for the same metric (oracle port of the
@@ -253,13 +254,26 @@ class B200Trainer:
             loss = self._micro(self.dev_images[i], self.dev_labels[i])
         return loss
 
-    def step_e2e(self) -> float:
-        """pinned host -> device every micro-batch, loss read back to the host every step"""
-        for i in range(ACCUM):
-            images = self.host_images[i].to(self.device, non_blocking=True)
-            labels = self.host_labels[i].to(self.device, non_blocking=True)
+    def run_e2e(self, steps: int) -> list[float]:
+        """`steps` optimizer steps fed from pinned host memory through the package's input
+        pipeline: the H2D copy of every micro-batch (second stream, one batch ahead) and a D2H read
+        of every step's loss (pinned slot, read one step later) are all inside the caller's timed
+        region; returns the losses."""
+        from image_classification_b200.prefetch import AsyncScalarReader, DevicePrefetcher
+
+        def host_batches():
+            for _ in range(steps):
+                for i in range(ACCUM):
+                    yield self.host_images[i], self.host_labels[i]
+
+        reader = AsyncScalarReader(self.device)
+        losses = []
+        for j, (images, labels) in enumerate(DevicePrefetcher(host_batches(), self.device)):
             loss = self._micro(images, labels)
-        return float(loss.item())
+            if (j + 1) % ACCUM == 0:
+                losses += reader.push(loss)
+        losses += reader.drain()
+        return losses
 
     @property
     def h2d_bytes_per_step(self):
@@ -382,9 +396,10 @@ def main_b200(args):
 
     e2e = None
     if not args.no_e2e:
-        for _ in range(2):
-            tr.step_e2e()
-        ms_e2e = timed_region(tr.step_e2e, args.steps, world, device)
+        tr.run_e2e(2)
+        e2e_losses = []
+        ms_e2e = timed_region(lambda: e2e_losses.extend(tr.run_e2e(args.steps)), 1, world, device)
+        assert len(e2e_losses) == args.steps and all(l == l for l in e2e_losses), e2e_losses
         e2e = {"value": round(imgs_per_step * args.steps / (ms_e2e * 1e-3), 2), "unit": UNIT,
                "h2d_bytes_per_step": tr.h2d_bytes_per_step, "d2h_bytes_per_step": 4,
                "ms_per_step": round(ms_e2e / args.steps, 3)}

@@ -393,3 +393,25 @@ def test_patch_conv_bias_grad_from_library(cnx_lib, cfg):
     t = torch.randn(1000, 96, device=dev).bfloat16()
     cs = ops.colsum_bf16(t)
     assert float((cs.double() - t.double().sum(0)).abs().max()) < 1e-3
+
+
+# ------------------------------------------------------------------------- input pipeline
+def test_device_prefetcher_and_async_scalar_reader(cnx_lib):
+    from image_classification_b200.prefetch import AsyncScalarReader, DevicePrefetcher
+    dev = _dev()
+    gen = torch.Generator().manual_seed(0)
+    host = [(torch.randn(8, 3, 32, 32, generator=gen).pin_memory(),
+             torch.randint(0, 44, (8,), generator=gen).pin_memory()) for _ in range(5)]
+    reader = AsyncScalarReader(dev, depth=2)
+    got, seen = [], 0
+    for i, (x, y) in enumerate(DevicePrefetcher(iter(host), dev)):
+        assert x.is_cuda and y.is_cuda
+        # a long kernel chain on the compute stream while the next copy is in flight
+        z = x
+        for _ in range(20):
+            z = z * 1.0001
+        assert torch.equal(x.cpu(), host[i][0]) and torch.equal(y.cpu(), host[i][1])
+        got += reader.push(z.sum() * 0 + float(i))
+        seen += 1
+    got += reader.drain()
+    assert seen == 5 and got == [0.0, 1.0, 2.0, 3.0, 4.0]
