@@ -243,7 +243,6 @@ class B200Trainer:
 
     def _micro(self, images, labels):
         mixed, targets = self.mixer(images, labels, rng=self.rng)
-        mixed = mixed.contiguous(memory_format=torch.channels_last)
         loss = self.step_obj.micro_step(mixed, targets, self.batch_idx)
         self.batch_idx += 1
         return loss

@@ -60,6 +60,9 @@ SIGNATURES = {
     "cnx_layernorm_fwd": (I, [P, P, P, P, P, P, I64, I, F, P]),
     "cnx_layernorm_bwd": (I, [P, P, P, P, P, P, P, P, I64, I, P]),
     "cnx_colsum_bf16": (I, [P, P, I64, I, P]),
+    "cnx_layernorm_patch_fwd": (I, [P, P, P, P, P, P, I, I, I, I, I, F, P]),
+    "cnx_layernorm_patch_bwd": (I, [P, P, P, P, P, P, P, P, I, I, I, I, I, P]),
+    "cnx_patchify_nchw_f32": (I, [P, P, I, I, I, I, I, P]),
     "cnx_gemm_bf16": (I, [P, I64, I, P, I64, I, I, I, I, I, P, I64, P, I64, P, P, I64, P, P]),
     "cnx_fc1_gelu_fwd": (I, [P, P, P, P, P, I, I, P]),
     "cnx_fc2_residual_fwd": (I, [P, P, P, P, P, I, I, P]),
@@ -111,7 +114,7 @@ def check(rc: int, what: str) -> None:
 # cudaMemsetAsync nodes are not counted)
 LAUNCHES_PER_CALL = {
     "cnx_prep_block_weights": 4, "cnx_unfold_block_grads": 3, "cnx_dwconv_ln_fwd": 2,
-    "cnx_dwconv_ln_bwd": 2, "cnx_dwconv_ln_bwd_acc": 2, "cnx_gemm_bf16": 1, "cnx_layernorm_fwd": 1, "cnx_layernorm_bwd": 1, "cnx_colsum_bf16": 1, "cnx_fc1_gelu_fwd": 1, "cnx_fc2_residual_fwd": 1,
+    "cnx_dwconv_ln_bwd": 2, "cnx_dwconv_ln_bwd_acc": 2, "cnx_gemm_bf16": 1, "cnx_layernorm_fwd": 1, "cnx_layernorm_bwd": 1, "cnx_colsum_bf16": 1, "cnx_layernorm_patch_fwd": 1, "cnx_layernorm_patch_bwd": 1, "cnx_patchify_nchw_f32": 1, "cnx_fc1_gelu_fwd": 1, "cnx_fc2_residual_fwd": 1,
     "cnx_mlp_bwd_dz": 1, "cnx_mlp_bwd_dxhat": 1, "cnx_mlp_bwd_wgrad": 2, "cnx_mix_batch": 1,
     "cnx_softce_fwd_bwd": 1, "cnx_ema_lerp_multi": 1, "cnx_optim_grad_norm": 1, "cnx_optim_adamw_ema": 1, "cnx_nchw_f32_to_nhwc_bf16": 1,
     "cnx_nhwc_bf16_to_nchw_f32": 1,

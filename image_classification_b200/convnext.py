@@ -111,11 +111,116 @@ class PatchConv2d(nn.Conv2d):
         return super().forward(x)
 
 
+def _w2d(weight: torch.Tensor) -> torch.Tensor:
+    """conv weight [Cout, Cin, k, k] -> [Cout, k*k*Cin] bf16 with inner order (kh, kw, c): a view
+    + cast when the parameter is channels_last (what `create_convnext(...).to(channels_last)` and
+    bench.py use), one small permute copy otherwise."""
+    return weight.detach().permute(0, 2, 3, 1).reshape(weight.shape[0], -1).to(torch.bfloat16)
+
+
+def _dw4d(dw2d: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+    """[Cout, k*k*Cin] fp32 gradient -> a tensor shaped and laid out like `weight`."""
+    Cout, Cin, k, _ = weight.shape
+    g = dw2d.view(Cout, k, k, Cin).permute(0, 3, 1, 2)
+    if g.stride() != weight.stride():
+        out = torch.empty_like(weight, dtype=torch.float32)
+        out.copy_(g)
+        return out
+    return g
+
+
+def _autocast_bf16() -> bool:
+    return torch.is_autocast_enabled() and torch.get_autocast_dtype("cuda") == torch.bfloat16
+
+
+class _PatchGemmFn(torch.autograd.Function):
+    """k x k stride-k convolution + bias on a patch-major operand P [M, k*k*Cin] bf16 as GEMMs of
+    libcnx_b200: z = P W^T + b (EPI_BIAS), dW = g^T P (split-K fp32), db = colsum(g),
+    dP = g W (only when P needs a gradient)."""
+
+    @staticmethod
+    def forward(ctx, P, weight, bias):
+        wq = _w2d(weight)
+        ctx.save_for_backward(P, wq)
+        ctx.w_like = weight.detach()
+        return ops.gemm_bf16(P, wq, epilogue=ops.EPI_BIAS, bias=bias.detach().float())
+
+    @staticmethod
+    def backward(ctx, g):
+        P, wq = ctx.saved_tensors
+        g = g.contiguous()
+        dw = ops.gemm_bf16(g, P, a_mn_major=True, b_mn_major=True, epilogue=ops.EPI_STORE_F32)
+        db = ops.colsum_bf16(g)
+        dP = ops.gemm_bf16(g, wq, b_mn_major=True) if ctx.needs_input_grad[0] else None
+        return dP, _dw4d(dw, ctx.w_like), db
+
+
+class _LayerNormPatchFn(torch.autograd.Function):
+    """LayerNorm2d of x [B,C,H,W] bf16 channels_last whose output is the patch-major operand of the
+    following k x k stride-k convolution ([B*H/k*W/k, k*k*C]); backward takes the patch-major
+    gradient the data-gradient GEMM produced."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, eps, patch):
+        xn = x.permute(0, 2, 3, 1)
+        y, mean, rstd = ops.layernorm_patch_fwd(xn, weight.detach(), bias.detach(), patch, eps)
+        ctx.save_for_backward(xn, weight, mean, rstd)
+        ctx.patch = patch
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        xn, weight, mean, rstd = ctx.saved_tensors
+        dx, dw, db = ops.layernorm_patch_bwd(g.contiguous(), xn, weight.detach(), mean, rstd, ctx.patch)
+        return dx.permute(0, 3, 1, 2), dw, db, None, None
+
+
+class DownsampleB200(nn.Sequential):
+    """timm's stage `downsample` = Sequential(LayerNorm2d, Conv2d(k=2, s=2)) with the same children
+    and state_dict keys.  bf16 channels_last CUDA activations under bf16 autocast run as
+    cnx_layernorm_patch_fwd -> tcgen05 GEMM (+bias); anything else takes the children one by one."""
+
+    def forward(self, x):
+        norm, conv = self[0], self[1]
+        B, C, H, W = x.shape
+        k = conv.kernel_size[0]
+        if (x.is_cuda and x.dtype == torch.bfloat16 and _autocast_bf16() and C % 8 == 0 and C <= 1024
+                and conv.kernel_size == (k, k) and conv.stride == (k, k) and conv.padding == (0, 0)
+                and conv.groups == 1 and conv.bias is not None and H % k == 0 and W % k == 0
+                and conv.out_channels % 8 == 0 and x.permute(0, 2, 3, 1).is_contiguous()
+                and norm.weight.dtype == torch.float32):
+            yp = _LayerNormPatchFn.apply(x, norm.weight, norm.bias, norm.eps, k)
+            z = _PatchGemmFn.apply(yp, conv.weight, conv.bias)
+            return z.view(B, H // k, W // k, conv.out_channels).permute(0, 3, 1, 2)
+        return super().forward(x)
+
+
+class StemB200(nn.Sequential):
+    """timm's `stem` = Sequential(Conv2d(k=4, s=4), LayerNorm2d).  A contiguous fp32 NCHW CUDA batch
+    under bf16 autocast (what the loop feeds, /root/reference/train_advanced_v4.py:211-218) runs as
+    cnx_patchify_nchw_f32 -> tcgen05 GEMM (+bias) -> cnx_layernorm_fwd."""
+
+    def forward(self, x):
+        conv, norm = self[0], self[1]
+        k = conv.kernel_size[0]
+        if (x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and x.is_contiguous()
+                and _autocast_bf16() and not x.requires_grad
+                and conv.kernel_size == (k, k) and conv.stride == (k, k) and conv.padding == (0, 0)
+                and conv.groups == 1 and conv.bias is not None and x.shape[2] % k == 0
+                and x.shape[3] % k == 0 and (k * k * x.shape[1]) % 8 == 0
+                and conv.out_channels % 8 == 0):
+            B, _, H, W = x.shape
+            P = ops.patchify_nchw_f32(x, k)
+            z = _PatchGemmFn.apply(P, conv.weight, conv.bias)
+            return norm(z.view(B, H // k, W // k, conv.out_channels).permute(0, 3, 1, 2))
+        return super().forward(x)
+
+
 class ConvNeXtStage(nn.Module):
     def __init__(self, in_chs: int, out_chs: int, depth: int, stride: int, block_cls, ls_init_value):
         super().__init__()
         if in_chs != out_chs or stride > 1:
-            self.downsample = nn.Sequential(
+            self.downsample = DownsampleB200(
                 LayerNorm2d(in_chs, eps=1e-6),
                 PatchConv2d(in_chs, out_chs, kernel_size=stride, stride=stride),
             )
@@ -148,7 +253,7 @@ class ConvNeXtTimmLike(nn.Module):
                  in_chans: int = 3, ls_init_value: float = 1e-6, block_cls=ConvNeXtBlockB200):
         super().__init__()
         self.num_classes = num_classes
-        self.stem = nn.Sequential(PatchConv2d(in_chans, dims[0], kernel_size=4, stride=4),
+        self.stem = StemB200(PatchConv2d(in_chans, dims[0], kernel_size=4, stride=4),
                                   LayerNorm2d(dims[0], eps=1e-6))
         stages, prev = [], dims[0]
         for i, (d, c) in enumerate(zip(depths, dims)):

@@ -113,7 +113,34 @@ int cnx_layernorm_fwd(const void* x, const float* weight, const float* bias, voi
   CNX_REQUIRE_DEVICE();
   CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(weight); CNX_REQUIRE_PTR(bias); CNX_REQUIRE_PTR(y);
   CNX_REQUIRE_PTR(mean); CNX_REQUIRE_PTR(rstd);
-  return ln_affine_fwd(x, weight, bias, y, mean, rstd, M, C, eps, as_stream(stream));
+  return ln_affine_fwd(x, weight, bias, y, mean, rstd, M, C, eps, 0, 0, 0, as_stream(stream));
+}
+
+int cnx_layernorm_patch_fwd(const void* x, const float* weight, const float* bias, void* y_patch,
+                            float* mean, float* rstd, int B, int H, int W, int C, int patch,
+                            float eps, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(weight); CNX_REQUIRE_PTR(bias); CNX_REQUIRE_PTR(y_patch);
+  CNX_REQUIRE_PTR(mean); CNX_REQUIRE_PTR(rstd);
+  return ln_affine_fwd(x, weight, bias, y_patch, mean, rstd, static_cast<int64_t>(B) * H * W, C,
+                       eps, H, W, patch, as_stream(stream));
+}
+
+int cnx_layernorm_patch_bwd(const void* dy_patch, const void* x, const float* weight,
+                            const float* mean, const float* rstd, void* dx, float* dweight,
+                            float* dbias, int B, int H, int W, int C, int patch, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(dy_patch); CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(weight); CNX_REQUIRE_PTR(mean);
+  CNX_REQUIRE_PTR(rstd); CNX_REQUIRE_PTR(dx); CNX_REQUIRE_PTR(dweight); CNX_REQUIRE_PTR(dbias);
+  return ln_affine_bwd(dy_patch, x, weight, mean, rstd, dx, dweight, dbias,
+                       static_cast<int64_t>(B) * H * W, C, H, W, patch, as_stream(stream));
+}
+
+int cnx_patchify_nchw_f32(const float* x, void* P, int B, int Cin, int H, int W, int patch,
+                          void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(P);
+  return patchify_nchw_f32(x, P, B, Cin, H, W, patch, as_stream(stream));
 }
 
 int cnx_colsum_bf16(const void* x, float* out, int64_t M, int C, void* stream) {
@@ -128,7 +155,8 @@ int cnx_layernorm_bwd(const void* dy, const void* x, const float* weight, const 
   CNX_REQUIRE_DEVICE();
   CNX_REQUIRE_PTR(dy); CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(weight); CNX_REQUIRE_PTR(mean);
   CNX_REQUIRE_PTR(rstd); CNX_REQUIRE_PTR(dx); CNX_REQUIRE_PTR(dweight); CNX_REQUIRE_PTR(dbias);
-  return ln_affine_bwd(dy, x, weight, mean, rstd, dx, dweight, dbias, M, C, as_stream(stream));
+  return ln_affine_bwd(dy, x, weight, mean, rstd, dx, dweight, dbias, M, C, 0, 0, 0,
+                       as_stream(stream));
 }
 
 int cnx_gemm_bf16(const void* A, int64_t lda, int a_mn_major, const void* B, int64_t ldb,

@@ -23,11 +23,13 @@ int dwconv_bwd(const void* dconv, const void* x, const void* dy, const float* wt
 
 // ---- ln_rows.cu : LayerNorm with affine over [M, C] bf16 rows (stem / downsample LayerNorm2d)
 int ln_affine_fwd(const void* x, const float* w, const float* b, void* y, float* mean, float* rstd,
-                  int64_t M, int C, float eps, cudaStream_t stream);
+                  int64_t M, int C, float eps, int pH, int pW, int pk, cudaStream_t stream);
+int patchify_nchw_f32(const float* x, void* P, int B, int Cin, int H, int W, int k,
+                      cudaStream_t stream);   // layout.cu
 int colsum_bf16(const void* x, float* out, int64_t M, int C, cudaStream_t stream);   // ln_rows.cu
 int ln_affine_bwd(const void* g, const void* x, const float* w, const float* mean,
                   const float* rstd, void* dx, float* dw, float* db, int64_t M, int C,
-                  cudaStream_t stream);
+                  int pH, int pW, int pk, cudaStream_t stream);
 
 // ---- mlp_gemm.cu  (tcgen05 / TMEM / TMA)
 enum GemmEpilogue : int {
@@ -36,6 +38,7 @@ enum GemmEpilogue : int {
   EPI_BIAS_RESIDUAL = 2,    // D = acc + bias[n] + R[m,n]               (bf16 out, R bf16)
   EPI_GELU_GRAD = 3,        // D = acc * gelu'(Z[m,n]); colsum[n] += D  (bf16 out, Z bf16)
   EPI_STORE_F32 = 4,        // D = acc                                  (fp32 out; weight grads)
+  EPI_BIAS = 6,             // D = acc + bias[n]                        (bf16 out; 5 is internal)
 };
 struct GemmArgs {
   // D[M,N] = A[M,K] * B[N,K]^T.  a_mn_major / b_mn_major: operand stored as [K,M] / [K,N].

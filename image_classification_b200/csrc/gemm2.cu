@@ -447,7 +447,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
           for (int j = 0; j < 16; ++j)
             f[j] = make_float2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
 
-          if (EPI == EPI_BIAS_GELU || EPI == EPI_BIAS_RESIDUAL) {
+          if (EPI == EPI_BIAS_GELU || EPI == EPI_BIAS_RESIDUAL || EPI == EPI_BIAS) {
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
               if (n + j < p.N) {
@@ -587,6 +587,7 @@ int dispatch(int epi, const CUtensorMap& ma, const CUtensorMap& mb, const CUtens
              cudaStream_t stream) {
   switch (epi) {
     case EPI_STORE_BF16:    return launch2<BN, EPI_STORE_BF16, PAIR>(ma, mb, md0, md1, mr, p, grid, stream);
+    case EPI_BIAS:          return launch2<BN, EPI_BIAS, PAIR>(ma, mb, md0, md1, mr, p, grid, stream);
     case EPI_BIAS_GELU:     return launch2<BN, EPI_BIAS_GELU, PAIR>(ma, mb, md0, md1, mr, p, grid, stream);
     case EPI_BIAS_RESIDUAL: return launch2<BN, EPI_BIAS_RESIDUAL, PAIR>(ma, mb, md0, md1, mr, p, grid, stream);
     case EPI_GELU_GRAD:     return launch2<BN, EPI_GELU_GRAD, PAIR>(ma, mb, md0, md1, mr, p, grid, stream);
@@ -669,9 +670,9 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
     return CNX_ERR_BAD_SHAPE;
   }
   int epi = a.epilogue;
-  const bool need_bias = (epi == EPI_BIAS_GELU || epi == EPI_BIAS_RESIDUAL);
+  const bool need_bias = (epi == EPI_BIAS_GELU || epi == EPI_BIAS_RESIDUAL || epi == EPI_BIAS);
   const bool need_r = (epi == EPI_BIAS_RESIDUAL || epi == EPI_GELU_GRAD);
-  if (epi < 0 || epi > EPI_STORE_F32 || (need_bias && !a.bias) || (need_r && !a.R) ||
+  if (epi < 0 || (epi > EPI_STORE_F32 && epi != EPI_BIAS) || (need_bias && !a.bias) || (need_r && !a.R) ||
       (epi == EPI_BIAS_GELU && !a.D1)) {
     set_last_error("gemm_bf16: unsupported epilogue %d or missing operand", a.epilogue);
     return CNX_ERR_BAD_ARG;
@@ -705,6 +706,7 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   switch (epi) {
     case EPI_STORE_F32:     pair = true; break;
     case EPI_STORE_BF16:
+    case EPI_BIAS:
     case EPI_BIAS_RESIDUAL: pair = a.K >= 1024 || (a.K >= 512 && a.N >= 1024); break;
     case EPI_BIAS_GELU:     pair = a.K >= 512; break;
     case EPI_GELU_GRAD:     pair = a.K >= 1024; break;

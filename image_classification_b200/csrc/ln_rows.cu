@@ -156,17 +156,30 @@ ln_rows_bwd_kernel(const __nv_bfloat16* __restrict__ dxhat, const __nv_bfloat16*
 
 // ---- LayerNorm WITH affine over [M, C] bf16 rows (timm LayerNorm2d of the stem and of the stage
 // `downsample` modules): y = (x - mean) * rstd * w + b; mean / rstd saved.
+// Row of the "patch-major" matrix a k x k stride-k convolution consumes as a plain GEMM operand:
+// pixel (b, h, w) of an [B, H, W, C] tensor -> row ((b*H/k + h/k)*W/k + w/k)*k*k + (h%k)*k + w%k of
+// an [B*H*W, C] matrix, i.e. [B*H/k*W/k, k*k*C] holds one im2col row per output pixel.  pk <= 1: identity.
+__device__ __forceinline__ int64_t patch_row(int64_t m, int pH, int pW, int pk) {
+  if (pk <= 1) return m;
+  const int w = static_cast<int>(m % pW);
+  const int64_t t = m / pW;
+  const int h = static_cast<int>(t % pH);
+  const int64_t b = t / pH;
+  return ((b * (pH / pk) + h / pk) * (pW / pk) + w / pk) * (pk * pk) + (h % pk) * pk + (w % pk);
+}
+
 template <int LPR, int NV>
 __global__ void __launch_bounds__(kRowThreads)
 ln_affine_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
                      const float* __restrict__ b, __nv_bfloat16* __restrict__ y,
                      float* __restrict__ mean_out, float* __restrict__ rstd_out, int64_t M, int C,
-                     float eps) {
+                     float eps, int pH, int pW, int pk) {
   const int lane_in_row = threadIdx.x % LPR;
   const int64_t row = static_cast<int64_t>(blockIdx.x) * (kRowThreads / LPR) + threadIdx.x / LPR;
   const bool row_ok = row < M;
   const int nvec = C >> 3;
   const int64_t off = (row_ok ? row : 0) * C;
+  const int64_t yoff = patch_row(row_ok ? row : 0, pH, pW, pk) * C;     // output row (patch-major)
   float f[NV][8];
   float s = 0.f;
 #pragma unroll
@@ -210,7 +223,7 @@ ln_affine_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restric
       float o[8];
 #pragma unroll
       for (int k = 0; k < 8; ++k) o[k] = fmaf((f[i][k] - mean) * rstd, wv[k], bv[k]);
-      st_v4(y + off + v * 8, pack8(o));
+      st_v4(y + yoff + v * 8, pack8(o));
     }
   }
   if (lane_in_row == 0) {
@@ -228,7 +241,7 @@ ln_affine_bwd_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* _
                      const float* __restrict__ w, const float* __restrict__ mean_in,
                      const float* __restrict__ rstd_in, __nv_bfloat16* __restrict__ dx,
                      float* __restrict__ dw, float* __restrict__ db, int64_t M, int C,
-                     int rows_per_cta) {
+                     int rows_per_cta, int pH, int pW, int pk) {
   __shared__ float s_dw[1024];
   __shared__ float s_db[1024];
   for (int i = threadIdx.x; i < C; i += kRowThreads) {
@@ -257,6 +270,7 @@ ln_affine_bwd_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* _
     const int64_t row = row_begin + r;
     const bool row_ok = row < M;            // uniform across the lanes sharing the row
     const int64_t off = (row_ok ? row : 0) * C;
+    const int64_t goff = patch_row(row_ok ? row : 0, pH, pW, pk) * C;   // gradient row (patch-major)
     const float mu = row_ok ? mean_in[row] : 0.f;
     const float rs = row_ok ? rstd_in[row] : 0.f;
     float gw[NV][8], xh[NV][8];
@@ -266,7 +280,7 @@ ln_affine_bwd_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* _
       const int v = lane_in_row + i * LPR;
       if (row_ok && v < nvec) {
         float gg[8], xx[8];
-        unpack8(ld_v4(g + off + v * 8), gg);
+        unpack8(ld_v4(g + goff + v * 8), gg);
         unpack8(ld_v4(x + off + v * 8), xx);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
@@ -420,21 +434,35 @@ int ln_rows_bwd(const void* dxhat, const void* xhat, const float* rstd, void* dc
   return launch_status("ln_rows_bwd");
 }
 
+int check_patch(const char* who, int64_t M, int pH, int pW, int pk) {
+  if (pk <= 1) return CNX_OK;
+  if (pH <= 0 || pW <= 0 || (pH % pk) != 0 || (pW % pk) != 0 || (M % (static_cast<int64_t>(pH) * pW)) != 0) {
+    set_last_error("%s: patch size %d must divide H=%d and W=%d, and M=%lld must be B*H*W", who, pk,
+                   pH, pW, (long long)M);
+    return CNX_ERR_BAD_SHAPE;
+  }
+  return CNX_OK;
+}
+
 int ln_affine_fwd(const void* x, const float* w, const float* b, void* y, float* mean, float* rstd,
-                  int64_t M, int C, float eps, cudaStream_t stream) {
+                  int64_t M, int C, float eps, int pH, int pW, int pk, cudaStream_t stream) {
   RowCfg cfg;
   int rc = check_rows("ln_affine_fwd", M, C, &cfg);
   if (rc != CNX_OK) return rc;
+  rc = check_patch("ln_affine_fwd", M, pH, pW, pk);
+  if (rc != CNX_OK) return rc;
   CNX_ROW_DISPATCH(ln_affine_fwd_kernel, static_cast<const __nv_bfloat16*>(x), w, b,
-                   static_cast<__nv_bfloat16*>(y), mean, rstd, M, C, eps);
+                   static_cast<__nv_bfloat16*>(y), mean, rstd, M, C, eps, pH, pW, pk);
   return launch_status("ln_affine_fwd");
 }
 
 int ln_affine_bwd(const void* g, const void* x, const float* w, const float* mean,
                   const float* rstd, void* dx, float* dw, float* db, int64_t M, int C,
-                  cudaStream_t stream) {
+                  int pH, int pW, int pk, cudaStream_t stream) {
   RowCfg cfg;
   int rc = check_rows("ln_affine_bwd", M, C, &cfg);
+  if (rc != CNX_OK) return rc;
+  rc = check_patch("ln_affine_bwd", M, pH, pW, pk);
   if (rc != CNX_OK) return rc;
   cudaMemsetAsync(dw, 0, sizeof(float) * C, stream);
   cudaMemsetAsync(db, 0, sizeof(float) * C, stream);
@@ -448,7 +476,7 @@ int ln_affine_bwd(const void* g, const void* x, const float* w, const float* mea
 #define CNX_LNB(LPR_, NV_)                                                                      \
   ln_affine_bwd_kernel<LPR_, NV_><<<grid, kRowThreads, 0, stream>>>(                            \
       static_cast<const __nv_bfloat16*>(g), static_cast<const __nv_bfloat16*>(x), w, mean, rstd, \
-      static_cast<__nv_bfloat16*>(dx), dw, db, M, C, rows_per_cta)
+      static_cast<__nv_bfloat16*>(dx), dw, db, M, C, rows_per_cta, pH, pW, pk)
   if (cfg.lpr == 8) CNX_LNB(8, 1);
   else if (cfg.lpr == 16) CNX_LNB(16, 1);
   else if (cfg.nv == 1) CNX_LNB(32, 1);

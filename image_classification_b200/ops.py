@@ -154,6 +154,43 @@ def layernorm_bwd(dy2d, x2d, weight, mean, rstd):
     return dx, dw, db
 
 
+def layernorm_patch_fwd(x_nhwc, weight, bias, patch: int, eps: float = LN_EPS):
+    """LayerNorm2d of x [B,H,W,C] bf16 written patch-major: -> (y [B*H/k*W/k, k*k*C] bf16, mean, rstd)."""
+    _chk(x_nhwc, torch.bfloat16, "x")
+    B, H, W, C = x_nhwc.shape
+    y = torch.empty(B * (H // patch) * (W // patch), patch * patch * C, device=x_nhwc.device,
+                    dtype=torch.bfloat16)
+    mean = torch.empty(B * H * W, device=x_nhwc.device, dtype=torch.float32)
+    rstd = torch.empty_like(mean)
+    _lib.call("cnx_layernorm_patch_fwd", _p(x_nhwc), _p(_chk(weight, torch.float32, "weight")),
+              _p(_chk(bias, torch.float32, "bias")), _p(y), _p(mean), _p(rstd), B, H, W, C, patch,
+              eps, _stream(x_nhwc))
+    return y, mean, rstd
+
+
+def layernorm_patch_bwd(dy_patch, x_nhwc, weight, mean, rstd, patch: int):
+    """-> (dx [B,H,W,C] bf16, dweight [C], dbias [C]); dy_patch is patch-major like the forward's y."""
+    _chk(dy_patch, torch.bfloat16, "dy")
+    _chk(x_nhwc, torch.bfloat16, "x")
+    B, H, W, C = x_nhwc.shape
+    dx = torch.empty_like(x_nhwc)
+    dw = torch.empty(C, device=x_nhwc.device, dtype=torch.float32)
+    db = torch.empty_like(dw)
+    _lib.call("cnx_layernorm_patch_bwd", _p(dy_patch), _p(x_nhwc), _p(_chk(weight, torch.float32, "weight")),
+              _p(mean), _p(rstd), _p(dx), _p(dw), _p(db), B, H, W, C, patch, _stream(x_nhwc))
+    return dx, dw, db
+
+
+def patchify_nchw_f32(x: torch.Tensor, patch: int) -> torch.Tensor:
+    """x [B,Cin,H,W] fp32 contiguous -> [B*H/k*W/k, k*k*Cin] bf16, inner order (kh, kw, c)."""
+    _chk(x, torch.float32, "x")
+    B, Cin, H, W = x.shape
+    P = torch.empty(B * (H // patch) * (W // patch), patch * patch * Cin, device=x.device,
+                    dtype=torch.bfloat16)
+    _lib.call("cnx_patchify_nchw_f32", _p(x), _p(P), B, Cin, H, W, patch, _stream(x))
+    return P
+
+
 def colsum_bf16(x2d: torch.Tensor) -> torch.Tensor:
     """[M, C] bf16 -> [C] fp32 column sums."""
     _chk(x2d, torch.bfloat16, "x")
@@ -165,6 +202,7 @@ def colsum_bf16(x2d: torch.Tensor) -> torch.Tensor:
 
 # ------------------------------------------------------------------ MLP GEMMs
 EPI_STORE_BF16, EPI_BIAS_GELU, EPI_BIAS_RESIDUAL, EPI_GELU_GRAD, EPI_STORE_F32 = range(5)
+EPI_BIAS = 6
 
 
 def gemm_bf16(A, B, *, a_mn_major=False, b_mn_major=False, epilogue=EPI_STORE_BF16, bias=None,

@@ -51,7 +51,8 @@ typedef enum cnx_epilogue {
   CNX_EPI_BIAS_GELU = 1,     /* D0 = z = acc + bias ; D1 = gelu(z)         */
   CNX_EPI_BIAS_RESIDUAL = 2, /* D0 = acc + bias + R                        */
   CNX_EPI_GELU_GRAD = 3,     /* D0 = acc * gelu'(R) ; colsum += sum_m D0   */
-  CNX_EPI_STORE_F32 = 4      /* D0 (fp32, zero-filled by caller) += acc    */
+  CNX_EPI_STORE_F32 = 4,     /* D0 (fp32, zero-filled by caller) += acc    */
+  CNX_EPI_BIAS = 6           /* D0 = acc + bias (patchify convolutions)    */
 } cnx_epilogue;
 
 /* One entry of the host-generated MixUp/CutMix plan (see cnx_mix_batch). 32 bytes. */
@@ -132,6 +133,22 @@ int cnx_layernorm_fwd(const void* x, const float* weight, const float* bias, voi
 int cnx_layernorm_bwd(const void* dy, const void* x, const float* weight, const float* mean,
                       const float* rstd, void* dx, float* dweight, float* dbias, int64_t M, int C,
                       void* stream);
+/* The k x k stride-k ("patchify") convolutions of the stem and the downsample layers as plain GEMMs
+ * (SURVEY.md 8 f-1): their im2col matrix is a permutation of the input, [B*H/k*W/k, k*k*C] with
+ * inner order (kh, kw, c) - the layout of a channels_last conv weight [Cout][kh][kw][C].
+ * cnx_layernorm_patch_fwd: LayerNorm2d whose OUTPUT rows are written patch-major (downsample:
+ *   LayerNorm2d -> 2x2 s2 conv); mean / rstd stay indexed by input pixel.
+ * cnx_layernorm_patch_bwd: its backward; dy_patch is the patch-major gradient the conv's data-
+ *   gradient GEMM produced, dx is in pixel order.  dweight / dbias are overwritten.
+ * cnx_patchify_nchw_f32: stem input [B,Cin,H,W] fp32 -> patch-major bf16 (k*k*Cin % 8 == 0). */
+int cnx_layernorm_patch_fwd(const void* x, const float* weight, const float* bias, void* y_patch,
+                            float* mean, float* rstd, int B, int H, int W, int C, int patch,
+                            float eps, void* stream);
+int cnx_layernorm_patch_bwd(const void* dy_patch, const void* x, const float* weight,
+                            const float* mean, const float* rstd, void* dx, float* dweight,
+                            float* dbias, int B, int H, int W, int C, int patch, void* stream);
+int cnx_patchify_nchw_f32(const float* x, void* P, int B, int Cin, int H, int W, int patch,
+                          void* stream);
 /* out[c] = sum_m x[m,c] for a bf16 [M,C] matrix (fp32 result, overwritten): the bias gradient of the
  * stem / downsample convolutions (sum of grad_output over batch and space in NHWC). */
 int cnx_colsum_bf16(const void* x, float* out, int64_t M, int C, void* stream);

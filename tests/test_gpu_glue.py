@@ -415,3 +415,75 @@ def test_device_prefetcher_and_async_scalar_reader(cnx_lib):
         seen += 1
     got += reader.drain()
     assert seen == 5 and got == [0.0, 1.0, 2.0, 3.0, 4.0]
+
+
+@pytest.mark.parametrize("cfg", [(128, 256, 28, True), (256, 512, 14, False), (96, 192, 12, True)])
+def test_downsample_b200_matches_torch_sequential(cnx_lib, cfg):
+    """LayerNorm2d -> 2x2 s2 conv as cnx_layernorm_patch_fwd + tcgen05 GEMMs vs the same modules
+    run by PyTorch in fp32/fp64: output, input gradient, all four parameter gradients."""
+    from image_classification_b200.convnext import DownsampleB200, LayerNorm2d, PatchConv2d
+    cin, cout, hw, cl = cfg
+    dev = _dev()
+    torch.manual_seed(cin)
+    mine = DownsampleB200(LayerNorm2d(cin, eps=1e-6), PatchConv2d(cin, cout, kernel_size=2, stride=2)).to(dev)
+    with torch.no_grad():
+        mine[0].weight.copy_(1 + 0.2 * torch.randn(cin))
+        mine[0].bias.copy_(0.1 * torch.randn(cin))
+        mine[1].weight.copy_(0.05 * torch.randn_like(mine[1].weight))
+        mine[1].bias.copy_(0.1 * torch.randn(cout))
+    if cl:
+        mine[1].to(memory_format=torch.channels_last)
+    x = torch.randn(3, cin, hw, hw, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    g = torch.randn(3, cout, hw // 2, hw // 2, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    xm = x.clone().requires_grad_()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        ym = mine(xm)
+    assert ym.dtype == torch.bfloat16 and ym.shape == g.shape
+    ym.backward(g)
+    # fp64 reference of the same two layers
+    xr = x.double().requires_grad_()
+    w = {k: v.detach().double() for k, v in mine.state_dict().items()}
+    for v in w.values():
+        v.requires_grad_()
+    yn = torch.nn.functional.layer_norm(xr.permute(0, 2, 3, 1), (cin,), w["0.weight"], w["0.bias"], 1e-6)
+    yr = torch.nn.functional.conv2d(yn.permute(0, 3, 1, 2), w["1.weight"], w["1.bias"], stride=2)
+    yr.backward(g.double())
+    rel = lambda a, b: float((a.double() - b).abs().max() / b.abs().max())
+    assert rel(ym, yr.detach()) < 2e-2
+    assert rel(xm.grad, xr.grad) < 2e-2
+    assert mine[1].weight.grad.stride() == mine[1].weight.stride()
+    for k, p in mine.named_parameters():
+        assert rel(p.grad, w[k].grad) < 2e-2, (k, rel(p.grad, w[k].grad))
+
+
+def test_stem_b200_matches_torch_sequential(cnx_lib):
+    from image_classification_b200.convnext import LayerNorm2d, PatchConv2d, StemB200
+    dev = _dev()
+    torch.manual_seed(7)
+    mine = StemB200(PatchConv2d(3, 128, kernel_size=4, stride=4), LayerNorm2d(128, eps=1e-6)).to(dev)
+    mine[0].to(memory_format=torch.channels_last)
+    with torch.no_grad():
+        mine[0].weight.copy_(0.1 * torch.randn_like(mine[0].weight))
+        mine[0].bias.copy_(0.1 * torch.randn(128))
+        mine[1].weight.copy_(1 + 0.2 * torch.randn(128))
+    x = torch.randn(4, 3, 64, 96, device=dev)
+    g = torch.randn(4, 128, 16, 24, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        ym = mine(x)
+    assert ym.dtype == torch.bfloat16 and ym.is_contiguous(memory_format=torch.channels_last)
+    ym.backward(g)
+    w = {k: v.detach().double().requires_grad_() for k, v in mine.state_dict().items()}
+    xb = x.bfloat16().double()                       # the kernels see bf16 pixels
+    yc = torch.nn.functional.conv2d(xb, w["0.weight"], w["0.bias"], stride=4)
+    yr = torch.nn.functional.layer_norm(yc.permute(0, 2, 3, 1), (128,), w["1.weight"], w["1.bias"], 1e-6)
+    yr = yr.permute(0, 3, 1, 2)
+    yr.backward(g.double())
+    rel = lambda a, b: float((a.double() - b).abs().max() / b.abs().max())
+    assert rel(ym, yr.detach()) < 2e-2
+    for k, p in mine.named_parameters():
+        assert rel(p.grad, w[k].grad) < 2e-2, (k, rel(p.grad, w[k].grad))
+    # the patchify permutation itself is exact
+    from image_classification_b200 import ops
+    P = ops.patchify_nchw_f32(x, 4)
+    ref = x.bfloat16().view(4, 3, 16, 4, 24, 4).permute(0, 2, 4, 3, 5, 1).reshape(4 * 16 * 24, 48)
+    assert torch.equal(P, ref)
