@@ -56,23 +56,33 @@ nhwc_to_nchw_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ d
 // bf16, inner order (kh, kw, c): one im2col row per output pixel of a k x k stride-k convolution
 // (no overlap, so this is a permutation + cast).  One CTA per (image, row of patches): coalesced
 // reads along W into shared memory, one contiguous run of W/k*k*k*Cin bf16 written out.
+// CIN / KK > 0: compile-time channel count and patch size (divisions become shifts / multiplies)
+template <int CIN, int KK>
 __global__ void __launch_bounds__(256)
-patchify_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ P, int Cin, int H, int W,
-                int k) {
-  extern __shared__ float s_in[];                 // [Cin][k][W]
+patchify_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ P, int Cin_rt, int H, int W,
+                int k_rt) {
+  extern __shared__ float s_in[];                 // [Cin][k][W + 1]  (+1: conflict-free gathers)
+  const int Cin = CIN > 0 ? CIN : Cin_rt, k = KK > 0 ? KK : k_rt;
   const int oh = blockIdx.x, b = blockIdx.y;
-  const int n_in = Cin * k * W;
-  for (int i = threadIdx.x; i < n_in; i += 256) {
-    const int w = i % W, t = i / W, kh = t % k, c = t / k;
-    s_in[i] = x[((static_cast<size_t>(b) * Cin + c) * H + oh * k + kh) * W + w];
+  const int WP = W + 1;
+  for (int r = threadIdx.x / 32; r < Cin * k; r += 8) {      // one warp per input row: coalesced
+    const int kh = r % k, c = r / k;
+    const float* src = x + ((static_cast<size_t>(b) * Cin + c) * H + oh * k + kh) * W;
+    for (int w = threadIdx.x & 31; w < W; w += 32) s_in[r * WP + w] = src[w];
   }
   __syncthreads();
   const int OW = W / k, K = k * k * Cin;
   __nv_bfloat16* dst = P + (static_cast<size_t>(b) * (H / k) + oh) * OW * K;
-  for (int e = threadIdx.x; e < OW * K; e += 256) {
-    const int ow = e / K, r = e - ow * K;
-    const int c = r % Cin, t = r / Cin, kw = t % k, kh = t / k;
-    dst[e] = __float2bfloat16_rn(s_in[(c * k + kh) * W + ow * k + kw]);
+  for (int e = 2 * threadIdx.x; e < OW * K; e += 512) {      // K is even: two outputs per thread
+    float v[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int ee = e + u;
+      const int ow = ee / K, r = ee - ow * K;
+      const int c = r % Cin, t = r / Cin, kw = t % k, kh = t / k;
+      v[u] = s_in[(c * k + kh) * WP + ow * k + kw];
+    }
+    *reinterpret_cast<__nv_bfloat162*>(dst + e) = __floats2bfloat162_rn(v[0], v[1]);
   }
 }
 
@@ -81,22 +91,22 @@ patchify_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ P, int 
 int patchify_nchw_f32(const float* x, void* P, int B, int Cin, int H, int W, int k,
                       cudaStream_t stream) {
   if (B <= 0 || Cin <= 0 || H <= 0 || W <= 0 || k <= 0 || (H % k) != 0 || (W % k) != 0 ||
-      B > 65535 || ((k * k * Cin) % 8) != 0 || static_cast<size_t>(Cin) * k * W * 4 > 160 * 1024) {
+      B > 65535 || ((k * k * Cin) % 8) != 0 || static_cast<size_t>(Cin) * k * (W + 1) * 4 > 160 * 1024) {
     set_last_error("patchify: bad shape B=%d Cin=%d H=%d W=%d k=%d (k must divide H and W, "
                    "k*k*Cin must be a multiple of 8)", B, Cin, H, W, k);
     return CNX_ERR_BAD_SHAPE;
   }
-  const size_t smem = static_cast<size_t>(Cin) * k * W * 4;
+  const size_t smem = static_cast<size_t>(Cin) * k * (W + 1) * 4;
+  auto kern = (Cin == 3 && k == 4) ? patchify_kernel<3, 4> : patchify_kernel<0, 0>;
   if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(patchify_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem));
     if (e != cudaSuccess) {
       set_last_error("patchify: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
       return CNX_ERR_LAUNCH;
     }
   }
-  patchify_kernel<<<dim3(H / k, B), 256, smem, stream>>>(x, static_cast<__nv_bfloat16*>(P), Cin, H,
-                                                         W, k);
+  kern<<<dim3(H / k, B), 256, smem, stream>>>(x, static_cast<__nv_bfloat16*>(P), Cin, H, W, k);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_last_error("patchify launch: %s", cudaGetErrorString(e));

@@ -161,11 +161,13 @@ ln_rows_bwd_kernel(const __nv_bfloat16* __restrict__ dxhat, const __nv_bfloat16*
 // an [B*H*W, C] matrix, i.e. [B*H/k*W/k, k*k*C] holds one im2col row per output pixel.  pk <= 1: identity.
 __device__ __forceinline__ int64_t patch_row(int64_t m, int pH, int pW, int pk) {
   if (pk <= 1) return m;
-  const int w = static_cast<int>(m % pW);
-  const int64_t t = m / pW;
-  const int h = static_cast<int>(t % pH);
-  const int64_t b = t / pH;
-  return ((b * (pH / pk) + h / pk) * (pW / pk) + w / pk) * (pk * pk) + (h % pk) * pk + (w % pk);
+  // 32-bit arithmetic (the host checks M < 2^31): 64-bit divisions would dominate the row loop
+  const unsigned um = static_cast<unsigned>(m), uW = static_cast<unsigned>(pW),
+                 uH = static_cast<unsigned>(pH), uk = static_cast<unsigned>(pk);
+  const unsigned t = um / uW, w = um - t * uW;
+  const unsigned b = t / uH, h = t - b * uH;
+  const unsigned oh = h / uk, kh = h - oh * uk, ow = w / uk, kw = w - ow * uk;
+  return static_cast<int64_t>(((b * (uH / uk) + oh) * (uW / uk) + ow) * (uk * uk) + kh * uk + kw);
 }
 
 template <int LPR, int NV>
@@ -436,7 +438,8 @@ int ln_rows_bwd(const void* dxhat, const void* xhat, const float* rstd, void* dc
 
 int check_patch(const char* who, int64_t M, int pH, int pW, int pk) {
   if (pk <= 1) return CNX_OK;
-  if (pH <= 0 || pW <= 0 || (pH % pk) != 0 || (pW % pk) != 0 || (M % (static_cast<int64_t>(pH) * pW)) != 0) {
+  if (pH <= 0 || pW <= 0 || (pH % pk) != 0 || (pW % pk) != 0 || M >= (1LL << 31) ||
+      (M % (static_cast<int64_t>(pH) * pW)) != 0) {
     set_last_error("%s: patch size %d must divide H=%d and W=%d, and M=%lld must be B*H*W", who, pk,
                    pH, pW, (long long)M);
     return CNX_ERR_BAD_SHAPE;
