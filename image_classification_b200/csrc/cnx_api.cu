@@ -217,7 +217,17 @@ int cnx_mix_batch(const float* x, const int64_t* labels, const cnx_mix_plan_entr
   CNX_REQUIRE_PTR(targets);
   static_assert(sizeof(cnx_mix_plan_entry) == sizeof(MixPlanEntry), "plan entry layout");
   return mix_batch(x, labels, reinterpret_cast<const MixPlanEntry*>(plan), out, targets, B, CH, H,
-                   W, num_classes, as_stream(stream));
+                   W, num_classes, 1.0f, 0.0f, as_stream(stream));
+}
+
+int cnx_mix_batch_smooth(const float* x, const int64_t* labels, const cnx_mix_plan_entry* plan,
+                         float* out, float* targets, int B, int CH, int H, int W, int num_classes,
+                         float on_value, float off_value, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(labels); CNX_REQUIRE_PTR(plan); CNX_REQUIRE_PTR(out);
+  CNX_REQUIRE_PTR(targets);
+  return mix_batch(x, labels, reinterpret_cast<const MixPlanEntry*>(plan), out, targets, B, CH, H,
+                   W, num_classes, on_value, off_value, as_stream(stream));
 }
 
 int cnx_softce_fwd_bwd(const float* logits, const float* targets, float* loss, float* dlogits,

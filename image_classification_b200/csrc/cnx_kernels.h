@@ -66,7 +66,8 @@ struct MixPlanEntry {          // one per sample; integers are bit-exact vs the 
   int32_t bbx1, bby1, bbx2, bby2;
 };
 int mix_batch(const float* x, const int64_t* labels, const MixPlanEntry* plan, float* out,
-              float* targets, int B, int CH, int H, int W, int num_classes, cudaStream_t stream);
+              float* targets, int B, int CH, int H, int W, int num_classes, float on_value,
+              float off_value, cudaStream_t stream);
 int softce_fwd_bwd(const float* logits, const float* targets, float* loss, float* dlogits, int B,
                    int NC, float label_smoothing, cudaStream_t stream);
 int ema_lerp_multi(const void* const* param_ptrs, void* const* shadow_ptrs,

@@ -21,7 +21,8 @@ namespace {
 __global__ void __launch_bounds__(256)
 mix_batch_kernel(const float* __restrict__ x, const int64_t* __restrict__ labels,
                  const MixPlanEntry* __restrict__ plan, float* __restrict__ out,
-                 float* __restrict__ targets, int CH, int H, int W, int NC) {
+                 float* __restrict__ targets, int CH, int H, int W, int NC, float on_value,
+                 float off_value) {
   const int b = blockIdx.y;
   const MixPlanEntry e = plan[b];
   const size_t per = static_cast<size_t>(CH) * H * W;
@@ -34,13 +35,15 @@ mix_batch_kernel(const float* __restrict__ x, const int64_t* __restrict__ labels
     const int64_t la = labels[b];
     const int64_t lb = labels[e.partner];
     for (int c = threadIdx.x; c < NC; c += blockDim.x) {
+      // (smoothed) one-hot rows blended like the pixels: y1 * lam + y2 * (1 - lam); with
+      // on = 1, off = 0 the products are exact, i.e. the reference's  oh1*lam + oh2*(1-lam)
+      const float ya = (c == la) ? on_value : off_value;
+      const float yb = (c == lb) ? on_value : off_value;
       float t;
       if (e.mode == 0) {
-        t = (c == la) ? 1.0f : 0.0f;
+        t = ya;
       } else {
-        const float ta = (c == la) ? e.lam : 0.0f;            // onehot * lam   (exact)
-        const float tb = (c == lb) ? e.one_minus_lam : 0.0f;  // onehot * (1-lam)
-        t = __fadd_rn(ta, tb);
+        t = __fadd_rn(__fmul_rn(ya, e.lam), __fmul_rn(yb, e.one_minus_lam));
       }
       targets[static_cast<size_t>(b) * NC + c] = t;
     }
@@ -166,7 +169,8 @@ ema_lerp_kernel(const void* const* __restrict__ pptr, void* const* __restrict__ 
 }  // namespace
 
 int mix_batch(const float* x, const int64_t* labels, const MixPlanEntry* plan, float* out,
-              float* targets, int B, int CH, int H, int W, int num_classes, cudaStream_t stream) {
+              float* targets, int B, int CH, int H, int W, int num_classes, float on_value,
+              float off_value, cudaStream_t stream) {
   if (B <= 0 || CH <= 0 || H <= 0 || W <= 0 || num_classes <= 0 || (W % 4) != 0) {
     set_last_error("mix_batch: bad shape B=%d CH=%d H=%d W=%d NC=%d (W must be a multiple of 4)", B,
                    CH, H, W, num_classes);
@@ -178,7 +182,8 @@ int mix_batch(const float* x, const int64_t* labels, const MixPlanEntry* plan, f
   }
   const size_t nvec = static_cast<size_t>(CH) * H * W / 4;
   dim3 grid(static_cast<unsigned>((nvec + 255) / 256), B);
-  mix_batch_kernel<<<grid, 256, 0, stream>>>(x, labels, plan, out, targets, CH, H, W, num_classes);
+  mix_batch_kernel<<<grid, 256, 0, stream>>>(x, labels, plan, out, targets, CH, H, W, num_classes,
+                                             on_value, off_value);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_last_error("mix_batch launch: %s", cudaGetErrorString(e));

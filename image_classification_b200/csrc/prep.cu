@@ -111,12 +111,29 @@ unfold_fc1_kernel(const float* __restrict__ dw1f, const float* __restrict__ db1f
 // fc2 side of the adjoint: one CTA per output channel c (row of fc2_w [C][4C]).
 //   d_fc2_w[c,j] = gamma[c]*dW2f[c,j]   d_fc2_b[c] = gamma[c]*db2f[c]
 //   d_gamma[c]   = sum_j dW2f[c,j]*fc2_w[c,j] + db2f[c]*fc2_b[c]
+// One launch for everything but the fc1 side: CTAs [0, C) = fc2 rows (as above), the CTAs after
+// them transpose the depthwise taps (d_dw_w[c][t] = dwt_dw[t][c]) and zero d_ln_w / d_ln_b, which
+// the fc1 kernel launched next accumulates into.
 __global__ void __launch_bounds__(256)
-unfold_fc2_kernel(const float* __restrict__ dw2f, const float* __restrict__ db2f,
-                  const float* __restrict__ fc2_w, const float* __restrict__ fc2_b,
-                  const float* __restrict__ gamma, float* __restrict__ d_fc2_w,
-                  float* __restrict__ d_fc2_b, float* __restrict__ d_gamma, int Cc, int R4) {
+unfold_fc2_dw_kernel(const float* __restrict__ dw2f, const float* __restrict__ db2f,
+                     const float* __restrict__ fc2_w, const float* __restrict__ fc2_b,
+                     const float* __restrict__ gamma, float* __restrict__ d_fc2_w,
+                     float* __restrict__ d_fc2_b, float* __restrict__ d_gamma,
+                     const float* __restrict__ dwt, float* __restrict__ d_dw_w,
+                     float* __restrict__ d_ln_w, float* __restrict__ d_ln_b, int Cc, int R4) {
   __shared__ float sred[8];
+  if (static_cast<int>(blockIdx.x) >= Cc) {
+    const int i = (blockIdx.x - Cc) * 256 + threadIdx.x;
+    if (i < 49 * Cc) {
+      const int c = i / 49, t = i % 49;
+      d_dw_w[i] = dwt[t * Cc + c];
+    }
+    if (i < Cc) {
+      d_ln_w[i] = 0.f;
+      d_ln_b[i] = 0.f;
+    }
+    return;
+  }
   const int c = blockIdx.x;
   const float g = gamma[c];
   float a = 0.f;
@@ -135,16 +152,6 @@ unfold_fc2_kernel(const float* __restrict__ dw2f, const float* __restrict__ db2f
     for (int i = 0; i < 8; ++i) t += sred[i];
     d_gamma[c] = fmaf(db2f[c], fc2_b[c], t);
     d_fc2_b[c] = g * db2f[c];
-  }
-}
-
-// d_dw_w[c][t] = dwt_dw[t][c]
-__global__ void __launch_bounds__(256)
-unfold_dw_kernel(const float* __restrict__ dwt, float* __restrict__ d_dw_w, int C) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < 49 * C) {
-    const int c = i / 49, t = i % 49;
-    d_dw_w[i] = dwt[t * C + c];
   }
 }
 
@@ -196,17 +203,15 @@ int unfold_block_grads(const float* dw1f, const float* db1f, const float* dw2f, 
     return CNX_ERR_BAD_SHAPE;
   }
   const int R4 = 4 * C;
-  cudaMemsetAsync(d_ln_w, 0, sizeof(float) * C, stream);
-  cudaMemsetAsync(d_ln_b, 0, sizeof(float) * C, stream);
+  unfold_fc2_dw_kernel<<<C + (49 * C + 255) / 256, 256, 0, stream>>>(
+      dw2f, db2f, fc2_w, fc2_b, ls_gamma, d_fc2_w, d_fc2_b, d_ls_gamma, dwt_dw, d_dw_w, d_ln_w,
+      d_ln_b, C, R4);
   {
     const int rows_per_block = 128;
     dim3 grid((C + 31) / 32, (R4 + rows_per_block - 1) / rows_per_block);
     unfold_fc1_kernel<<<grid, 256, 0, stream>>>(dw1f, db1f, fc1_w, ln_w, ln_b, d_fc1_w, d_ln_w,
                                                 d_ln_b, R4, C, rows_per_block);
   }
-  unfold_fc2_kernel<<<C, 256, 0, stream>>>(dw2f, db2f, fc2_w, fc2_b, ls_gamma, d_fc2_w, d_fc2_b,
-                                           d_ls_gamma, C, R4);
-  unfold_dw_kernel<<<(49 * C + 255) / 256, 256, 0, stream>>>(dwt_dw, d_dw_w, C);
   return check_launch("unfold_block_grads");
 }
 

@@ -66,9 +66,11 @@ def plan_mix_batch(batch_size: int, height: int, width: int, *, mixup_alpha: flo
     return plan
 
 
-def mix_batch(images: torch.Tensor, labels: torch.Tensor, plan: np.ndarray, num_classes: int):
+def mix_batch(images: torch.Tensor, labels: torch.Tensor, plan: np.ndarray, num_classes: int,
+              on_value: float = 1.0, off_value: float = 0.0):
     """Apply `plan` on the device: images [B,CH,H,W] fp32 (NCHW), labels [B] int64 ->
-    (mixed images, soft targets [B,num_classes] fp32)."""
+    (mixed images, soft targets [B,num_classes] fp32).  on/off: values of the (smoothed) one-hot
+    rows that are blended (1/0 = the reference's plain one-hot)."""
     if not images.is_cuda:
         raise _lib.CnxError("mix_batch: images must be a CUDA tensor (no CPU path)")
     if images.dtype != torch.float32 or not images.is_contiguous():
@@ -81,9 +83,14 @@ def mix_batch(images: torch.Tensor, labels: torch.Tensor, plan: np.ndarray, num_
                                                                             non_blocking=True)
     out = torch.empty_like(images)
     targets = torch.empty(B, num_classes, device=images.device, dtype=torch.float32)
-    _lib.call("cnx_mix_batch", images.data_ptr(), labels.data_ptr(), plan_dev.data_ptr(),
-              out.data_ptr(), targets.data_ptr(), B, CH, H, W, num_classes,
-              torch.cuda.current_stream(images.device).cuda_stream)
+    stream = torch.cuda.current_stream(images.device).cuda_stream
+    if on_value == 1.0 and off_value == 0.0:
+        _lib.call("cnx_mix_batch", images.data_ptr(), labels.data_ptr(), plan_dev.data_ptr(),
+                  out.data_ptr(), targets.data_ptr(), B, CH, H, W, num_classes, stream)
+    else:
+        _lib.call("cnx_mix_batch_smooth", images.data_ptr(), labels.data_ptr(), plan_dev.data_ptr(),
+                  out.data_ptr(), targets.data_ptr(), B, CH, H, W, num_classes,
+                  float(np.float32(on_value)), float(np.float32(off_value)), stream)
     return out, targets
 
 
@@ -101,3 +108,81 @@ class BatchMixUpCutMix:
         plan = plan_mix_batch(B, H, W, mixup_alpha=self.mixup_alpha, cutmix_alpha=self.cutmix_alpha,
                               prob=self.prob, rng=rng)
         return mix_batch(images, labels, plan, self.num_classes)
+
+
+def plan_timm_batch_mixup(batch_size: int, height: int, width: int, *, mixup_alpha: float = 1.0,
+                          cutmix_alpha: float = 0.0, prob: float = 1.0, switch_prob: float = 0.5,
+                          correct_lam: bool = True, rng=None) -> np.ndarray:
+    """timm `Mixup(mode='batch')` parameters as a plan: ONE lambda / mode / box for the whole batch,
+    partner = the flipped batch (`x.flip(0)`).  RNG call order of timm.data.mixup
+    (`_params_per_batch`, `rand_bbox`): rand() gate, [rand() switch], beta, [randint(H) THEN
+    randint(W)].  timm is not vendored in the reference (requirements.txt:3): restated from the
+    upstream source the reference imports at previous/V2-convbase/dataset.py:10,119-129."""
+    rng = np.random if rng is None else rng
+    if batch_size % 2 != 0:
+        raise _lib.CnxError("timm batch Mixup: batch size must be even")       # timm asserts this
+    lam, use_cutmix = 1.0, False
+    if (mixup_alpha > 0 or cutmix_alpha > 0) and rng.rand() < prob:
+        if mixup_alpha > 0.0 and cutmix_alpha > 0.0:
+            use_cutmix = rng.rand() < switch_prob
+            lam_mix = rng.beta(cutmix_alpha, cutmix_alpha) if use_cutmix else \
+                rng.beta(mixup_alpha, mixup_alpha)
+        elif mixup_alpha > 0.0:
+            lam_mix = rng.beta(mixup_alpha, mixup_alpha)
+        else:
+            use_cutmix = True
+            lam_mix = rng.beta(cutmix_alpha, cutmix_alpha)
+        lam = float(lam_mix)
+    plan = np.zeros(batch_size, dtype=PLAN_DTYPE)
+    plan["partner"] = np.arange(batch_size - 1, -1, -1)
+    if lam == 1.0:
+        plan["mode"], plan["lam"], plan["one_minus_lam"] = MODE_PASS, 1.0, 0.0
+        return plan
+    if use_cutmix:
+        H, W = height, width
+        ratio = np.sqrt(1 - lam)
+        cut_h, cut_w = int(H * ratio), int(W * ratio)
+        cy = rng.randint(0, H)
+        cx = rng.randint(0, W)
+        yl, yh = int(np.clip(cy - cut_h // 2, 0, H)), int(np.clip(cy + cut_h // 2, 0, H))
+        xl, xh = int(np.clip(cx - cut_w // 2, 0, W)), int(np.clip(cx + cut_w // 2, 0, W))
+        if correct_lam:
+            lam = 1.0 - (yh - yl) * (xh - xl) / float(H * W)
+        plan["mode"] = MODE_CUTMIX
+        plan["bbx1"], plan["bby1"], plan["bbx2"], plan["bby2"] = xl, yl, xh, yh
+    else:
+        plan["mode"] = MODE_MIXUP
+    plan["lam"] = np.float32(lam)
+    plan["one_minus_lam"] = np.float32(1.0 - lam)
+    return plan
+
+
+@dataclass
+class TimmBatchMixup:
+    """Device-side timm `Mixup(..., mode='batch')`: same constructor arguments
+    as the object the reference builds at previous/V2-convbase/dataset.py:119-129; targets are
+    label-smoothed one-hot rows blended with the batch lambda (`mixup_target`)."""
+
+    mixup_alpha: float = 1.0
+    cutmix_alpha: float = 0.0
+    cutmix_minmax: tuple | None = None
+    prob: float = 1.0
+    switch_prob: float = 0.5
+    mode: str = "batch"
+    correct_lam: bool = True
+    label_smoothing: float = 0.1
+    num_classes: int = 1000
+
+    def __post_init__(self):
+        if self.mode != "batch" or self.cutmix_minmax is not None:
+            raise _lib.CnxError("TimmBatchMixup: only mode='batch' without cutmix_minmax is built")
+
+    def __call__(self, images: torch.Tensor, labels: torch.Tensor, rng=None):
+        B, _, H, W = images.shape
+        plan = plan_timm_batch_mixup(B, H, W, mixup_alpha=self.mixup_alpha,
+                                     cutmix_alpha=self.cutmix_alpha, prob=self.prob,
+                                     switch_prob=self.switch_prob, correct_lam=self.correct_lam,
+                                     rng=rng)
+        off = self.label_smoothing / self.num_classes
+        on = 1.0 - self.label_smoothing + off
+        return mix_batch(images, labels, plan, self.num_classes, on, off)

@@ -182,6 +182,12 @@ int cnx_mlp_bwd_wgrad(const void* dy, const void* h, const void* dz, const void*
 int cnx_mix_batch(const float* x, const int64_t* labels, const cnx_mix_plan_entry* plan,
                   float* out, float* targets, int B, int CH, int H, int W, int num_classes,
                   void* stream);
+/* Same with label-smoothed one-hot rows (timm Mixup semantics; constructed at
+ * /root/reference/previous/V2-convbase/dataset.py:119-129): a target row is
+ * y(label)*lam + y(partner label)*(1-lam) with y = on_value at the label, off_value elsewhere. */
+int cnx_mix_batch_smooth(const float* x, const int64_t* labels, const cnx_mix_plan_entry* plan,
+                         float* out, float* targets, int B, int CH, int H, int W, int num_classes,
+                         float on_value, float off_value, void* stream);
 
 /* nn.CrossEntropyLoss(label_smoothing) on probability targets
  * (/root/reference/train_advanced_v4.py:626,221): loss (scalar, mean over B) and, if dlogits is

@@ -71,3 +71,52 @@ def mix_dataset_ref(images: np.ndarray, labels: np.ndarray, *, mixup_alpha, cutm
         out[i], targets[i] = d, t
         info.append(inf)
     return out, targets, info
+
+
+# ----------------------------------------------------------------------------------------------
+# timm `Mixup(mode='batch')`.  PARITY UNPINNED: timm is an un-vendored dependency
+# of the reference (requirements.txt:3 `timm>=0.9.2`; imported and constructed at
+# previous/V2-convbase/dataset.py:10,119-129, never called) and is not installable here, so this
+# restates the published algorithm of timm/data/mixup.py (`Mixup._params_per_batch`, `_mix_batch`,
+# `rand_bbox`, `cutmix_bbox_and_lam`, `mixup_target`, `one_hot`) with torch ops on CPU tensors, in
+# the upstream order of operations (in-place mul_/add_ on the batch, x.flip(0) as the partner).
+def timm_batch_mixup_ref(x, target, *, mixup_alpha=1.0, cutmix_alpha=0.0, prob=1.0, switch_prob=0.5,
+                         correct_lam=True, label_smoothing=0.1, num_classes=1000, rng=None):
+    import torch
+    rng = np.random if rng is None else rng
+    assert len(x) % 2 == 0
+    x = x.clone()
+    lam, use_cutmix = 1.0, False
+    if (mixup_alpha > 0 or cutmix_alpha > 0) and rng.rand() < prob:
+        if mixup_alpha > 0.0 and cutmix_alpha > 0.0:
+            use_cutmix = rng.rand() < switch_prob
+            lam_mix = rng.beta(cutmix_alpha, cutmix_alpha) if use_cutmix else rng.beta(mixup_alpha, mixup_alpha)
+        elif mixup_alpha > 0.0:
+            lam_mix = rng.beta(mixup_alpha, mixup_alpha)
+        else:
+            use_cutmix = True
+            lam_mix = rng.beta(cutmix_alpha, cutmix_alpha)
+        lam = float(lam_mix)
+    if lam != 1.0:
+        if use_cutmix:
+            img_h, img_w = x.shape[-2:]
+            ratio = np.sqrt(1 - lam)
+            cut_h, cut_w = int(img_h * ratio), int(img_w * ratio)
+            cy = rng.randint(0, img_h)
+            cx = rng.randint(0, img_w)
+            yl, yh = np.clip(cy - cut_h // 2, 0, img_h), np.clip(cy + cut_h // 2, 0, img_h)
+            xl, xh = np.clip(cx - cut_w // 2, 0, img_w), np.clip(cx + cut_w // 2, 0, img_w)
+            if correct_lam:
+                lam = 1.0 - (yh - yl) * (xh - xl) / float(img_h * img_w)
+            x[:, :, yl:yh, xl:xh] = x.flip(0)[:, :, yl:yh, xl:xh]
+        else:
+            x_flipped = x.flip(0).mul_(1.0 - lam)
+            x.mul_(lam).add_(x_flipped)
+    off_value = label_smoothing / num_classes
+    on_value = 1.0 - label_smoothing + off_value
+
+    def one_hot(t):
+        return torch.full((t.size(0), num_classes), off_value).scatter_(1, t.long().view(-1, 1), on_value)
+
+    y = one_hot(target) * lam + one_hot(target.flip(0)) * (1.0 - lam)
+    return x, y, float(lam)

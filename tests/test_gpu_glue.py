@@ -487,3 +487,27 @@ def test_stem_b200_matches_torch_sequential(cnx_lib):
     P = ops.patchify_nchw_f32(x, 4)
     ref = x.bfloat16().view(4, 3, 16, 4, 24, 4).permute(0, 2, 4, 3, 5, 1).reshape(4 * 16 * 24, 48)
     assert torch.equal(P, ref)
+
+
+# ------------------------------------------------------- timm batch-mode Mixup
+@pytest.mark.parametrize("cfg", [dict(mixup_alpha=0.8, cutmix_alpha=0.0), dict(mixup_alpha=0.0, cutmix_alpha=1.0),
+                                 dict(mixup_alpha=0.2, cutmix_alpha=1.0, switch_prob=0.5, prob=0.7)])
+def test_timm_batch_mixup_bit_exact_vs_oracle(cnx_lib, cfg):
+    from image_classification_b200 import mix
+    dev = _dev()
+    mixer = mix.TimmBatchMixup(label_smoothing=0.1, num_classes=44, **cfg)
+    modes = set()
+    for seed in range(8):
+        gen = torch.Generator().manual_seed(seed)
+        x = torch.randn(6, 3, 32, 48, generator=gen)
+        y = torch.randint(0, 44, (6,), generator=gen)
+        xr, tr, lam = mix_oracle.timm_batch_mixup_ref(x, y, label_smoothing=0.1, num_classes=44,
+                                                       rng=np.random.RandomState(seed), **cfg)
+        xm, tm = mixer(x.to(dev), y.to(dev), rng=np.random.RandomState(seed))
+        assert torch.equal(xm.cpu(), xr), (seed, lam)
+        assert torch.equal(tm.cpu(), tr), (seed, lam)
+        assert abs(float(tm.sum(1).mean()) - 1.0) < 1e-5
+        modes.add("pass" if lam == 1.0 else "mix")
+    assert "mix" in modes
+    with pytest.raises(Exception):
+        mixer(torch.zeros(5, 3, 8, 8, device=dev), torch.zeros(5, dtype=torch.long, device=dev))

@@ -136,3 +136,34 @@ def test_bench_reference_arm_other_ranks_exit_quietly():
                           "--gpus", "2", "--steps", "1", "--warmup", "0"], env=env,
                          capture_output=True, text=True, timeout=120)
     assert res.returncode == 0 and res.stdout.strip() == ""
+
+
+def test_timm_batch_mixup_planner_follows_oracle_rng_order():
+    """Host planner of TimmBatchMixup vs the oracle restatement of timm's Mixup(mode='batch'):
+    same RNG consumption, lambda, box and mode for every seed (no GPU needed)."""
+    import numpy as np
+    import torch
+    from image_classification_b200 import mix
+    from oracle import mix_oracle
+    for cfg in (dict(mixup_alpha=0.8, cutmix_alpha=0.0), dict(mixup_alpha=0.0, cutmix_alpha=1.0),
+                dict(mixup_alpha=0.2, cutmix_alpha=1.0, prob=0.7, switch_prob=0.3)):
+        for seed in range(12):
+            x = torch.zeros(4, 3, 16, 24)
+            x[:, :, :, :] = torch.arange(4).view(4, 1, 1, 1).float()
+            y = torch.arange(4)
+            r1, r2 = np.random.RandomState(seed), np.random.RandomState(seed)
+            xr, tr, lam = mix_oracle.timm_batch_mixup_ref(x, y, num_classes=44, rng=r1, **cfg)
+            plan = mix.plan_timm_batch_mixup(4, 16, 24, rng=r2, **cfg)
+            assert r1.rand() == r2.rand()                      # identical RNG consumption
+            assert list(plan["partner"]) == [3, 2, 1, 0]
+            if lam == 1.0:          # no mixing drawn, or a cut box clipped to zero area
+                empty = (plan["bbx2"] - plan["bbx1"]) * (plan["bby2"] - plan["bby1"]) == 0
+                assert ((plan["mode"] == mix.MODE_PASS) | ((plan["mode"] == mix.MODE_CUTMIX) & empty)).all()
+                assert (plan["lam"] == 1.0).all()
+                continue
+            assert (plan["lam"] == np.float32(lam)).all()
+            if plan["mode"][0] == mix.MODE_CUTMIX:
+                pasted = (xr[0, 0] == 3.0)                     # sample 0 received pixels of sample 3
+                box = np.zeros((16, 24), dtype=bool)
+                box[plan["bby1"][0]:plan["bby2"][0], plan["bbx1"][0]:plan["bbx2"][0]] = True
+                assert np.array_equal(pasted.numpy(), box)
