@@ -34,6 +34,7 @@ import numpy as np
 import torch
 
 METRIC = "ConvNeXt-Base 224 bf16 train images/sec"
+SM_COUNT = 148
 UNIT = "images/s"
 NUM_CLASSES = 44
 MICRO_BATCH = 128
@@ -423,6 +424,18 @@ def main_b200(args):
                 k.update(bound="tensor", achieved=round(d["work"] / d["ms"] * 1e-9, 1),
                          unit="TFLOP/s", peak=pk["bf16_tflops_sustained"])
             k["frac"] = round(k["achieved"] / k["peak"], 4)
+        if name in ("dwconv_ln_fwd", "dwconv_ln_bwd") and d["work"] > 0:
+            # these kernels are bound by the FP32 FMA pipe, not HBM: 49 FMAs per
+            # element forward (work = 2*E*2 B), 98 backward (work = 4*E*2 B); peak = 128 FMA/clk/SM
+            elems = d["work"] / (4.0 if name == "dwconv_ln_fwd" else 8.0)
+            fmas = elems * (49.0 if name == "dwconv_ln_fwd" else 98.0)
+            sm_hz = (clocks or {}).get("sm_mhz", 1965.0) * 1e6
+            peak = 128.0 * SM_COUNT * sm_hz
+            k["fma_pipe"] = {"achieved_tfma": round(fmas / d["ms"] * 1e-9, 2),
+                             "peak_tfma": round(peak * 1e-12, 2),
+                             "frac": round(fmas / (d["ms"] * 1e-3) / peak, 4),
+                             "note": "includes the LayerNorm row kernel's time; tensor cores measured "
+                                     "2.4x slower for this op (profiles/r01_ubench_diag_mma.txt)"}
         kernels[name] = k
     dom = max((n for n in kernels if "frac" in kernels[n]), key=lambda n: kernels[n]["ms_per_step"])
     roof = {"kernel": dom, "bound": kernels[dom]["bound"], "achieved": kernels[dom]["achieved"],
