@@ -698,7 +698,7 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   // CTA pairs (256-row tiles through cta_group::2) whenever there are at least two row tiles
   // (CNX_GEMM_NO_PAIR=1 forces the single-CTA kernel: A/B debugging switch)
   static const bool no_pair = getenv("CNX_GEMM_NO_PAIR") != nullptr;
-  // measured with tools/gemm_sweep.py (profiles/r01_gemm_sweep.txt), same process A/B: every one of
+  // measured with tools/gemm_sweep.py (profiles/r01_gemm_sweep_v2.txt), same process A/B: every one of
   // these GEMMs is bound by operand bytes pulled from L2 (~8 TB/s chip-wide), so the pair tile
   // (2/3 of the operand bytes per MAC) wins wherever the main loop dominates; with short K the
   // two CTAs' heavy epilogues gate each other's next tile and the single-CTA kernel stays ahead
@@ -708,8 +708,8 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
     case EPI_STORE_BF16:
     case EPI_BIAS:
     case EPI_BIAS_RESIDUAL: pair = a.K >= 1024 || (a.K >= 512 && a.N >= 1024); break;
-    case EPI_BIAS_GELU:     pair = a.K >= 512; break;
-    case EPI_GELU_GRAD:     pair = a.K >= 1024; break;
+    case EPI_BIAS_GELU:     pair = a.K >= 256; break;
+    case EPI_GELU_GRAD:     pair = a.K >= 512; break;
     default: break;
   }
   pair = pair && !no_pair && a.M > BM && nsm >= 2;
@@ -747,7 +747,7 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
       const int kb = (nkb + s - 1) / s;
       const int eff = (nkb + kb - 1) / kb;
       const long rounds = (static_cast<long>(tiles) * eff + units - 1) / units;
-      const long cost = rounds * (kb + 6);     // + ~6 k-blocks of prologue/epilogue per item
+      const long cost = rounds * (kb + 12);    // + ~12 k-blocks of prologue/epilogue/atomics per item
       if (best < 0 || cost < best) { best = cost; splits = eff; }
     }
   }
