@@ -138,7 +138,7 @@ def run_cpu_reference(steps: int, warmup: int, micro_batch: int, res: int, model
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     torch.manual_seed(0)
-    model = loop_oracle.build_oracle_model(model_name, NUM_CLASSES).train()
+    model = loop_oracle.build_oracle_model(model_name, NUM_CLASSES, deep_supervision=True).train()
     opt = torch.optim.AdamW(model.parameters(), lr=1e-4, weight_decay=1e-2)   # config.py:35-36
     sched = get_cosine_schedule_with_warmup(opt, 10, 1000, 1e-6)
     ema = loop_oracle.EMARef(model, 0.9997)
@@ -208,11 +208,16 @@ class B200Trainer:
 
     def __init__(self, device, world, rank, micro_batch, res):
         from image_classification_b200 import ddp, ema, loss, mix, train_step
-        from image_classification_b200.convnext import create_convnext
+        from image_classification_b200.convnext import create_convnext, DeepSupervisionModelB200
         self.device, self.world, self.rank = device, world, rank
         self.micro_batch, self.res = micro_batch, res
         torch.manual_seed(0)                      # identical replicas on every rank
-        self.model = create_convnext("convnext_base", NUM_CLASSES).to(device).train()
+        # create_model(): timm convnext_base wrapped for deep supervision (config.py:22, :494-495);
+        # the loop keeps outputs[0], the three auxiliary heads run forward only
+        self.model = DeepSupervisionModelB200(create_convnext("convnext_base", NUM_CLASSES),
+                                              NUM_CLASSES).to(device).train()
+        if os.environ.get("CNX_NO_AUX"):          # A/B switch: skip the dead auxiliary heads (f-1)
+            self.model.compute_aux = False
         for m in self.model.modules():            # stem / downsample convs produce NHWC directly
             if isinstance(m, torch.nn.Conv2d) and m.groups == 1:
                 m.to(memory_format=torch.channels_last)

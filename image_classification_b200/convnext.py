@@ -3,9 +3,11 @@
 `timm` is not installable here, so the object `timm.create_model('convnext_base',
 num_classes=44)` returns (/root/reference/train_advanced_v4.py:488-492) is re-stated with the
 same attribute layout the reference touches: `stem`, `stages[i].downsample`, `stages[i].blocks[j]`,
-`head.{global_pool,norm,flatten,drop,fc}` (:106-111, :131-143).  Stem / downsample / head stay
-plain PyTorch (SURVEY.md §8 f-1 marks them "next"); only the 36 blocks are libcnx_b200 kernels.
-The residual stream is kept channels_last so the NHWC kernels are zero-copy between blocks.
+`head.{global_pool,norm,flatten,drop,fc}` (:106-111, :131-143).  The 36 blocks, the stem, the
+stage downsamples and the head's pool + norm run on libcnx_b200 kernels; only
+the 44-way `head.fc` / auxiliary Linear layers on [B, C] stay `nn.Linear`.  The residual stream is
+kept channels_last so the NHWC kernels are zero-copy between blocks.  `DeepSupervisionModelB200`
+mirrors the wrapper the reference puts around the backbone (:96-152).
 """
 from __future__ import annotations
 
@@ -49,13 +51,13 @@ class _LayerNorm2dFn(torch.autograd.Function):
 class LayerNorm2d(nn.LayerNorm):
     """LayerNorm over the channel dim of an NCHW tensor (timm's LayerNorm2d).  bf16 channels_last
     CUDA activations (the stem / downsample stream of the B200 model) go through
-    cnx_layernorm_fwd/bwd; anything else (the oracle on CPU, the 1x1 head) takes the PyTorch op."""
+    cnx_layernorm_fwd/bwd (the pooled [B,C,1,1] map of the head included); anything else (the
+    oracle on CPU) takes the PyTorch op."""
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         C = x.shape[1]
         if (x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 4 and C % 8 == 0 and C <= 1024
-                and x.shape[2] * x.shape[3] > 1 and x.permute(0, 2, 3, 1).is_contiguous()
-                and self.weight.dtype == torch.float32):
+                and x.permute(0, 2, 3, 1).is_contiguous() and self.weight.dtype == torch.float32):
             return _LayerNorm2dFn.apply(x, self.weight, self.bias, self.eps)
         y = x.permute(0, 2, 3, 1)
         y = F.layer_norm(y, self.normalized_shape, self.weight, self.bias, self.eps)
@@ -233,10 +235,42 @@ class ConvNeXtStage(nn.Module):
         return self.blocks(self.downsample(x))
 
 
+class _GlobalAvgPoolFn(torch.autograd.Function):
+    """[B,C,H,W] bf16 channels_last -> [B,C,1,1] bf16: cnx_avgpool_nhwc_fwd / _bwd."""
+
+    @staticmethod
+    def forward(ctx, x):
+        ctx.hw = x.shape[2:]
+        y = ops.avgpool_nhwc_fwd(x.permute(0, 2, 3, 1))
+        return y.view(y.shape[0], y.shape[1], 1, 1)
+
+    @staticmethod
+    def backward(ctx, g):
+        B, C = g.shape[:2]
+        g2 = g.reshape(B, C).to(torch.bfloat16).contiguous()
+        return ops.avgpool_nhwc_bwd(g2, *ctx.hw).permute(0, 3, 1, 2)
+
+
+class GlobalAvgPoolB200(nn.AdaptiveAvgPool2d):
+    """`nn.AdaptiveAvgPool2d(1)` (head.global_pool, /root/reference/train_advanced_v4.py:140, and the
+    auxiliary classifiers, :119-121) reading the bf16 channels_last stream in place; any other
+    input takes the PyTorch op."""
+
+    def __init__(self, output_size=1):
+        super().__init__(output_size)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if (self.output_size in (1, (1, 1)) and x.is_cuda and x.dtype == torch.bfloat16
+                and x.dim() == 4 and x.shape[1] % 8 == 0 and x.shape[0] <= 65535
+                and x.permute(0, 2, 3, 1).is_contiguous()):
+            return _GlobalAvgPoolFn.apply(x)
+        return super().forward(x)
+
+
 class _Head(nn.Module):
     def __init__(self, dim: int, num_classes: int):
         super().__init__()
-        self.global_pool = nn.AdaptiveAvgPool2d(1)
+        self.global_pool = GlobalAvgPoolB200(1)
         self.norm = LayerNorm2d(dim, eps=1e-6)
         self.flatten = nn.Flatten(1)
         self.drop = nn.Dropout(0.0)
@@ -277,6 +311,48 @@ class ConvNeXtTimmLike(nn.Module):
 
     def forward(self, x):
         return self.head(self.forward_features(x))
+
+
+class DeepSupervisionModelB200(nn.Module):
+    """The wrapper `create_model` puts around the backbone when `cfg.use_deep_supervision` is set
+    (config.py:22; /root/reference/train_advanced_v4.py:96-152, :494-495): same attributes
+    (`base_model`, `aux_classifiers`), same forward (stem, stages, then head.global_pool / norm /
+    flatten / fc child by child — `head.drop` is skipped there too) and the same return value
+    `[main_out] + aux_outs`.  The training loop keeps `outputs[0]` only (:219-220), so the three
+    auxiliary heads never receive a gradient; `compute_aux=False` skips their
+    forward and returns `[main_out]`."""
+
+    def __init__(self, base_model: nn.Module, num_classes: int, compute_aux: bool = True):
+        super().__init__()
+        self.base_model = base_model
+        if not hasattr(base_model, "stages"):
+            raise NotImplementedError("Deep supervision only implemented for ConvNeXt")   # :115
+        channels = []
+        for stage in base_model.stages[1:]:
+            last_block = stage.blocks[-1]
+            if hasattr(last_block, "conv_dw"):
+                channels.append(last_block.conv_dw.out_channels)
+            elif hasattr(last_block, "dwconv"):
+                channels.append(last_block.dwconv.out_channels)
+            else:
+                raise NotImplementedError("cannot read the block's channel count")         # :113
+        self.aux_classifiers = nn.ModuleList([
+            nn.Sequential(GlobalAvgPoolB200(1), nn.Flatten(), nn.Linear(dim, num_classes))
+            for dim in channels])
+        self.compute_aux = compute_aux
+
+    def forward(self, x):
+        features = []
+        x = self.base_model.stem(x)
+        for i, stage in enumerate(self.base_model.stages):
+            x = stage(x)
+            if i > 0:
+                features.append(x)
+        head = self.base_model.head
+        main_out = head.fc(head.flatten(head.norm(head.global_pool(x))))
+        if not self.compute_aux:
+            return [main_out]
+        return [main_out] + [clf(f) for f, clf in zip(features, self.aux_classifiers)]
 
 
 def create_convnext(name: str = "convnext_base", num_classes: int = 44, block_cls=ConvNeXtBlockB200,

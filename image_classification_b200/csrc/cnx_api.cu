@@ -149,6 +149,18 @@ int cnx_colsum_bf16(const void* x, float* out, int64_t M, int C, void* stream) {
   return colsum_bf16(x, out, M, C, as_stream(stream));
 }
 
+int cnx_avgpool_nhwc_fwd(const void* x, void* y, int B, int HW, int C, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(y);
+  return avgpool_nhwc_fwd(x, y, B, HW, C, as_stream(stream));
+}
+
+int cnx_avgpool_nhwc_bwd(const void* g, void* dx, int B, int HW, int C, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(g); CNX_REQUIRE_PTR(dx);
+  return avgpool_nhwc_bwd(g, dx, B, HW, C, as_stream(stream));
+}
+
 int cnx_layernorm_bwd(const void* dy, const void* x, const float* weight, const float* mean,
                       const float* rstd, void* dx, float* dweight, float* dbias, int64_t M, int C,
                       void* stream) {

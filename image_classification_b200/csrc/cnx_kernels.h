@@ -27,6 +27,8 @@ int ln_affine_fwd(const void* x, const float* w, const float* b, void* y, float*
 int patchify_nchw_f32(const float* x, void* P, int B, int Cin, int H, int W, int k,
                       cudaStream_t stream);   // layout.cu
 int colsum_bf16(const void* x, float* out, int64_t M, int C, cudaStream_t stream);   // ln_rows.cu
+int avgpool_nhwc_fwd(const void* x, void* y, int B, int HW, int C, cudaStream_t stream);
+int avgpool_nhwc_bwd(const void* g, void* dx, int B, int HW, int C, cudaStream_t stream);
 int ln_affine_bwd(const void* g, const void* x, const float* w, const float* mean,
                   const float* rstd, void* dx, float* dw, float* db, int64_t M, int C,
                   int pH, int pW, int pk, cudaStream_t stream);

@@ -382,6 +382,57 @@ colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out,
   for (int i = threadIdx.x; i < C; i += kColsumThreads) atomicAdd(out + i, s_cs[i]);
 }
 
+// Global average pool of an NHWC bf16 map, [B, HW, C] -> [B, C] (head.global_pool and the three
+// auxiliary classifiers of the reference's DeepSupervisionModel).  A CTA owns one image and a
+// 64-channel slab: 8 vector lanes x 32 row lanes, row lanes meet in shared memory in a fixed order
+// (deterministic).  Backward is the broadcast dx[b, p, c] = g[b, c] / HW.
+constexpr int kPoolThreads = 256;
+__global__ void __launch_bounds__(kPoolThreads)
+avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int HW, int C,
+                   float inv_hw) {
+  __shared__ float s_part[32][65];
+  const int v = threadIdx.x & 7, rl = threadIdx.x >> 3;
+  const int c0 = blockIdx.x * 64 + v * 8;
+  const __nv_bfloat16* xb = x + static_cast<int64_t>(blockIdx.y) * HW * C;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (c0 < C) {
+    for (int r = rl; r < HW; r += 32) {
+      float f[8];
+      unpack8(ld_v4(xb + static_cast<int64_t>(r) * C + c0), f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += f[k];
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s_part[rl][v * 8 + k] = acc[k];
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    const int c = blockIdx.x * 64 + threadIdx.x;
+    if (c < C) {
+      float t = 0.f;
+#pragma unroll
+      for (int r = 0; r < 32; ++r) t += s_part[r][threadIdx.x];
+      y[static_cast<int64_t>(blockIdx.y) * C + c] = __float2bfloat16_rn(t * inv_hw);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kPoolThreads)
+avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ g, __nv_bfloat16* __restrict__ dx, int HW,
+                   int nvec, int64_t total_vec, float inv_hw) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * kPoolThreads;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * kPoolThreads + threadIdx.x; i < total_vec;
+       i += stride) {
+    const int v = static_cast<int>(i % nvec);
+    const int64_t b = i / nvec / HW;
+    float f[8];
+    unpack8(ld_v4(g + (b * nvec + v) * 8), f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[k] *= inv_hw;
+    st_v4(dx + i * 8, pack8(f));
+  }
+}
+
 int launch_status(const char* who) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
@@ -503,6 +554,32 @@ int colsum_bf16(const void* x, float* out, int64_t M, int C, cudaStream_t stream
   colsum_bf16_kernel<<<grid, kColsumThreads, sizeof(float) * C, stream>>>(
       static_cast<const __nv_bfloat16*>(x), out, M, C, static_cast<int>(rpc));
   return launch_status("colsum_bf16");
+}
+
+int avgpool_nhwc_fwd(const void* x, void* y, int B, int HW, int C, cudaStream_t stream) {
+  if (B <= 0 || HW <= 0 || C <= 0 || (C % 8) != 0 || B > 65535) {
+    set_last_error("avgpool_nhwc_fwd: bad shape B=%d HW=%d C=%d (C must be a multiple of 8)", B, HW, C);
+    return CNX_ERR_BAD_SHAPE;
+  }
+  dim3 grid((C + 63) / 64, B);
+  avgpool_fwd_kernel<<<grid, kPoolThreads, 0, stream>>>(static_cast<const __nv_bfloat16*>(x),
+                                                         static_cast<__nv_bfloat16*>(y), HW, C,
+                                                         1.0f / static_cast<float>(HW));
+  return launch_status("avgpool_nhwc_fwd");
+}
+
+int avgpool_nhwc_bwd(const void* g, void* dx, int B, int HW, int C, cudaStream_t stream) {
+  if (B <= 0 || HW <= 0 || C <= 0 || (C % 8) != 0) {
+    set_last_error("avgpool_nhwc_bwd: bad shape B=%d HW=%d C=%d (C must be a multiple of 8)", B, HW, C);
+    return CNX_ERR_BAD_SHAPE;
+  }
+  const int64_t total_vec = static_cast<int64_t>(B) * HW * (C >> 3);
+  int64_t grid = (total_vec + kPoolThreads - 1) / kPoolThreads;
+  if (grid > 16 * sm_count()) grid = 16 * sm_count();
+  avgpool_bwd_kernel<<<static_cast<unsigned>(grid), kPoolThreads, 0, stream>>>(
+      static_cast<const __nv_bfloat16*>(g), static_cast<__nv_bfloat16*>(dx), HW, C >> 3, total_vec,
+      1.0f / static_cast<float>(HW));
+  return launch_status("avgpool_nhwc_bwd");
 }
 
 }  // namespace cnx

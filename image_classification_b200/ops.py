@@ -191,6 +191,24 @@ def patchify_nchw_f32(x: torch.Tensor, patch: int) -> torch.Tensor:
     return P
 
 
+def avgpool_nhwc_fwd(x: torch.Tensor) -> torch.Tensor:
+    """[B, H, W, C] bf16 (contiguous NHWC) -> [B, C] bf16 mean over the pixels."""
+    _chk(x, torch.bfloat16, "x")
+    B, H, W, C = x.shape
+    y = torch.empty(B, C, device=x.device, dtype=torch.bfloat16)
+    _lib.call("cnx_avgpool_nhwc_fwd", _p(x), _p(y), B, H * W, C, _stream(x))
+    return y
+
+
+def avgpool_nhwc_bwd(g: torch.Tensor, H: int, W: int) -> torch.Tensor:
+    """[B, C] bf16 gradient of the pooled map -> [B, H, W, C] bf16 (g / (H*W) at every pixel)."""
+    _chk(g, torch.bfloat16, "g")
+    B, C = g.shape
+    dx = torch.empty(B, H, W, C, device=g.device, dtype=torch.bfloat16)
+    _lib.call("cnx_avgpool_nhwc_bwd", _p(g), _p(dx), B, H * W, C, _stream(g))
+    return dx
+
+
 def colsum_bf16(x2d: torch.Tensor) -> torch.Tensor:
     """[M, C] bf16 -> [C] fp32 column sums."""
     _chk(x2d, torch.bfloat16, "x")

@@ -152,6 +152,12 @@ int cnx_patchify_nchw_f32(const float* x, void* P, int B, int Cin, int H, int W,
 /* out[c] = sum_m x[m,c] for a bf16 [M,C] matrix (fp32 result, overwritten): the bias gradient of the
  * stem / downsample convolutions (sum of grad_output over batch and space in NHWC). */
 int cnx_colsum_bf16(const void* x, float* out, int64_t M, int C, void* stream);
+/* Global average pool over the pixels of an NHWC bf16 map: y[b,c] = mean_p x[b,p,c] (fp32 sum,
+ * bf16 result) and its backward dx[b,p,c] = g[b,c] / HW.  Replaces `nn.AdaptiveAvgPool2d(1)` of
+ * head.global_pool (/root/reference/train_advanced_v4.py:140) and of the auxiliary classifiers
+ * (:119-121) on the channels-last stream.  C % 8 == 0. */
+int cnx_avgpool_nhwc_fwd(const void* x, void* y, int B, int HW, int C, void* stream);
+int cnx_avgpool_nhwc_bwd(const void* g, void* dx, int B, int HW, int C, void* stream);
 
 /* Generic tensor-core GEMM: D[M,N] = epilogue(A[M,K] * B[N,K]^T), bf16 in, fp32 accumulate.
  * a_mn_major / b_mn_major != 0: the operand is stored [K, rows] (row-major) instead. */

@@ -30,10 +30,14 @@ class EMARef:
                 self.shadow[name] = new_average.clone()
 
 
-def build_oracle_model(name: str = "convnext_base", num_classes: int = 44, ls_init_value=1e-6):
-    from image_classification_b200.convnext import create_convnext   # skeleton only (pure torch)
-    return create_convnext(name, num_classes, block_cls=block_oracle.OracleConvNeXtBlock,
+def build_oracle_model(name: str = "convnext_base", num_classes: int = 44, ls_init_value=1e-6,
+                       deep_supervision: bool = False):
+    # skeleton / wrapper only: on CPU tensors every module of these classes is the plain PyTorch op
+    from image_classification_b200.convnext import create_convnext, DeepSupervisionModelB200
+    base = create_convnext(name, num_classes, block_cls=block_oracle.OracleConvNeXtBlock,
                            ls_init_value=ls_init_value)
+    # config.py:22 use_deep_supervision = True -> DeepSupervisionModel(base, num_classes) (:494-495)
+    return DeepSupervisionModelB200(base, num_classes) if deep_supervision else base
 
 
 def reference_cpu_step(model, optimizer, scheduler, ema, images, labels, *, accum: int,
@@ -46,6 +50,8 @@ def reference_cpu_step(model, optimizer, scheduler, ema, images, labels, *, accu
             images[i].numpy(), labels[i].numpy(), mixup_alpha=0.2, cutmix_alpha=1.0, prob=0.5,
             num_classes=num_classes, rng=rng)                                 # :593-599
         out = model(torch.from_numpy(mixed))                                  # :240
+        if isinstance(out, list):
+            out = out[0]                                                      # :241-242
         loss = criterion(out, torch.from_numpy(targets)) / accum              # :243-244
         loss.backward()                                                       # :245
         last = float(loss.item())                                             # :268

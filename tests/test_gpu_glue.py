@@ -11,6 +11,11 @@ pytestmark = pytest.mark.gpu
 from oracle import block_oracle, mix_oracle  # noqa: E402  (checker only)
 
 
+def _rel(a, b):
+    a, b = a.double(), b.double()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
 def _dev():
     assert torch.cuda.is_available(), "GPU tests need a B200"
     return torch.device("cuda:0")
@@ -511,3 +516,98 @@ def test_timm_batch_mixup_bit_exact_vs_oracle(cnx_lib, cfg):
     assert "mix" in modes
     with pytest.raises(Exception):
         mixer(torch.zeros(5, 3, 8, 8, device=dev), torch.zeros(5, dtype=torch.long, device=dev))
+
+
+# ------------------------------------------------------------------ head: pool (+norm), aux heads
+@pytest.mark.parametrize("shape", [(128, 7, 7, 1024), (16, 14, 14, 512), (5, 28, 28, 256),
+                                   (3, 5, 3, 96), (2, 1, 1, 64), (4, 24, 24, 384)])
+def test_avgpool_nhwc_fwd_bwd_vs_fp64(cnx_lib, shape):
+    """cnx_avgpool_nhwc_fwd/_bwd against the definition in fp64 (bf16 rounding of the result only)."""
+    from image_classification_b200 import ops
+    dev = _dev()
+    B, H, W, C = shape
+    torch.manual_seed(B * 131 + C)
+    x = (torch.randn(B, H, W, C, device=dev) + 0.5).bfloat16()
+    y = ops.avgpool_nhwc_fwd(x)
+    ref = x.double().mean(dim=(1, 2))
+    assert y.shape == (B, C) and y.dtype == torch.bfloat16
+    assert torch.equal(y, ref.to(torch.bfloat16)) or \
+        float((y.double() - ref).abs().max()) <= 2 ** -8 * float(ref.abs().max())
+    g = torch.randn(B, C, device=dev).bfloat16()
+    dx = ops.avgpool_nhwc_bwd(g, H, W)
+    want = (g.float() * (1.0 / (H * W))).to(torch.bfloat16)[:, None, None, :].expand(B, H, W, C)
+    assert torch.equal(dx, want)
+
+
+def test_avgpool_rejects_bad_shapes(cnx_lib):
+    from image_classification_b200 import ops, _lib
+    dev = _dev()
+    with pytest.raises(_lib.CnxError):
+        ops.avgpool_nhwc_fwd(torch.zeros(2, 3, 3, 12, device=dev, dtype=torch.bfloat16))   # C % 8
+    with pytest.raises(_lib.CnxError):
+        ops.avgpool_nhwc_fwd(torch.zeros(2, 3, 3, 16, device=dev))                         # fp32
+
+
+def test_head_pool_norm_on_library_matches_torch(cnx_lib):
+    """head.global_pool + head.norm on the channels_last bf16 stream (f-1) vs the PyTorch ops in fp32."""
+    from image_classification_b200 import _lib
+    from image_classification_b200.convnext import _Head
+    dev = _dev()
+    torch.manual_seed(5)
+    head = _Head(512, 44).to(dev)
+    with torch.no_grad():
+        head.norm.weight.copy_(torch.rand(512, device=dev) + 0.5)
+        head.norm.bias.copy_(torch.randn(512, device=dev) * 0.1)
+    x0 = torch.randn(8, 512, 7, 7, device=dev)
+    xa = x0.bfloat16().contiguous(memory_format=torch.channels_last).requires_grad_()
+    xb = xa.detach().float().requires_grad_()
+    n0 = _lib.launch_count
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        ya = head(xa)
+    assert _lib.launch_count - n0 == 2            # pool + layernorm rows
+    p = xb.mean(dim=(2, 3))
+    yb = torch.nn.functional.linear(
+        torch.nn.functional.layer_norm(p, (512,), head.norm.weight, head.norm.bias, 1e-6),
+        head.fc.weight, head.fc.bias)
+    g = torch.randn_like(yb)
+    ya.backward(g.to(ya.dtype))
+    yb.backward(g)
+    assert _rel(ya.float(), yb) < 2e-2
+    assert _rel(xa.grad.float(), xb.grad) < 3e-2
+    assert xa.grad.is_contiguous(memory_format=torch.channels_last)
+
+
+def test_deep_supervision_wrapper_mirrors_reference(cnx_lib):
+    """DeepSupervisionModelB200 = the reference's DeepSupervisionModel (:96-152): [main] + 3 aux
+    outputs, aux heads get no gradient from the loop's outputs[0] loss; compute_aux=False drops them."""
+    from image_classification_b200.convnext import ConvNeXtTimmLike, DeepSupervisionModelB200
+    dev = _dev()
+    torch.manual_seed(2)
+    base = ConvNeXtTimmLike((1, 1, 1, 1), (64, 128, 256, 512), 44).to(dev)
+    model = DeepSupervisionModelB200(base, 44).to(dev)
+    assert [c[2].in_features for c in model.aux_classifiers] == [128, 256, 512]
+    assert sorted(k.split(".")[0] for k in model.state_dict()).count("aux_classifiers") == 6
+    x = torch.randn(4, 3, 64, 64, device=dev)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        outs = model(x)
+        plain = base(x)
+    assert isinstance(outs, list) and len(outs) == 4 and all(o.shape == (4, 44) for o in outs)
+    assert torch.equal(outs[0], plain)
+    # aux head i = Linear(mean over pixels of stage i+1's output)
+    feats = []
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        h = base.stem(x)
+        for i, st in enumerate(base.stages):
+            h = st(h)
+            if i > 0:
+                feats.append(h)
+    for f, clf, o in zip(feats, model.aux_classifiers, outs[1:]):
+        want = torch.nn.functional.linear(f.float().mean(dim=(2, 3)), clf[2].weight, clf[2].bias)
+        assert _rel(o.float(), want) < 2e-2
+    outs[0].float().sum().backward()
+    assert all(p.grad is None for p in model.aux_classifiers.parameters())
+    assert all(p.grad is not None for p in base.parameters())
+    model.compute_aux = False
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        only = model(x)
+    assert len(only) == 1 and torch.equal(only[0], plain)
