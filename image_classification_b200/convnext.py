@@ -355,6 +355,66 @@ class DeepSupervisionModelB200(nn.Module):
         return [main_out] + [clf(f) for f, clf in zip(features, self.aux_classifiers)]
 
 
+def _as_layernorm2d(m: nn.Module) -> nn.Module:
+    if isinstance(m, LayerNorm2d) or not isinstance(m, nn.LayerNorm) or not m.elementwise_affine:
+        return m
+    new = LayerNorm2d(m.normalized_shape[0], eps=m.eps)
+    new.weight, new.bias = m.weight, m.bias          # the same Parameter objects
+    return new.train(m.training)
+
+
+def _as_patch_conv(c: nn.Module) -> nn.Module:
+    if isinstance(c, PatchConv2d) or not isinstance(c, nn.Conv2d) or c.bias is None:
+        return c
+    if c.kernel_size != c.stride or c.padding != (0, 0) or c.groups != 1 or c.dilation != (1, 1):
+        return c
+    new = PatchConv2d(c.in_channels, c.out_channels, kernel_size=c.kernel_size, stride=c.stride)
+    new.weight, new.bias = c.weight, c.bias
+    return new.train(c.training)
+
+
+def swap_trunk(model: nn.Module) -> int:
+    """The f-1 counterpart of `block.swap_blocks` for a timm-style ConvNeXt built elsewhere
+    (`timm.create_model('convnext_base', ...)`, /root/reference/train_advanced_v4.py:488-492):
+    `stem` -> StemB200, `stages[i].downsample` -> DownsampleB200, `head.global_pool` ->
+    GlobalAvgPoolB200, `head.norm` -> this module's LayerNorm2d.  The new modules hold the SAME
+    Parameter objects under the same names, so `state_dict()`, the optimizer and the EMA shadow are
+    untouched.  Anything that does not look like timm's layout is left alone.  Returns the number
+    of modules replaced."""
+    n = 0
+    stem = getattr(model, "stem", None)
+    if (isinstance(stem, nn.Sequential) and not isinstance(stem, StemB200) and len(stem) == 2
+            and isinstance(stem[0], nn.Conv2d) and isinstance(stem[1], nn.LayerNorm)):
+        conv = _as_patch_conv(stem[0])
+        if isinstance(conv, PatchConv2d):
+            model.stem = StemB200(conv, _as_layernorm2d(stem[1]))
+            n += 1
+    for stage in getattr(model, "stages", []):
+        ds = getattr(stage, "downsample", None)
+        if (isinstance(ds, nn.Sequential) and not isinstance(ds, DownsampleB200) and len(ds) == 2
+                and isinstance(ds[0], nn.LayerNorm) and isinstance(ds[1], nn.Conv2d)):
+            conv = _as_patch_conv(ds[1])
+            if isinstance(conv, PatchConv2d):
+                stage.downsample = DownsampleB200(_as_layernorm2d(ds[0]), conv)
+                n += 1
+    head = getattr(model, "head", None)
+    if head is not None:
+        gp = getattr(head, "global_pool", None)
+        # nn.AdaptiveAvgPool2d(1), or timm's SelectAdaptivePool2d('avg') that leaves flattening to
+        # head.flatten
+        is_avg1 = (isinstance(gp, nn.AdaptiveAvgPool2d) and gp.output_size in (1, (1, 1))) or \
+                  (getattr(gp, "pool_type", None) == "avg"
+                   and isinstance(getattr(gp, "flatten", None), nn.Identity))
+        if is_avg1 and not isinstance(gp, GlobalAvgPoolB200):
+            head.global_pool = GlobalAvgPoolB200(1)
+            n += 1
+        norm = getattr(head, "norm", None)
+        if isinstance(norm, nn.LayerNorm) and not isinstance(norm, LayerNorm2d):
+            head.norm = _as_layernorm2d(norm)
+            n += 1
+    return n
+
+
 def create_convnext(name: str = "convnext_base", num_classes: int = 44, block_cls=ConvNeXtBlockB200,
                     ls_init_value: float = 1e-6) -> ConvNeXtTimmLike:
     """Stand-in for `timm.create_model(name, pretrained=False, num_classes=...)`."""

@@ -176,3 +176,36 @@ def test_grad_window_matches_per_microbatch_accumulation(cnx_lib):
     again = run(None)                                   # detached: back to the plain path
     for n in ref:
         assert torch.allclose(again[n], ref[n], rtol=1e-4, atol=1e-6), n
+
+
+def test_swap_blocks_plus_swap_trunk_equals_native_model(cnx_lib):
+    """A timm-style ConvNeXt built from foreign torch modules, after swap_blocks + swap_trunk, runs
+    the same kernels as the model create_convnext builds: identical logits and gradients."""
+    from _foreign import _foreign_convnext
+    from image_classification_b200 import _lib
+    from image_classification_b200.block import swap_blocks
+    from image_classification_b200.convnext import ConvNeXtTimmLike, swap_trunk
+    dev = _dev()
+    torch.manual_seed(0)
+    depths, dims = (1, 1, 2, 1), (64, 128, 256, 512)
+    foreign = _foreign_convnext(depths, dims).to(dev)
+    native = ConvNeXtTimmLike(depths, dims, 44).to(dev)
+    sd = {k: v.clone() for k, v in foreign.state_dict().items()}
+    assert swap_blocks(foreign) == sum(depths) and swap_trunk(foreign) == 6
+    assert sorted(foreign.state_dict()) == sorted(sd)
+    native.load_state_dict(sd)
+    x = torch.randn(4, 3, 64, 64, device=dev)
+    outs, grads, launches = [], [], []
+    for m in (foreign, native):
+        n0 = _lib.launch_count
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            y = m(x)
+        y.float().square().sum().backward()
+        launches.append(_lib.launch_count - n0)
+        outs.append(y)
+        grads.append({n: p.grad.clone() for n, p in m.named_parameters()})
+    assert launches[0] == launches[1] and launches[0] > 0
+    assert torch.equal(outs[0], outs[1])
+    # the split-K weight-gradient reductions are atomic (order varies run to run): compare loosely
+    for n in grads[0]:
+        assert _rel(grads[0][n], grads[1][n]) < 1e-3, n

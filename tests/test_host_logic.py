@@ -167,3 +167,26 @@ def test_timm_batch_mixup_planner_follows_oracle_rng_order():
                 box = np.zeros((16, 24), dtype=bool)
                 box[plan["bby1"][0]:plan["bby2"][0], plan["bbx1"][0]:plan["bbx2"][0]] = True
                 assert np.array_equal(pasted.numpy(), box)
+
+
+def test_swap_trunk_keeps_parameters_names_and_results():
+    """swap_trunk (f-1): stem / downsample / head pool + norm of a foreign timm-style model become
+    the B200 modules around the SAME Parameter objects; on CPU they fall back to the PyTorch ops, so
+    the logits must not change at all."""
+    from image_classification_b200.convnext import (DownsampleB200, GlobalAvgPoolB200, LayerNorm2d,
+                                                    StemB200, swap_trunk)
+    from _foreign import _foreign_convnext
+    torch.manual_seed(0)
+    m = _foreign_convnext((1, 1, 1, 1), (16, 32, 64, 128)).eval()
+    x = torch.randn(2, 3, 64, 64)
+    before = m(x)
+    keys = list(m.state_dict())
+    params = {n: p for n, p in m.named_parameters()}
+    assert swap_trunk(m) == 1 + 3 + 2
+    assert isinstance(m.stem, StemB200) and isinstance(m.head.global_pool, GlobalAvgPoolB200)
+    assert isinstance(m.head.norm, LayerNorm2d)
+    assert all(isinstance(st.downsample, DownsampleB200) for st in m.stages[1:])
+    assert list(m.state_dict()) == keys
+    assert all(p is params[n] for n, p in m.named_parameters())
+    assert torch.equal(m(x), before)
+    assert swap_trunk(m) == 0                                     # idempotent
