@@ -70,7 +70,9 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    """nvidia-smi clocks / throttle reasons sampled every 100 ms.  The process is started during
+    warm-up (nvidia-smi needs ~0.2 s to come up) and `mark()` drops what it printed before the
+    timed region, so every remaining sample was taken under the timed load."""
 
     FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
               "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
@@ -83,7 +85,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}",
-                 "--format=csv,noheader,nounits", "-lms", "200"],
+                 "--format=csv,noheader,nounits", "-lms", "100"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._pump, daemon=True)
             self.thread.start()
@@ -93,6 +95,9 @@ class ClockSampler:
     def _pump(self):
         for line in self.proc.stdout:
             self.lines.append(line.strip())
+
+    def mark(self):
+        self.before, self.lines = self.lines[-1:], []
 
     def stop(self) -> dict:
         if self.proc is None:
@@ -104,7 +109,8 @@ class ClockSampler:
             self.proc.kill()
         sm, smax, power, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        # a timed region shorter than the sampling period: the last warm-up sample (same load)
+        for ln in (self.lines or getattr(self, "before", [])):
             parts = [p.strip() for p in ln.split(",")]
             if len(parts) < 7:
                 continue
@@ -384,15 +390,16 @@ def main_b200(args):
 
     tr = B200Trainer(device, world, rank, args.micro_batch, args.res)
     imgs_per_step = ACCUM * args.micro_batch * world
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
     for _ in range(max(3, args.warmup)):
         tr.step_resident()
     if tr.reducer is not None:
         tr.reducer.discover_unused()
     torch.cuda.synchronize(device)
 
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
+    sampler.mark()
     l0 = _lib.launch_count
     ms = timed_region(tr.step_resident, args.steps, world, device)
     launches = _lib.launch_count - l0
@@ -434,7 +441,7 @@ def main_b200(args):
             # element forward (work = 2*E*2 B), 98 backward (work = 4*E*2 B); peak = 128 FMA/clk/SM
             elems = d["work"] / (4.0 if name == "dwconv_ln_fwd" else 8.0)
             fmas = elems * (49.0 if name == "dwconv_ln_fwd" else 98.0)
-            sm_hz = (clocks or {}).get("sm_mhz", 1965.0) * 1e6
+            sm_hz = ((clocks or {}).get("sm_mhz") or 1965.0) * 1e6
             peak = 128.0 * SM_COUNT * sm_hz
             k["fma_pipe"] = {"achieved_tfma": round(fmas / d["ms"] * 1e-9, 2),
                              "peak_tfma": round(peak * 1e-12, 2),
