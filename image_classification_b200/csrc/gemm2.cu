@@ -419,9 +419,6 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
           continue;
         }
 
-        // staging buffers must have been drained by the previous chunk's TMA stores
-        if (lane == 0) tma_store_wait_read();
-        __syncwarp();
         if (kHasR) {
           mbar_wait(rbar, r_jobs & 1, p.timeout_flag);
           ++r_jobs;
@@ -473,19 +470,27 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
           uint32_t pk[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) pk[j] = f32x2_to_bf16x2(f[j].x, f[j].y);
-#pragma unroll
-          for (int k = 0; k < 4; ++k)
-            st_shared_v4(buf0_u + row_off + (((sub * 4 + k) ^ sw) << 4), pk[4 * k], pk[4 * k + 1],
-                         pk[4 * k + 2], pk[4 * k + 3]);
-
+          uint32_t hk[EPI == EPI_BIAS_GELU ? 16 : 1];
           if (EPI == EPI_BIAS_GELU) {
             // activation of the ROUNDED pre-activation (what backward will see), second output
-            uint32_t hk[16];
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
               const float2 h2 = gelu2(bf16x2_to_f32x2(pk[j]));
               hk[j] = f32x2_to_bf16x2(h2.x, h2.y);
             }
+          }
+          if (sub == 0) {
+            // the staging buffers must have been drained by the previous chunk's TMA stores; waiting
+            // here (not at the top of the chunk) lets the drain overlap this chunk's first TMEM
+            // read and arithmetic
+            if (lane == 0) tma_store_wait_read();
+            __syncwarp();
+          }
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            st_shared_v4(buf0_u + row_off + (((sub * 4 + k) ^ sw) << 4), pk[4 * k], pk[4 * k + 1],
+                         pk[4 * k + 2], pk[4 * k + 3]);
+          if (EPI == EPI_BIAS_GELU) {
 #pragma unroll
             for (int k = 0; k < 4; ++k)
               st_shared_v4(buf1_u + row_off + (((sub * 4 + k) ^ sw) << 4), hk[4 * k],
