@@ -20,6 +20,7 @@ SOURCES = [
     "cnx_util.cu",
     "cnx_api.cu",
     "dwconv7.cu",
+    "dwconvk.cu",
     "ln_rows.cu",
     "gemm2.cu",
     "elementwise.cu",

@@ -149,6 +149,24 @@ int cnx_colsum_bf16(const void* x, float* out, int64_t M, int C, void* stream) {
   return colsum_bf16(x, out, M, C, as_stream(stream));
 }
 
+int cnx_dwconv_kxk_fwd(const void* x, const float* wt, void* y, int B, int H, int W, int C, int k,
+                       int stride, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(wt); CNX_REQUIRE_PTR(y);
+  return dwconv_kxk_fwd(x, wt, y, B, H, W, C, k, stride, as_stream(stream));
+}
+
+int cnx_dwconv_kxk_bwd(const void* dy, const void* x, const float* wt, void* dx, float* dwt, int B,
+                       int H, int W, int C, int k, int stride, int accumulate, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(dy); CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(wt);
+  if (dx == nullptr && dwt == nullptr) {
+    set_last_error("cnx_dwconv_kxk_bwd: both dx and dwt are NULL, nothing to compute");
+    return CNX_ERR_BAD_ARG;
+  }
+  return dwconv_kxk_bwd(dy, x, wt, dx, dwt, B, H, W, C, k, stride, accumulate, as_stream(stream));
+}
+
 int cnx_avgpool_nhwc_fwd(const void* x, void* y, int B, int HW, int C, void* stream) {
   CNX_REQUIRE_DEVICE();
   CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(y);

@@ -21,6 +21,12 @@ int dwconv_bwd(const void* dconv, const void* x, const void* dy, const float* wt
                float* dwt, float* dbias, float* dy_colsum, int B, int H, int W, int C,
                int accumulate, cudaStream_t stream);
 
+// ---- dwconvk.cu : depthwise k x k (3 / 5), stride 1 / 2, NHWC bf16 (EfficientNet path, §8 f-4)
+int dwconv_kxk_fwd(const void* x, const float* wt, void* y, int B, int H, int W, int C, int k,
+                   int stride, cudaStream_t stream);
+int dwconv_kxk_bwd(const void* dy, const void* x, const float* wt, void* dx, float* dwt, int B,
+                   int H, int W, int C, int k, int stride, int accumulate, cudaStream_t stream);
+
 // ---- ln_rows.cu : LayerNorm with affine over [M, C] bf16 rows (stem / downsample LayerNorm2d)
 int ln_affine_fwd(const void* x, const float* w, const float* b, void* y, float* mean, float* rstd,
                   int64_t M, int C, float eps, int pH, int pW, int pk, cudaStream_t stream);

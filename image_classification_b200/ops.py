@@ -191,6 +191,43 @@ def patchify_nchw_f32(x: torch.Tensor, patch: int) -> torch.Tensor:
     return P
 
 
+def dwconv_kxk_fwd(x: torch.Tensor, wt: torch.Tensor, k: int, stride: int) -> torch.Tensor:
+    """x [B,H,W,C] bf16, wt [k*k, C] fp32 tap-major -> y [B,Ho,Wo,C] bf16 (padding k//2, no bias)."""
+    _chk(x, torch.bfloat16, "x")
+    _chk(wt, torch.float32, "wt")
+    B, H, W, C = x.shape
+    if wt.shape != (k * k, C):
+        raise _lib.CnxError(f"dwconv_kxk_fwd: wt must be [{k * k}, {C}], got {tuple(wt.shape)}")
+    p = k // 2
+    Ho, Wo = (H + 2 * p - k) // stride + 1, (W + 2 * p - k) // stride + 1
+    y = torch.empty(B, Ho, Wo, C, device=x.device, dtype=torch.bfloat16)
+    _lib.call("cnx_dwconv_kxk_fwd", _p(x), _p(wt), _p(y), B, H, W, C, k, stride, _stream(x))
+    return y
+
+
+def dwconv_kxk_bwd(dy: torch.Tensor, x: torch.Tensor, wt: torch.Tensor, k: int, stride: int, *,
+                   need_dx: bool = True, need_dw: bool = True, dwt_acc: torch.Tensor = None):
+    """-> (dx [B,H,W,C] bf16 or None, dwt [k*k, C] fp32 or None).  dwt_acc: += into this buffer."""
+    _chk(dy, torch.bfloat16, "dy")
+    _chk(x, torch.bfloat16, "x")
+    _chk(wt, torch.float32, "wt")
+    B, H, W, C = x.shape
+    p = k // 2
+    Ho, Wo = (H + 2 * p - k) // stride + 1, (W + 2 * p - k) // stride + 1
+    if dy.shape != (B, Ho, Wo, C) or wt.shape != (k * k, C):
+        raise _lib.CnxError(f"dwconv_kxk_bwd: dy {tuple(dy.shape)} / wt {tuple(wt.shape)} do not "
+                            f"match x {tuple(x.shape)}, k={k}, stride={stride}")
+    dx = torch.empty_like(x) if need_dx else None
+    dwt = None
+    if need_dw:
+        dwt = dwt_acc if dwt_acc is not None else torch.empty(k * k, C, device=x.device,
+                                                              dtype=torch.float32)
+        _chk(dwt, torch.float32, "dwt")
+    _lib.call("cnx_dwconv_kxk_bwd", _p(dy), _p(x), _p(wt), _p(dx), _p(dwt), B, H, W, C, k, stride,
+              int(dwt_acc is not None), _stream(x))
+    return dx, dwt
+
+
 def avgpool_nhwc_fwd(x: torch.Tensor) -> torch.Tensor:
     """[B, H, W, C] bf16 (contiguous NHWC) -> [B, C] bf16 mean over the pixels."""
     _chk(x, torch.bfloat16, "x")

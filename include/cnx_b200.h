@@ -152,6 +152,18 @@ int cnx_patchify_nchw_f32(const float* x, void* P, int B, int Cin, int H, int W,
 /* out[c] = sum_m x[m,c] for a bf16 [M,C] matrix (fp32 result, overwritten): the bias gradient of the
  * stem / downsample convolutions (sum of grad_output over batch and space in NHWC). */
 int cnx_colsum_bf16(const void* x, float* out, int64_t M, int C, void* stream);
+/* Depthwise k x k convolution, k in {3, 5}, stride in {1, 2}, padding k/2, no bias, NHWC bf16 with
+ * fp32 accumulation: the `conv_dw` of timm efficientnet_b2's DepthwiseSeparableConv /
+ * InvertedResidual blocks (model built at /root/reference/previous/V3-efb2/train_advanced_v3.0.py:330;
+ * SURVEY.md §8 f-4, BASELINE config 5).  Replaces F.conv2d(x, w, groups=C) and its autograd backward.
+ *   x  [B,H,W,C] bf16;  wt [k*k, C] fp32 tap-major (wt[kh*k+kw, c] = conv.weight[c, 0, kh, kw]);
+ *   y / dy [B,Ho,Wo,C] bf16 with Ho = (H + 2*(k/2) - k) / stride + 1.
+ * cnx_dwconv_kxk_bwd: dx [B,H,W,C] bf16 (may be NULL), dwt [k*k, C] fp32 (may be NULL; overwritten,
+ * or += when accumulate != 0).  C % 8 == 0. */
+int cnx_dwconv_kxk_fwd(const void* x, const float* wt, void* y, int B, int H, int W, int C, int k,
+                       int stride, void* stream);
+int cnx_dwconv_kxk_bwd(const void* dy, const void* x, const float* wt, void* dx, float* dwt, int B,
+                       int H, int W, int C, int k, int stride, int accumulate, void* stream);
 /* Global average pool over the pixels of an NHWC bf16 map: y[b,c] = mean_p x[b,p,c] (fp32 sum,
  * bf16 result) and its backward dx[b,p,c] = g[b,c] / HW.  Replaces `nn.AdaptiveAvgPool2d(1)` of
  * head.global_pool (/root/reference/train_advanced_v4.py:140) and of the auxiliary classifiers

@@ -1,0 +1,194 @@
+"""GPU parity for the depthwise-separable path (BASELINE config 5): the k x k
+depthwise kernels against oracle/dwsep_oracle.py (pinned to torch's conv2d on the CPU side) at
+small ragged shapes, against float64 conv2d on the device at EfficientNet-B2's own shapes, and
+torchvision's efficientnet_b2 with its convolutions swapped against the untouched fp32 model.
+bf16 tolerance 2e-2 of the tensor's max (the north-star's bf16 bound), written at each assert."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from oracle import dwsep_oracle  # noqa: E402  (checker only)
+
+BF16_REL = 2e-2
+
+
+def _dev():
+    assert torch.cuda.is_available(), "GPU tests need a B200"
+    return torch.device("cuda:0")
+
+
+def _rel(a, b):
+    a, b = a.double(), b.double()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def _tap_major(w4):          # [C,1,k,k] -> [k*k, C] fp32
+    C, _, k, _ = w4.shape
+    return w4.reshape(C, k * k).t().contiguous().float()
+
+
+@pytest.mark.parametrize("k,stride,B,H,W,C", [
+    (3, 1, 2, 7, 9, 16), (3, 2, 2, 8, 8, 24), (3, 2, 1, 9, 7, 8), (5, 1, 2, 6, 11, 40),
+    (5, 2, 2, 10, 13, 16), (5, 2, 1, 9, 9, 72), (3, 1, 1, 1, 1, 8), (5, 2, 3, 2, 3, 8),
+    (3, 1, 1, 5, 4, 264), (5, 1, 1, 3, 17, 96)])
+def test_dwconv_kxk_vs_oracle_small(cnx_lib, k, stride, B, H, W, C):
+    """ragged strips (W not a multiple of 4), single pixels, odd sizes with stride 2, C not a
+    power of two: bf16 inputs are exact in the oracle, so only the output rounding differs."""
+    from image_classification_b200 import ops
+    dev = _dev()
+    rng = np.random.RandomState(k * 1000 + stride * 100 + H * 10 + C)
+    x = torch.from_numpy(rng.randn(B, H, W, C).astype(np.float32)).bfloat16()
+    w4 = torch.from_numpy(rng.randn(C, 1, k, k).astype(np.float32) * 0.3).bfloat16().float()
+    wn = w4[:, 0].permute(1, 2, 0).double().numpy()                 # [k,k,C]
+    y_ref = dwsep_oracle.dwconv_fwd_ref(x.double().numpy(), wn, stride)
+    wt = _tap_major(w4).to(dev)
+    y = ops.dwconv_kxk_fwd(x.to(dev), wt, k, stride)
+    assert tuple(y.shape) == y_ref.shape
+    assert _rel(y.cpu(), torch.from_numpy(y_ref)) < 2.0 ** -8            # one bf16 rounding
+    dy = torch.from_numpy(rng.randn(*y_ref.shape).astype(np.float32)).bfloat16()
+    dx_ref, dw_ref = dwsep_oracle.dwconv_bwd_ref(dy.double().numpy(), x.double().numpy(), wn, stride)
+    dx, dwt = ops.dwconv_kxk_bwd(dy.to(dev), x.to(dev), wt, k, stride)
+    assert _rel(dx.cpu(), torch.from_numpy(dx_ref)) < 2.0 ** -8
+    assert _rel(dwt.cpu(), torch.from_numpy(dw_ref).reshape(k * k, C)) < 1e-5   # fp32 sums
+    # accumulate mode adds on top; dx-only / dw-only calls
+    dx2, dwt2 = ops.dwconv_kxk_bwd(dy.to(dev), x.to(dev), wt, k, stride, dwt_acc=dwt.clone())
+    assert _rel(dwt2, 2 * dwt) < 1e-5 and torch.equal(dx2, dx)
+    only_dx, none = ops.dwconv_kxk_bwd(dy.to(dev), x.to(dev), wt, k, stride, need_dw=False)
+    assert none is None and torch.equal(only_dx, dx)
+    none, only_dw = ops.dwconv_kxk_bwd(dy.to(dev), x.to(dev), wt, k, stride, need_dx=False)
+    assert none is None and _rel(only_dw, dwt) < 1e-5
+
+
+# (k, stride, C, H) of every depthwise convolution in efficientnet_b2 at 260x260
+EFFNET_B2_DW = [(3, 1, 32, 130), (3, 1, 16, 130), (3, 2, 96, 130), (3, 1, 144, 65), (5, 2, 144, 65),
+                (5, 1, 288, 33), (3, 2, 288, 33), (3, 1, 528, 17), (5, 1, 528, 17), (5, 1, 720, 17),
+                (5, 2, 720, 17), (5, 1, 1248, 9), (3, 1, 1248, 9), (3, 1, 2112, 9)]
+
+
+@pytest.mark.parametrize("k,stride,C,H", EFFNET_B2_DW)
+def test_dwconv_kxk_effnet_b2_shapes_vs_conv2d_fp64(cnx_lib, k, stride, C, H):
+    """Batch 48 (previous/V3-efb2/config.py:14) at the network's own shapes, against
+    F.conv2d(groups=C) + autograd in float64 on the device."""
+    from image_classification_b200 import ops
+    dev = _dev()
+    B = 48 if C * H * H <= 96 * 130 * 130 else 16
+    torch.manual_seed(C + H)
+    x = torch.randn(B, C, H, H, device=dev).bfloat16()
+    w4 = (torch.randn(C, 1, k, k, device=dev) * 0.2).bfloat16().float()
+    xr = x.double().requires_grad_()
+    wr = w4.double().requires_grad_()
+    yr = F.conv2d(xr, wr, stride=stride, padding=k // 2, groups=C)
+    g = torch.randn_like(yr).bfloat16()
+    yr.backward(g.double())
+    xn = x.permute(0, 2, 3, 1).contiguous()
+    wt = _tap_major(w4)
+    y = ops.dwconv_kxk_fwd(xn, wt, k, stride)
+    assert _rel(y.permute(0, 3, 1, 2), yr.detach()) < 2.0 ** -8
+    dx, dwt = ops.dwconv_kxk_bwd(g.permute(0, 2, 3, 1).contiguous(), xn, wt, k, stride)
+    assert _rel(dx.permute(0, 3, 1, 2), xr.grad) < 2.0 ** -8
+    assert _rel(dwt.t().reshape(C, 1, k, k), wr.grad) < 1e-4          # fp32 atomics over 10^5 terms
+
+
+def test_dwconv_kxk_rejects_bad_arguments(cnx_lib):
+    from image_classification_b200 import ops, _lib
+    dev = _dev()
+    x = torch.zeros(1, 4, 4, 16, device=dev, dtype=torch.bfloat16)
+    with pytest.raises(_lib.CnxError):
+        ops.dwconv_kxk_fwd(x, torch.zeros(49, 16, device=dev), 7, 1)           # k = 7: dwconv7 path
+    with pytest.raises(_lib.CnxError):
+        ops.dwconv_kxk_fwd(x, torch.zeros(9, 16, device=dev), 3, 3)            # stride 3
+    with pytest.raises(_lib.CnxError):
+        ops.dwconv_kxk_fwd(x[..., :12].contiguous(), torch.zeros(9, 12, device=dev), 3, 1)   # C % 8
+    with pytest.raises(_lib.CnxError):
+        ops.dwconv_kxk_fwd(x.float(), torch.zeros(9, 16, device=dev), 3, 1)    # fp32 activations
+
+
+@pytest.mark.parametrize("cfg", [(96, 24, 65, False), (144, 48, 33, False), (32, 16, 130, False),
+                                 (528, 88, 17, True), (352, 1408, 9, False)])
+def test_pointwise_conv_module_matches_conv2d(cnx_lib, cfg):
+    """1x1 convolutions of the MBConv blocks (expand / project / head widths, N and K far from
+    tile multiples) through the tcgen05 GEMM vs nn.Conv2d in fp32."""
+    from image_classification_b200 import _lib
+    from image_classification_b200.efficientnet import PointwiseConv2dB200
+    dev = _dev()
+    Cin, Cout, H, bias = cfg
+    torch.manual_seed(Cin + Cout)
+    conv = PointwiseConv2dB200(Cin, Cout, 1, bias=bias).to(dev)
+    x0 = torch.randn(16, Cin, H, H, device=dev)          # >= PointwiseConv2dB200.min_rows pixels
+    xa = x0.bfloat16().contiguous(memory_format=torch.channels_last).requires_grad_()
+    xb = xa.detach().float().requires_grad_()
+    n0 = _lib.launch_count
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        ya = conv(xa)
+    assert _lib.launch_count > n0 and ya.dtype == torch.bfloat16
+    wq = conv.weight.detach().bfloat16().float()          # the GEMM sees bf16 weights (autocast)
+    yb = F.conv2d(xb, wq, conv.bias)
+    g = torch.randn_like(yb).bfloat16()
+    ya.backward(g)
+    gw, gb = conv.weight.grad.clone(), None if conv.bias is None else conv.bias.grad.clone()
+    conv.weight.grad = None
+    yb.backward(g.float())
+    assert _rel(ya.float(), yb) < BF16_REL
+    assert _rel(xa.grad.float(), xb.grad) < BF16_REL
+    wref = torch.autograd.grad(F.conv2d(xb.detach(), conv.weight, conv.bias), conv.weight, g.float())[0]
+    assert _rel(gw, wref) < 1e-3
+    if bias:
+        assert _rel(gb, g.float().sum(dim=(0, 2, 3))) < 1e-4
+
+
+def test_efficientnet_b2_swapped_vs_fp32_model(cnx_lib):
+    """torchvision efficientnet_b2 (same architecture as timm's, random init, 44 classes) with its
+    23 depthwise and 45 large 1x1 convolutions on libcnx_b200 under bf16 autocast, against the
+    untouched model in fp32: logits, loss and gradient norm within the bf16 bound."""
+    import copy
+    import torchvision
+    from image_classification_b200 import _lib
+    from image_classification_b200.efficientnet import swap_depthwise_separable
+    dev = _dev()
+    torch.manual_seed(0)
+    ref = torchvision.models.efficientnet_b2(weights=None, num_classes=44).to(dev).train()
+    for m in ref.modules():                       # no stochastic depth / dropout: same function twice
+        if isinstance(m, torchvision.ops.StochasticDepth):
+            m.p = 0.0
+        if isinstance(m, torch.nn.Dropout):
+            m.p = 0.0
+    prod = copy.deepcopy(ref)
+    amp = copy.deepcopy(ref).to(memory_format=torch.channels_last)       # PyTorch's own bf16 path
+    assert swap_depthwise_separable(prod) == (23, 49)
+    prod = prod.to(memory_format=torch.channels_last)
+    x = torch.randn(16, 3, 260, 260, device=dev)         # 9x9 maps x 16 >= min_rows of the 1x1 path
+    labels = torch.randint(0, 44, (16,), device=dev)
+    crit = torch.nn.CrossEntropyLoss()                                  # train_advanced_v3.0.py:449
+    lo = ref(x)
+    loss_o = crit(lo, labels)
+    loss_o.backward()
+    xcl = x.contiguous(memory_format=torch.channels_last)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        la = amp(xcl)
+        loss_a = crit(la.float(), labels)
+    loss_a.backward()
+    n0 = _lib.launch_count
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        lp = prod(xcl)
+        loss_p = crit(lp.float(), labels)
+    loss_p.backward()
+    # 23 depthwise fwd + 23 x 2 bwd + 45 pointwise x (1 fwd + 2 bwd) (+ split-K zero fills are torch's)
+    assert _lib.launch_count - n0 >= 23 * 3 + 45 * 3 - 1
+
+    def gnorm(m):
+        return float(torch.sqrt(sum((p.grad.double() ** 2).sum() for p in m.parameters())))
+
+    # 100+ bf16 layers with batch-statistics BatchNorm in between: the yardstick is how far
+    # PyTorch's own bf16 autocast path (cuDNN / cuBLAS kernels) lands from the fp32 model
+    e_amp, e_prod = _rel(la.float(), lo), _rel(lp.float(), lo)
+    assert e_prod < max(1.5 * e_amp, BF16_REL), (e_prod, e_amp)
+    assert e_prod < 0.15, e_prod
+    d_amp = abs(loss_a.item() - loss_o.item()) / abs(loss_o.item())
+    d_prod = abs(loss_p.item() - loss_o.item()) / abs(loss_o.item())
+    assert d_prod < max(1.5 * d_amp, BF16_REL), (d_prod, d_amp)
+    g_o, g_a, g_p = gnorm(ref), gnorm(amp), gnorm(prod)
+    assert abs(g_p - g_o) < max(1.5 * abs(g_a - g_o), 5e-2 * g_o), (g_p, g_a, g_o)
+    assert all(p.grad is not None and p.grad.dtype == torch.float32 for p in prod.parameters())

@@ -5,6 +5,7 @@ import subprocess
 import sys
 
 import pytest
+import numpy as np
 import torch
 
 from conftest import ROOT
@@ -190,3 +191,50 @@ def test_swap_trunk_keeps_parameters_names_and_results():
     assert all(p is params[n] for n, p in m.named_parameters())
     assert torch.equal(m(x), before)
     assert swap_trunk(m) == 0                                     # idempotent
+
+
+@pytest.mark.parametrize("k,stride,H,W", [(3, 1, 7, 9), (3, 2, 8, 8), (3, 2, 9, 7), (5, 1, 6, 11),
+                                          (5, 2, 10, 13), (5, 2, 9, 9), (3, 1, 1, 1), (5, 2, 2, 3)])
+def test_dwsep_oracle_pinned_to_torch_conv2d(k, stride, H, W):
+    """oracle/dwsep_oracle.py against torch.nn.functional.conv2d (+ autograd) in float64: the op
+    timm's efficientnet blocks call (previous/V3-efb2/train_advanced_v3.0.py:330)."""
+    from oracle import dwsep_oracle as o
+    torch.manual_seed(k * 100 + stride * 10 + H)
+    B, C = 2, 6
+    x = torch.randn(B, C, H, W, dtype=torch.float64, requires_grad=True)
+    w = torch.randn(C, 1, k, k, dtype=torch.float64, requires_grad=True)
+    y = torch.nn.functional.conv2d(x, w, stride=stride, padding=k // 2, groups=C)
+    g = torch.randn_like(y)
+    y.backward(g)
+    xn = x.detach().permute(0, 2, 3, 1).numpy()
+    wn = w.detach()[:, 0].permute(1, 2, 0).numpy()
+    yo = o.dwconv_fwd_ref(xn, wn, stride)
+    assert yo.shape == (B, o.out_size(H, k, stride), o.out_size(W, k, stride), C)
+    np.testing.assert_allclose(yo, y.detach().permute(0, 2, 3, 1).numpy(), rtol=1e-12, atol=1e-12)
+    dxo, dwo = o.dwconv_bwd_ref(g.permute(0, 2, 3, 1).numpy(), xn, wn, stride)
+    np.testing.assert_allclose(dxo, x.grad.permute(0, 2, 3, 1).numpy(), rtol=1e-12, atol=1e-12)
+    np.testing.assert_allclose(dwo, w.grad[:, 0].permute(1, 2, 0).numpy(), rtol=1e-12, atol=1e-12)
+
+
+def test_swap_depthwise_separable_on_cpu_keeps_parameters_and_results():
+    """f-4: the swapped convolutions hold the same Parameter objects and, off the fast path (CPU),
+    are plain nn.Conv2d: identical logits, identical state_dict keys."""
+    import torchvision
+    from image_classification_b200.efficientnet import (DepthwiseConv2dB200, PointwiseConv2dB200,
+                                                        swap_depthwise_separable)
+    torch.manual_seed(0)
+    m = torchvision.models.efficientnet_b2(weights=None, num_classes=44).eval()
+    x = torch.randn(1, 3, 64, 64)
+    before = m(x)
+    keys = list(m.state_dict())
+    params = {n: p for n, p in m.named_parameters()}
+    n_dw, n_pw = swap_depthwise_separable(m)
+    # 23 depthwise; 45 expand / project / head 1x1 convs + the 4 squeeze-excite ones whose channel
+    # counts are multiples of 8 (those stay on nn.Conv2d.forward at run time: [B,C,1,1] maps)
+    assert (n_dw, n_pw) == (23, 49)
+    assert sum(isinstance(c, DepthwiseConv2dB200) for c in m.modules()) == 23
+    assert sum(isinstance(c, PointwiseConv2dB200) for c in m.modules()) == 49
+    assert list(m.state_dict()) == keys
+    assert all(p is params[n] for n, p in m.named_parameters())
+    assert torch.equal(m(x), before)
+    assert swap_depthwise_separable(m) == (0, 0)

@@ -1,0 +1,3 @@
+#!/bin/bash
+cd "${GRAFT_REPO_ROOT:-/root/repo}"; mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_dwsep.py -q -m gpu -p no:cacheprovider > gpurun_out/test_dwsep.log 2>&1; echo "exit=$?"; grep -E "^(E  |FAILED)" gpurun_out/test_dwsep.log | cut -c1-250 | head -40; tail -3 gpurun_out/test_dwsep.log
