@@ -21,6 +21,7 @@ SOURCES = [
     "cnx_api.cu",
     "dwconv7.cu",
     "dwconvk.cu",
+    "bnse.cu",
     "ln_rows.cu",
     "gemm2.cu",
     "elementwise.cu",

@@ -179,6 +179,54 @@ int cnx_avgpool_nhwc_bwd(const void* g, void* dx, int B, int HW, int C, void* st
   return avgpool_nhwc_bwd(g, dx, B, HW, C, as_stream(stream));
 }
 
+int cnx_bn_stats(const void* x, float* sums, int64_t M, int C, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(sums);
+  return bn_stats(x, sums, M, C, as_stream(stream));
+}
+
+int cnx_bn_act_fwd(const void* x, const float* sums, const float* weight, const float* bias,
+                   float* running_mean, float* running_var, float momentum, float eps, int act,
+                   void* y, float* mean_out, float* rstd_out, float* pool_sum, int B, int HW, int C,
+                   void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(weight); CNX_REQUIRE_PTR(bias); CNX_REQUIRE_PTR(y);
+  CNX_REQUIRE_PTR(mean_out); CNX_REQUIRE_PTR(rstd_out);
+  return bn_act_fwd(x, sums, weight, bias, running_mean, running_var, momentum, eps, act, y,
+                    mean_out, rstd_out, pool_sum, B, HW, C, as_stream(stream));
+}
+
+int cnx_bn_act_bwd(const void* g, const void* x, const float* weight, const float* bias,
+                   const float* mean, const float* rstd, int act, void* dx, float* dweight,
+                   float* dbias, int64_t M, int C, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(g); CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(weight); CNX_REQUIRE_PTR(bias);
+  CNX_REQUIRE_PTR(mean); CNX_REQUIRE_PTR(rstd); CNX_REQUIRE_PTR(dx); CNX_REQUIRE_PTR(dweight);
+  CNX_REQUIRE_PTR(dbias);
+  return bn_act_bwd(g, x, weight, bias, mean, rstd, act, dx, dweight, dbias, M, C,
+                    as_stream(stream));
+}
+
+int cnx_se_scale_fwd(const void* x, const float* gate, void* y, int B, int HW, int C, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(gate); CNX_REQUIRE_PTR(y);
+  return se_scale_fwd(x, gate, y, B, HW, C, as_stream(stream));
+}
+
+int cnx_se_scale_bwd_reduce(const void* g, const void* x, float* dgate, int B, int HW, int C,
+                            void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(g); CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(dgate);
+  return se_scale_bwd_reduce(g, x, dgate, B, HW, C, as_stream(stream));
+}
+
+int cnx_se_scale_bwd_apply(const void* g, const float* gate, const float* dpool, void* dx, int B,
+                           int HW, int C, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(g); CNX_REQUIRE_PTR(gate); CNX_REQUIRE_PTR(dpool); CNX_REQUIRE_PTR(dx);
+  return se_scale_bwd_apply(g, gate, dpool, dx, B, HW, C, as_stream(stream));
+}
+
 int cnx_layernorm_bwd(const void* dy, const void* x, const float* weight, const float* mean,
                       const float* rstd, void* dx, float* dweight, float* dbias, int64_t M, int C,
                       void* stream) {

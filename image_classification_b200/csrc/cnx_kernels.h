@@ -27,6 +27,22 @@ int dwconv_kxk_fwd(const void* x, const float* wt, void* y, int B, int H, int W,
 int dwconv_kxk_bwd(const void* dy, const void* x, const float* wt, void* dx, float* dwt, int B,
                    int H, int W, int C, int k, int stride, int accumulate, cudaStream_t stream);
 
+// ---- bnse.cu : BatchNorm2d (batch statistics) + SiLU, squeeze-excite scaling (EfficientNet path)
+int bn_stats(const void* x, float* sums, int64_t M, int C, cudaStream_t stream);
+int bn_act_fwd(const void* x, const float* sums, const float* weight, const float* bias,
+               float* running_mean, float* running_var, float momentum, float eps, int act, void* y,
+               float* mean_out, float* rstd_out, float* pool_sum, int B, int HW, int C,
+               cudaStream_t stream);
+int bn_act_bwd(const void* g, const void* x, const float* weight, const float* bias,
+               const float* mean, const float* rstd, int act, void* dx, float* dweight,
+               float* dbias, int64_t M, int C, cudaStream_t stream);
+int se_scale_fwd(const void* x, const float* gate, void* y, int B, int HW, int C,
+                 cudaStream_t stream);
+int se_scale_bwd_reduce(const void* g, const void* x, float* dgate, int B, int HW, int C,
+                        cudaStream_t stream);
+int se_scale_bwd_apply(const void* g, const float* gate, const float* dpool, void* dx, int B,
+                       int HW, int C, cudaStream_t stream);
+
 // ---- ln_rows.cu : LayerNorm with affine over [M, C] bf16 rows (stem / downsample LayerNorm2d)
 int ln_affine_fwd(const void* x, const float* w, const float* b, void* y, float* mean, float* rstd,
                   int64_t M, int C, float eps, int pH, int pW, int pk, cudaStream_t stream);

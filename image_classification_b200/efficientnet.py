@@ -15,8 +15,17 @@ module moves the two convolution kinds onto the library:
 Both are `nn.Conv2d` subclasses holding the SAME Parameter objects after
 `swap_depthwise_separable(model)`, so `state_dict()`, the optimizer and SWA / EMA copies are
 untouched; inputs that do not fit the fast path (CPU tensors, no bf16 autocast, odd shapes, the
-[B,C,1,1] squeeze-excite convolutions) take `nn.Conv2d.forward`.  BatchNorm, SiLU and squeeze-excite
-stay PyTorch ops in this first slice of f-4.  timm is not installable here; the
+[B,C,1,1] squeeze-excite convolutions) take `nn.Conv2d.forward`.  The memory-bound glue between
+the convolutions is on the library too (csrc/bnse.cu):
+
+* `BatchNormActB200`     — `nn.BatchNorm2d` (+ the SiLU that follows it) -> `cnx_bn_stats` +
+  `cnx_bn_act_fwd`, backward `cnx_bn_act_bwd`; running statistics updated like nn.BatchNorm2d;
+* `SqueezeExciteB200`    — x * sigmoid(fc2(silu(fc1(mean x)))): the pooled sums come out of the
+  preceding `BatchNormActB200` pass, the two [B,C] layers are fp32 PyTorch ops (a few kFLOP), the
+  scaling and its backward are `cnx_se_scale_*`;
+* `swap_efficientnet(model)` installs all four kinds.
+
+timm is not installable here; the
 swap is written against `nn.Conv2d` attributes only, so it applies to timm's and torchvision's
 EfficientNets alike (the parity tests use torchvision's `efficientnet_b2`, same architecture).
 """
@@ -25,7 +34,7 @@ from __future__ import annotations
 import torch
 from torch import nn
 
-from . import ops
+from . import _lib, ops
 
 
 def _autocast_bf16() -> bool:
@@ -171,3 +180,175 @@ def swap_depthwise_separable(model: nn.Module) -> tuple[int, int]:
                 setattr(parent, name, _rebind(child, PointwiseConv2dB200))
                 n_pw += 1
     return n_dw, n_pw
+
+
+# ----------------------------------------------------------------------- BatchNorm (+ SiLU)
+class _BnActFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, running_mean, running_var, training, momentum, eps, act,
+                want_pool):
+        xn = _nhwc_bf16(x)
+        w, b = weight.detach().float().contiguous(), bias.detach().float().contiguous()
+        y, mean, rstd, pool = ops.bn_act_fwd(xn, w, b, running_mean, running_var, training=training,
+                                             momentum=momentum, eps=eps, act=act, want_pool=want_pool)
+        ctx.save_for_backward(xn, w, b, mean, rstd)
+        ctx.act, ctx.training, ctx.x_dtype = act, training, x.dtype
+        if pool is None:
+            pool = xn.new_empty(0)
+        ctx.mark_non_differentiable(pool)
+        return y.permute(0, 3, 1, 2), pool
+
+    @staticmethod
+    def backward(ctx, g, _gpool):
+        if not ctx.training:
+            raise _lib.CnxError("BatchNormActB200: backward through eval-mode statistics is not "
+                                "implemented (the reference never trains in eval mode)")
+        xn, w, b, mean, rstd = ctx.saved_tensors
+        dx, dw, db = ops.bn_act_bwd(_nhwc_bf16(g), xn, w, b, mean, rstd, ctx.act)
+        dx = dx.permute(0, 3, 1, 2)
+        if ctx.x_dtype != torch.bfloat16:
+            dx = dx.to(ctx.x_dtype)
+        return dx, dw, db, None, None, None, None, None, None, None
+
+
+class BatchNormActB200(nn.BatchNorm2d):
+    """`nn.BatchNorm2d` followed by `act` ("silu" or None) as ONE pass over the NHWC bf16 map
+    (plus the statistics pass in training).  `emit_pool`: also leave the per-image channel sums of
+    the output on the returned tensor (`_cnx_pool_sum`) for the squeeze-excite block that follows."""
+
+    act: str | None = None
+    emit_pool: bool = False
+
+    def _fast(self, x: torch.Tensor) -> bool:
+        return (x.is_cuda and x.dim() == 4 and self.affine and self.num_features % 8 == 0
+                and self.momentum is not None and self.weight.dtype == torch.float32
+                and (self.training or self.running_mean is not None)
+                and (x.dtype == torch.bfloat16 or (x.is_floating_point() and _autocast_bf16())))
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if not self._fast(x):
+            y = super().forward(x)
+            return torch.nn.functional.silu(y) if self.act == "silu" else y
+        training = self.training or self.running_mean is None
+        if training and self.num_batches_tracked is not None:
+            self.num_batches_tracked.add_(1)
+        y, pool = _BnActFn.apply(x, self.weight, self.bias, self.running_mean, self.running_var,
+                                 training, float(self.momentum), float(self.eps),
+                                 ops.ACT_SILU if self.act == "silu" else ops.ACT_NONE,
+                                 self.emit_pool)
+        if self.emit_pool:
+            y._cnx_pool_sum = pool
+        return y
+
+
+# ----------------------------------------------------------------------- squeeze-excite
+def _se_gate(pooled, w1, b1, w2, b2):
+    """[B,C] fp32 pooled means -> [B,C] fp32 gate (the two 1x1 convolutions on a 1x1 map)."""
+    h = torch.nn.functional.silu(torch.nn.functional.linear(pooled, w1, b1))
+    return torch.sigmoid(torch.nn.functional.linear(h, w2, b2))
+
+
+class _SqueezeExciteFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, pool_sum, w1, b1, w2, b2):
+        xn = _nhwc_bf16(x)
+        B, H, W, C = xn.shape
+        if pool_sum is not None and pool_sum.numel() == B * C:
+            pooled = pool_sum * (1.0 / (H * W))
+        else:
+            pooled = ops.avgpool_nhwc_fwd(xn).float()
+        params = [t.detach().float().reshape(t.shape[0], -1) if t.dim() == 4 else t.detach().float()
+                  for t in (w1, b1, w2, b2)]
+        gate = _se_gate(pooled, *params).contiguous()
+        y = ops.se_scale_fwd(xn, gate)
+        ctx.save_for_backward(xn, pooled, gate, *params)
+        ctx.x_dtype, ctx.w_shapes = x.dtype, (w1.shape, w2.shape)
+        return y.permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, g):
+        xn, pooled, gate, w1, b1, w2, b2 = ctx.saved_tensors
+        gn = _nhwc_bf16(g)
+        dgate = ops.se_scale_bwd_reduce(gn, xn)
+        with torch.enable_grad():                 # the [B,C] gate layers: a few kFLOP of PyTorch
+            leaves = [t.detach().requires_grad_() for t in (pooled, w1, b1, w2, b2)]
+            dpool, dw1, db1, dw2, db2 = torch.autograd.grad(_se_gate(*leaves), leaves, dgate)
+        dx = ops.se_scale_bwd_apply(gn, gate, dpool.contiguous()).permute(0, 3, 1, 2)
+        if ctx.x_dtype != torch.bfloat16:
+            dx = dx.to(ctx.x_dtype)
+        return dx, None, dw1.reshape(ctx.w_shapes[0]), db1, dw2.reshape(ctx.w_shapes[1]), db2
+
+
+class SqueezeExciteB200(nn.Module):
+    """Drop-in for torchvision `SqueezeExcitation` / timm `SqueezeExcite` with SiLU + sigmoid:
+    holds the SAME two 1x1 convolution modules under their original attribute names."""
+
+    def __init__(self, reduce_conv: nn.Conv2d, expand_conv: nn.Conv2d,
+                 names: tuple[str, str] = ("fc1", "fc2")):
+        super().__init__()
+        self._names = names
+        setattr(self, names[0], reduce_conv)
+        setattr(self, names[1], expand_conv)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        r, e = getattr(self, self._names[0]), getattr(self, self._names[1])
+        fast = (x.is_cuda and x.dim() == 4 and x.shape[1] % 8 == 0
+                and (x.dtype == torch.bfloat16 or (x.is_floating_point() and _autocast_bf16())))
+        if not fast:
+            s = torch.sigmoid(e(torch.nn.functional.silu(r(x.mean((2, 3), keepdim=True)))))
+            return s * x
+        return _SqueezeExciteFn.apply(x, getattr(x, "_cnx_pool_sum", None), r.weight, r.bias,
+                                      e.weight, e.bias)
+
+
+def _rebind_bn(bn: nn.BatchNorm2d, act: str | None) -> BatchNormActB200:
+    new = BatchNormActB200(bn.num_features, bn.eps, bn.momentum, bn.affine, bn.track_running_stats)
+    if bn.affine:
+        new.weight, new.bias = bn.weight, bn.bias                 # the same Parameter objects
+    if bn.track_running_stats:
+        new.running_mean, new.running_var = bn.running_mean, bn.running_var
+        new.num_batches_tracked = bn.num_batches_tracked
+    new.act = act
+    return new.train(bn.training)
+
+
+def _is_se(m: nn.Module) -> bool:
+    return (all(hasattr(m, a) for a in ("fc1", "fc2", "activation", "scale_activation"))
+            and isinstance(m.activation, nn.SiLU) and isinstance(m.scale_activation, nn.Sigmoid)
+            and isinstance(m.fc1, nn.Conv2d) and isinstance(m.fc2, nn.Conv2d)
+            and m.fc1.bias is not None and m.fc2.bias is not None)
+
+
+def swap_efficientnet(model: nn.Module) -> dict:
+    """Install the library modules in an EfficientNet built from conv -> BatchNorm2d -> SiLU
+    sequences and squeeze-excite blocks (torchvision's layout; timm's un-fused layout alike):
+    depthwise / 1x1 convolutions (`swap_depthwise_separable`), every `nn.BatchNorm2d` inside an
+    `nn.Sequential` (the `nn.SiLU` after it is absorbed and replaced by `nn.Identity`), and every
+    SiLU / sigmoid squeeze-excite block; the BatchNorm right before a squeeze-excite block also
+    emits its pooled sums.  Parameters and buffers are the same objects.  Returns the counts."""
+    n_dw, n_pw = swap_depthwise_separable(model)
+    n_bn = n_se = 0
+    for parent in list(model.modules()):
+        if not isinstance(parent, nn.Sequential):
+            continue
+        kids = list(parent.named_children())
+        for i, (name, child) in enumerate(kids):
+            if type(child) is nn.BatchNorm2d and child.affine and child.num_features % 8 == 0:
+                nxt = kids[i + 1] if i + 1 < len(kids) else None
+                act = "silu" if nxt is not None and type(nxt[1]) is nn.SiLU else None
+                setattr(parent, name, _rebind_bn(child, act))
+                if act:
+                    setattr(parent, nxt[0], nn.Identity())
+                n_bn += 1
+    for parent in list(model.modules()):
+        kids = list(parent.named_children())
+        for i, (name, child) in enumerate(kids):
+            if not _is_se(child):
+                continue
+            setattr(parent, name, SqueezeExciteB200(child.fc1, child.fc2).train(child.training))
+            n_se += 1
+            if i > 0 and isinstance(kids[i - 1][1], nn.Sequential):
+                tail = [m for m in kids[i - 1][1].children() if not isinstance(m, nn.Identity)]
+                if tail and isinstance(tail[-1], BatchNormActB200):
+                    tail[-1].emit_pool = True      # its output is exactly what this block pools
+    return {"depthwise": n_dw, "pointwise": n_pw, "batchnorm": n_bn, "squeeze_excite": n_se}

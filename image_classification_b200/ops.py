@@ -255,6 +255,95 @@ def colsum_bf16(x2d: torch.Tensor) -> torch.Tensor:
     return out
 
 
+# ------------------------------------------------------------------ BatchNorm + SiLU, squeeze-excite
+ACT_NONE, ACT_SILU = 0, 1
+
+
+def bn_act_fwd(x: torch.Tensor, weight, bias, running_mean, running_var, *, training: bool,
+               momentum: float, eps: float, act: int, want_pool: bool = False):
+    """x [B,H,W,C] bf16 NHWC -> (y bf16 same shape, mean [C], rstd [C], pool_sum [B,C] fp32 | None).
+    training: batch statistics (cnx_bn_stats), running buffers updated in place when given;
+    otherwise the running statistics normalise.  pool_sum = sum over the pixels of y per image."""
+    _chk(x, torch.bfloat16, "x")
+    B, H, W, C = x.shape
+    f32 = torch.float32
+    for n, t in (("weight", weight), ("bias", bias)):
+        _chk(t, f32, n)
+        if t.numel() != C:
+            raise _lib.CnxError(f"bn_act_fwd: {n} must have {C} elements, got {t.numel()}")
+    for n, t in (("running_mean", running_mean), ("running_var", running_var)):
+        if t is not None:
+            _chk(t, f32, n)
+    dev = x.device
+    sums = None
+    if training:
+        sums = torch.empty(2 * C, device=dev, dtype=f32)
+        _lib.call("cnx_bn_stats", _p(x), _p(sums), B * H * W, C, _stream(x))
+    y = torch.empty_like(x)
+    mean = torch.empty(C, device=dev, dtype=f32)
+    rstd = torch.empty(C, device=dev, dtype=f32)
+    pool = torch.empty(B, C, device=dev, dtype=f32) if want_pool else None
+    _lib.call("cnx_bn_act_fwd", _p(x), _p(sums), _p(weight), _p(bias), _p(running_mean),
+              _p(running_var), float(momentum), float(eps), int(act), _p(y), _p(mean), _p(rstd),
+              _p(pool), B, H * W, C, _stream(x))
+    return y, mean, rstd, pool
+
+
+def bn_act_bwd(g: torch.Tensor, x: torch.Tensor, weight, bias, mean, rstd, act: int):
+    """-> (dx bf16 like x, dweight [C] fp32, dbias [C] fp32) of y = act(bn(x)) with batch statistics."""
+    _chk(g, torch.bfloat16, "g")
+    _chk(x, torch.bfloat16, "x")
+    if g.shape != x.shape:
+        raise _lib.CnxError(f"bn_act_bwd: g {tuple(g.shape)} vs x {tuple(x.shape)}")
+    C = x.shape[-1]
+    M = x.numel() // C
+    for n, t in (("weight", weight), ("bias", bias), ("mean", mean), ("rstd", rstd)):
+        _chk(t, torch.float32, n)
+    dx = torch.empty_like(x)
+    dw = torch.empty(C, device=x.device, dtype=torch.float32)
+    db = torch.empty(C, device=x.device, dtype=torch.float32)
+    _lib.call("cnx_bn_act_bwd", _p(g), _p(x), _p(weight), _p(bias), _p(mean), _p(rstd), int(act),
+              _p(dx), _p(dw), _p(db), M, C, _stream(x))
+    return dx, dw, db
+
+
+def se_scale_fwd(x: torch.Tensor, gate: torch.Tensor) -> torch.Tensor:
+    """x [B,H,W,C] bf16, gate [B,C] fp32 -> x * gate[:, None, None, :] (bf16)."""
+    _chk(x, torch.bfloat16, "x")
+    _chk(gate, torch.float32, "gate")
+    B, H, W, C = x.shape
+    if tuple(gate.shape) != (B, C):
+        raise _lib.CnxError(f"se_scale_fwd: gate must be [{B}, {C}], got {tuple(gate.shape)}")
+    y = torch.empty_like(x)
+    _lib.call("cnx_se_scale_fwd", _p(x), _p(gate), _p(y), B, H * W, C, _stream(x))
+    return y
+
+
+def se_scale_bwd_reduce(g: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    """-> dgate [B,C] fp32 = sum over pixels of g * x."""
+    _chk(g, torch.bfloat16, "g")
+    _chk(x, torch.bfloat16, "x")
+    if g.shape != x.shape:
+        raise _lib.CnxError(f"se_scale_bwd_reduce: g {tuple(g.shape)} vs x {tuple(x.shape)}")
+    B, H, W, C = x.shape
+    dgate = torch.empty(B, C, device=x.device, dtype=torch.float32)
+    _lib.call("cnx_se_scale_bwd_reduce", _p(g), _p(x), _p(dgate), B, H * W, C, _stream(x))
+    return dgate
+
+
+def se_scale_bwd_apply(g: torch.Tensor, gate: torch.Tensor, dpool: torch.Tensor) -> torch.Tensor:
+    """-> dx = g * gate + dpool / (H*W), bf16 like g (dpool [B,C] fp32: gradient at the pooled mean)."""
+    _chk(g, torch.bfloat16, "g")
+    _chk(gate, torch.float32, "gate")
+    _chk(dpool, torch.float32, "dpool")
+    B, H, W, C = g.shape
+    if tuple(gate.shape) != (B, C) or tuple(dpool.shape) != (B, C):
+        raise _lib.CnxError(f"se_scale_bwd_apply: gate / dpool must be [{B}, {C}]")
+    dx = torch.empty_like(g)
+    _lib.call("cnx_se_scale_bwd_apply", _p(g), _p(gate), _p(dpool), _p(dx), B, H * W, C, _stream(g))
+    return dx
+
+
 # ------------------------------------------------------------------ MLP GEMMs
 EPI_STORE_BF16, EPI_BIAS_GELU, EPI_BIAS_RESIDUAL, EPI_GELU_GRAD, EPI_STORE_F32 = range(5)
 EPI_BIAS = 6

@@ -171,6 +171,43 @@ int cnx_dwconv_kxk_bwd(const void* dy, const void* x, const float* wt, void* dx,
 int cnx_avgpool_nhwc_fwd(const void* x, void* y, int B, int HW, int C, void* stream);
 int cnx_avgpool_nhwc_bwd(const void* g, void* dx, int B, int HW, int C, void* stream);
 
+/* BatchNorm2d with batch statistics (+ optional SiLU) over an NHWC bf16 map, the `bn1 / bn2 / bn3`
+ * (timm BatchNormAct2d) of efficientnet_b2's MBConv blocks (model built at
+ * /root/reference/previous/V3-efb2/train_advanced_v3.0.py:330; forward / backward :100-104;
+ * SURVEY.md §8 f-4).  Replaces F.batch_norm(training) -> F.silu and their autograd backward.
+ *   cnx_bn_stats   : sums[0..C) = sum_m x[m,c], sums[C..2C) = sum_m x[m,c]^2 (fp32, overwritten).
+ *   cnx_bn_act_fwd : y = act((x - mean) * rstd * weight + bias), act 0 = identity, 1 = SiLU.
+ *                    sums != NULL: training (mean / biased var from sums over M = B*HW rows;
+ *                    running_mean / running_var, when given, are updated with `momentum` and the
+ *                    unbiased variance like nn.BatchNorm2d).  sums == NULL: eval, statistics are
+ *                    running_mean / running_var.  mean_out / rstd_out [C] are saved for backward.
+ *                    pool_sum [B,C] fp32 (may be NULL; overwritten) = sum over the HW pixels of
+ *                    image b of y: the squeeze-excite average pool without another pass.
+ *   cnx_bn_act_bwd : dx [M,C] bf16, dweight [C], dbias [C] fp32 (overwritten) from g = dL/dy and
+ *                    the saved x, mean, rstd (u = xhat*w + b is recomputed for SiLU').
+ * C % 8 == 0. */
+int cnx_bn_stats(const void* x, float* sums, int64_t M, int C, void* stream);
+int cnx_bn_act_fwd(const void* x, const float* sums, const float* weight, const float* bias,
+                   float* running_mean, float* running_var, float momentum, float eps, int act,
+                   void* y, float* mean_out, float* rstd_out, float* pool_sum, int B, int HW, int C,
+                   void* stream);
+int cnx_bn_act_bwd(const void* g, const void* x, const float* weight, const float* bias,
+                   const float* mean, const float* rstd, int act, void* dx, float* dweight,
+                   float* dbias, int64_t M, int C, void* stream);
+/* Squeeze-excite scaling of an NHWC bf16 map by a per-image, per-channel gate (timm SqueezeExcite /
+ * torchvision SqueezeExcitation: x * sigmoid(fc2(silu(fc1(mean_p x))))); the two tiny [B,C] layers
+ * stay with the caller.
+ *   cnx_se_scale_fwd        : y[b,p,c] = x[b,p,c] * gate[b,c]              (gate fp32 [B,C])
+ *   cnx_se_scale_bwd_reduce : dgate[b,c] = sum_p g[b,p,c] * x[b,p,c]       (fp32, overwritten)
+ *   cnx_se_scale_bwd_apply  : dx[b,p,c] = g[b,p,c] * gate[b,c] + dpool[b,c] / HW, where dpool is
+ *                             the gradient that came back through the gate layers to the pooled
+ *                             mean: scaling path and pooling path in one pass.            */
+int cnx_se_scale_fwd(const void* x, const float* gate, void* y, int B, int HW, int C, void* stream);
+int cnx_se_scale_bwd_reduce(const void* g, const void* x, float* dgate, int B, int HW, int C,
+                            void* stream);
+int cnx_se_scale_bwd_apply(const void* g, const float* gate, const float* dpool, void* dx, int B,
+                           int HW, int C, void* stream);
+
 /* Generic tensor-core GEMM: D[M,N] = epilogue(A[M,K] * B[N,K]^T), bf16 in, fp32 accumulate.
  * a_mn_major / b_mn_major != 0: the operand is stored [K, rows] (row-major) instead. */
 int cnx_gemm_bf16(const void* A, int64_t lda, int a_mn_major, const void* B, int64_t ldb,

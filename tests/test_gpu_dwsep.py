@@ -192,3 +192,204 @@ def test_efficientnet_b2_swapped_vs_fp32_model(cnx_lib):
     g_o, g_a, g_p = gnorm(ref), gnorm(amp), gnorm(prod)
     assert abs(g_p - g_o) < max(1.5 * abs(g_a - g_o), 5e-2 * g_o), (g_p, g_a, g_o)
     assert all(p.grad is not None and p.grad.dtype == torch.float32 for p in prod.parameters())
+
+
+# ------------------------------------------------------------------ BatchNorm + SiLU, squeeze-excite
+@pytest.mark.parametrize("B,H,W,C,silu", [
+    (2, 3, 5, 8, True), (1, 1, 1, 16, True), (3, 7, 9, 24, False), (2, 6, 11, 88, True),
+    (1, 5, 4, 264, True), (4, 9, 9, 1408, False), (2, 33, 17, 144, True), (5, 2, 3, 2112, True)])
+def test_bn_act_vs_oracle_small(cnx_lib, B, H, W, C, silu):
+    """Batch-statistics BatchNorm (+SiLU) forward, running-buffer update, pooled sums and backward
+    against oracle/dwsep_oracle.py (pinned to F.batch_norm / F.silu on the CPU side) at ragged
+    shapes: C below / across / far above one 64-channel slab, a single pixel, odd row counts."""
+    from image_classification_b200 import ops
+    dev = _dev()
+    rng = np.random.RandomState(B * 1000 + H * 100 + C)
+    M, eps, mom = B * H * W, 1e-5, 0.1
+    x = torch.from_numpy((rng.randn(B, H, W, C) * 1.5 + 0.5).astype(np.float32)).bfloat16()
+    w = torch.from_numpy((rng.rand(C) + 0.5).astype(np.float32))
+    b = torch.from_numpy((rng.randn(C) * 0.3).astype(np.float32))
+    rm = torch.from_numpy(rng.randn(C).astype(np.float32))
+    rv = torch.from_numpy((rng.rand(C) + 0.5).astype(np.float32))
+    act = ops.ACT_SILU if silu else ops.ACT_NONE
+    x2 = x.double().numpy().reshape(M, C)
+    y_ref, mean_ref, var_ref = dwsep_oracle.bn_act_fwd_ref(x2, w.numpy(), b.numpy(), eps, silu)
+    rm_ref, rv_ref = dwsep_oracle.bn_running_update_ref(rm.numpy(), rv.numpy(), mean_ref, var_ref, M, mom)
+    rmd, rvd = rm.to(dev), rv.to(dev)
+    y, mean, rstd, pool = ops.bn_act_fwd(x.to(dev), w.to(dev), b.to(dev), rmd, rvd, training=True,
+                                         momentum=mom, eps=eps, act=act, want_pool=True)
+    if M > 1:           # a single row has zero variance: y = act(bias), rstd = eps^-1/2
+        assert _rel(y.cpu().reshape(M, C), torch.from_numpy(y_ref)) < 2.0 ** -7
+    assert _rel(mean.cpu(), torch.from_numpy(mean_ref)) < 1e-5
+    assert _rel(rstd.cpu(), torch.from_numpy(1.0 / np.sqrt(var_ref + eps))) < 1e-4
+    assert _rel(rmd.cpu(), torch.from_numpy(rm_ref)) < 1e-5
+    assert _rel(rvd.cpu(), torch.from_numpy(rv_ref)) < 1e-4
+    pool_ref = y.float().reshape(B, H * W, C).sum(dim=1)          # sums of the ROUNDED outputs
+    assert _rel(pool, pool_ref) < 1e-5
+    # the same call without the pooled sums takes the flat geometry: identical y
+    y2, *_ = ops.bn_act_fwd(x.to(dev), w.to(dev), b.to(dev), None, None, training=True,
+                            momentum=mom, eps=eps, act=act)
+    assert torch.equal(y2, y)
+    g = torch.from_numpy(rng.randn(B, H, W, C).astype(np.float32)).bfloat16()
+    dx_ref, dw_ref, db_ref = dwsep_oracle.bn_act_bwd_ref(g.double().numpy().reshape(M, C), x2, w.numpy(),
+                                                         b.numpy(), eps, silu)
+    dx, dw, db = ops.bn_act_bwd(g.to(dev), x.to(dev), w.to(dev), b.to(dev), mean, rstd, act)
+    if M > 1:
+        assert _rel(dx.cpu().reshape(M, C), torch.from_numpy(dx_ref)) < 2.0 ** -7
+        assert _rel(dw.cpu(), torch.from_numpy(dw_ref)) < 1e-4
+    assert _rel(db.cpu(), torch.from_numpy(db_ref)) < 1e-4
+    # eval mode: the (updated) running statistics normalise, buffers untouched
+    rm_before, rv_before = rmd.clone(), rvd.clone()
+    ye, *_ = ops.bn_act_fwd(x.to(dev), w.to(dev), b.to(dev), rmd, rvd, training=False,
+                            momentum=mom, eps=eps, act=act)
+    u = (x.double() - rm_before.cpu().double()) / torch.sqrt(rv_before.cpu().double() + eps) * w.double() + b.double()
+    ye_ref = u * torch.sigmoid(u) if silu else u
+    assert _rel(ye.cpu(), ye_ref) < 2.0 ** -7
+    assert torch.equal(rmd, rm_before) and torch.equal(rvd, rv_before)
+
+
+# (C, H) of the BatchNorm inputs of efficientnet_b2 at 260x260: expand, depthwise and project widths
+EFFNET_B2_BN = [(32, 130), (16, 130), (96, 130), (96, 65), (24, 65), (144, 65), (144, 33), (48, 33),
+                (288, 33), (288, 17), (88, 17), (528, 17), (120, 17), (720, 17), (720, 9), (208, 9),
+                (1248, 9), (352, 9), (2112, 9), (1408, 9)]
+
+
+@pytest.mark.parametrize("C,H", EFFNET_B2_BN)
+def test_bn_silu_effnet_b2_shapes_vs_torch_fp64(cnx_lib, C, H):
+    """Batch 48 (previous/V3-efb2/config.py:14) at the network's own shapes against
+    F.batch_norm(training) -> F.silu and autograd in float64 on the device."""
+    from image_classification_b200 import ops
+    dev = _dev()
+    B = 48
+    torch.manual_seed(C * 7 + H)
+    x = (torch.randn(B, H, H, C, device=dev) * 1.3 + 0.2).bfloat16()
+    w = torch.rand(C, device=dev) + 0.5
+    b = torch.randn(C, device=dev) * 0.2
+    xr = x.double().reshape(-1, C).requires_grad_()
+    wr, br = w.double().requires_grad_(), b.double().requires_grad_()
+    yr = F.silu(F.batch_norm(xr, None, None, wr, br, True, 0.1, 1e-5))
+    g = torch.randn(B, H, H, C, device=dev).bfloat16()
+    yr.backward(g.double().reshape(-1, C))
+    y, mean, rstd, _ = ops.bn_act_fwd(x, w, b, None, None, training=True, momentum=0.1, eps=1e-5,
+                                      act=ops.ACT_SILU)
+    assert _rel(y.reshape(-1, C), yr.detach()) < 2.0 ** -7                # bf16 rounding of y
+    dx, dw, db = ops.bn_act_bwd(g, x, w, b, mean, rstd, ops.ACT_SILU)
+    assert _rel(dx.reshape(-1, C), xr.grad) < BF16_REL
+    assert _rel(dw, wr.grad) < 1e-3                                       # fp32 sums over ~10^5..10^6 rows
+    assert _rel(db, br.grad) < 1e-3
+
+
+@pytest.mark.parametrize("B,H,W,C,Cs", [(2, 3, 5, 8, 2), (3, 1, 1, 16, 4), (2, 9, 7, 96, 4),
+                                        (4, 17, 17, 528, 22), (2, 5, 6, 2112, 88)])
+def test_squeeze_excite_vs_oracle(cnx_lib, B, H, W, C, Cs):
+    """se_scale kernels + SqueezeExciteB200 (fc1 / fc2 as fp32 [B,C] layers) against the oracle
+    (pinned to torchvision SqueezeExcitation): output, input gradient, all four parameter grads;
+    with and without the pooled sums handed over by the preceding BatchNorm pass."""
+    from image_classification_b200.efficientnet import SqueezeExciteB200
+    dev = _dev()
+    torch.manual_seed(B * 100 + C)
+    fc1 = torch.nn.Conv2d(C, Cs, 1).to(dev)
+    fc2 = torch.nn.Conv2d(Cs, C, 1).to(dev)
+    with torch.no_grad():
+        fc1.weight.mul_(3.0), fc2.weight.mul_(3.0)            # gates away from 0.5
+    se = SqueezeExciteB200(fc1, fc2)
+    x = torch.randn(B, C, H, W, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    g = torch.randn(B, C, H, W, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    w1, b1 = fc1.weight.detach().reshape(Cs, C).cpu().numpy(), fc1.bias.detach().cpu().numpy()
+    w2, b2 = fc2.weight.detach().reshape(C, Cs).cpu().numpy(), fc2.bias.detach().cpu().numpy()
+    xn = x.permute(0, 2, 3, 1).reshape(B, H * W, C).double().cpu().numpy()
+    gn = g.permute(0, 2, 3, 1).reshape(B, H * W, C).double().cpu().numpy()
+    y_ref, _ = dwsep_oracle.se_fwd_ref(xn, w1, b1, w2, b2)
+    dx_ref, dw1, db1, dw2, db2 = dwsep_oracle.se_bwd_ref(gn, xn, w1, b1, w2, b2)
+    for handed in (False, True):
+        xa = x.clone().requires_grad_()
+        if handed:
+            xa._cnx_pool_sum = x.permute(0, 2, 3, 1).float().sum(dim=(1, 2))
+        for p in se.parameters():
+            p.grad = None
+        y = se(xa)
+        y.backward(g)
+        flat = lambda t: t.permute(0, 2, 3, 1).reshape(B, H * W, C).cpu()
+        assert _rel(flat(y), torch.from_numpy(y_ref)) < 2.0 ** -7
+        assert _rel(flat(xa.grad), torch.from_numpy(dx_ref)) < 2.0 ** -7
+        assert _rel(fc1.weight.grad.reshape(Cs, C).cpu(), torch.from_numpy(dw1)) < 1e-3
+        assert _rel(fc1.bias.grad.cpu(), torch.from_numpy(db1)) < 1e-3
+        assert _rel(fc2.weight.grad.reshape(C, Cs).cpu(), torch.from_numpy(dw2)) < 1e-3
+        assert _rel(fc2.bias.grad.cpu(), torch.from_numpy(db2)) < 1e-3
+
+
+def test_bn_se_reject_bad_arguments(cnx_lib):
+    from image_classification_b200 import ops, _lib
+    dev = _dev()
+    x = torch.zeros(2, 4, 4, 16, device=dev, dtype=torch.bfloat16)
+    w = torch.ones(16, device=dev)
+    with pytest.raises(_lib.CnxError):                        # C % 8
+        ops.bn_act_fwd(x[..., :12].contiguous(), w[:12], w[:12], None, None, training=True,
+                       momentum=0.1, eps=1e-5, act=0)
+    with pytest.raises(_lib.CnxError):                        # unknown activation
+        ops.bn_act_fwd(x, w, w, None, None, training=True, momentum=0.1, eps=1e-5, act=7)
+    with pytest.raises(_lib.CnxError):                        # eval mode without running statistics
+        ops.bn_act_fwd(x, w, w, None, None, training=False, momentum=0.1, eps=1e-5, act=0)
+    with pytest.raises(_lib.CnxError):                        # fp32 activations
+        ops.bn_act_fwd(x.float(), w, w, None, None, training=True, momentum=0.1, eps=1e-5, act=0)
+    with pytest.raises(_lib.CnxError):                        # gate of the wrong shape
+        ops.se_scale_fwd(x, torch.ones(2, 8, device=dev))
+
+
+def test_efficientnet_b2_fully_swapped_vs_fp32_model(cnx_lib):
+    """torchvision efficientnet_b2 with convolutions, BatchNorm+SiLU and squeeze-excite all on
+    libcnx_b200 (swap_efficientnet) under bf16 autocast, one training forward/backward with the
+    reference's criterion, against the untouched fp32 model; PyTorch's own bf16 autocast path is
+    the yardstick for how far 100+ bf16 layers may drift.  Running statistics must match too."""
+    import copy
+    import torchvision
+    from image_classification_b200 import _lib
+    from image_classification_b200.efficientnet import swap_efficientnet
+    dev = _dev()
+    torch.manual_seed(0)
+    ref = torchvision.models.efficientnet_b2(weights=None, num_classes=44).to(dev).train()
+    for m in ref.modules():
+        if isinstance(m, (torchvision.ops.StochasticDepth, torch.nn.Dropout)):
+            m.p = 0.0
+    prod = copy.deepcopy(ref)
+    amp = copy.deepcopy(ref).to(memory_format=torch.channels_last)
+    counts = swap_efficientnet(prod)
+    assert counts == {"depthwise": 23, "pointwise": 49, "batchnorm": 69, "squeeze_excite": 23}
+    prod = prod.to(memory_format=torch.channels_last)
+    x = torch.randn(16, 3, 260, 260, device=dev)
+    labels = torch.randint(0, 44, (16,), device=dev)
+    crit = torch.nn.CrossEntropyLoss()                                  # train_advanced_v3.0.py:449
+    lo = ref(x)
+    loss_o = crit(lo, labels)
+    loss_o.backward()
+    xcl = x.contiguous(memory_format=torch.channels_last)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        la = amp(xcl)
+        loss_a = crit(la.float(), labels)
+    loss_a.backward()
+    n0 = _lib.launch_count
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        lp = prod(xcl)
+        loss_p = crit(lp.float(), labels)
+    loss_p.backward()
+    # + 68 BatchNorm x (stats + apply + 2 bwd) + 23 squeeze-excite x (scale + reduce + apply)
+    assert _lib.launch_count - n0 >= 23 * 3 + 45 * 3 + 68 * 4 + 23 * 3 - 1
+
+    def gnorm(m):
+        return float(torch.sqrt(sum((p.grad.double() ** 2).sum() for p in m.parameters())))
+
+    e_amp, e_prod = _rel(la.float(), lo), _rel(lp.float(), lo)
+    assert e_prod < max(1.5 * e_amp, BF16_REL), (e_prod, e_amp)
+    d_amp = abs(loss_a.item() - loss_o.item()) / abs(loss_o.item())
+    d_prod = abs(loss_p.item() - loss_o.item()) / abs(loss_o.item())
+    assert d_prod < max(1.5 * d_amp, BF16_REL), (d_prod, d_amp)
+    g_o, g_a, g_p = gnorm(ref), gnorm(amp), gnorm(prod)
+    assert abs(g_p - g_o) < max(1.5 * abs(g_a - g_o), 5e-2 * g_o), (g_p, g_a, g_o)
+    assert all(p.grad is not None and p.grad.dtype == torch.float32 for p in prod.parameters())
+    worst = 0.0
+    for (n, a), (_, b) in zip(prod.named_buffers(), ref.named_buffers()):
+        if n.endswith("num_batches_tracked"):
+            assert int(a) == int(b) == 1
+        else:
+            worst = max(worst, _rel(a, b))
+    assert worst < 0.1, worst            # bf16 activations under the statistics of 69 layers

@@ -238,3 +238,92 @@ def test_swap_depthwise_separable_on_cpu_keeps_parameters_and_results():
     assert all(p is params[n] for n, p in m.named_parameters())
     assert torch.equal(m(x), before)
     assert swap_depthwise_separable(m) == (0, 0)
+
+
+@pytest.mark.parametrize("silu", [True, False])
+def test_bn_act_oracle_pinned_to_torch_batch_norm(silu):
+    """oracle bn_act_* against F.batch_norm(training=True) [-> F.silu] and autograd in float64,
+    including nn.BatchNorm2d's running-buffer update."""
+    from oracle import dwsep_oracle as o
+    torch.manual_seed(3 + silu)
+    M, C, eps, mom = 37, 5, 1e-5, 0.1
+    x = (torch.randn(M, C, dtype=torch.float64) * 2 + 0.7).requires_grad_()
+    w = torch.randn(C, dtype=torch.float64).requires_grad_()
+    b = torch.randn(C, dtype=torch.float64).requires_grad_()
+    rm, rv = torch.randn(C, dtype=torch.float64), torch.rand(C, dtype=torch.float64) + 0.5
+    rm0, rv0 = rm.clone(), rv.clone()
+    y = torch.nn.functional.batch_norm(x, rm, rv, w, b, True, mom, eps)
+    if silu:
+        y = torch.nn.functional.silu(y)
+    g = torch.randn_like(y)
+    y.backward(g)
+    yo, mean, var = o.bn_act_fwd_ref(x.detach().numpy(), w.detach().numpy(), b.detach().numpy(), eps, silu)
+    np.testing.assert_allclose(yo, y.detach().numpy(), rtol=1e-11, atol=1e-12)
+    rmo, rvo = o.bn_running_update_ref(rm0.numpy(), rv0.numpy(), mean, var, M, mom)
+    np.testing.assert_allclose(rmo, rm.numpy(), rtol=1e-12)
+    np.testing.assert_allclose(rvo, rv.numpy(), rtol=1e-12)
+    dx, dw, db = o.bn_act_bwd_ref(g.numpy(), x.detach().numpy(), w.detach().numpy(),
+                                  b.detach().numpy(), eps, silu)
+    np.testing.assert_allclose(dx, x.grad.numpy(), rtol=1e-9, atol=1e-11)
+    np.testing.assert_allclose(dw, w.grad.numpy(), rtol=1e-10, atol=1e-12)
+    np.testing.assert_allclose(db, b.grad.numpy(), rtol=1e-10, atol=1e-12)
+
+
+def test_se_oracle_pinned_to_torchvision_squeeze_excitation():
+    """oracle se_* against torchvision.ops.SqueezeExcitation(SiLU, Sigmoid) — the block of
+    efficientnet_b2 — and autograd in float64."""
+    import torchvision
+    from oracle import dwsep_oracle as o
+    torch.manual_seed(5)
+    B, C, Cs, H, W = 3, 8, 2, 4, 5
+    se = torchvision.ops.SqueezeExcitation(C, Cs, activation=torch.nn.SiLU).double()
+    x = torch.randn(B, C, H, W, dtype=torch.float64, requires_grad=True)
+    y = se(x)
+    g = torch.randn_like(y)
+    y.backward(g)
+    w1, b1 = se.fc1.weight.detach().reshape(Cs, C).numpy(), se.fc1.bias.detach().numpy()
+    w2, b2 = se.fc2.weight.detach().reshape(C, Cs).numpy(), se.fc2.bias.detach().numpy()
+    xn = x.detach().permute(0, 2, 3, 1).reshape(B, H * W, C).numpy()
+    gn = g.permute(0, 2, 3, 1).reshape(B, H * W, C).numpy()
+    yo, _ = o.se_fwd_ref(xn, w1, b1, w2, b2)
+    np.testing.assert_allclose(yo, y.detach().permute(0, 2, 3, 1).reshape(B, H * W, C).numpy(), rtol=1e-12)
+    dx, dw1, db1, dw2, db2 = o.se_bwd_ref(gn, xn, w1, b1, w2, b2)
+    np.testing.assert_allclose(dx, x.grad.permute(0, 2, 3, 1).reshape(B, H * W, C).numpy(), rtol=1e-10, atol=1e-13)
+    np.testing.assert_allclose(dw1, se.fc1.weight.grad.reshape(Cs, C).numpy(), rtol=1e-10, atol=1e-13)
+    np.testing.assert_allclose(db1, se.fc1.bias.grad.numpy(), rtol=1e-10, atol=1e-13)
+    np.testing.assert_allclose(dw2, se.fc2.weight.grad.reshape(C, Cs).numpy(), rtol=1e-10, atol=1e-13)
+    np.testing.assert_allclose(db2, se.fc2.bias.grad.numpy(), rtol=1e-10, atol=1e-13)
+
+
+def test_swap_efficientnet_on_cpu_keeps_parameters_buffers_and_results():
+    """f-4: conv + BatchNorm(+SiLU) + squeeze-excite modules swapped around the same Parameter and
+    buffer objects; off the fast path (CPU) the model computes what it did before, in eval and in
+    train mode (running statistics included)."""
+    import copy
+    import torchvision
+    from image_classification_b200.efficientnet import BatchNormActB200, swap_efficientnet
+    torch.manual_seed(0)
+    m = torchvision.models.efficientnet_b2(weights=None, num_classes=44)
+    for mod in m.modules():
+        if isinstance(mod, (torchvision.ops.StochasticDepth, torch.nn.Dropout)):
+            mod.p = 0.0
+    ref = copy.deepcopy(m)
+    keys = list(m.state_dict())
+    params = {n: p for n, p in m.named_parameters()}
+    bufs = {n: b for n, b in m.named_buffers()}
+    counts = swap_efficientnet(m)
+    assert counts == {"depthwise": 23, "pointwise": 49, "batchnorm": 69, "squeeze_excite": 23}
+    assert sum(isinstance(c, BatchNormActB200) and c.emit_pool for c in m.modules()) == 23
+    assert not any(type(c) is torch.nn.BatchNorm2d for c in m.modules())
+    assert list(m.state_dict()) == keys
+    assert all(p is params[n] for n, p in m.named_parameters())
+    assert all(b is bufs[n] for n, b in m.named_buffers())
+    x = torch.randn(2, 3, 64, 64)
+    m.train(), ref.train()
+    assert torch.allclose(m(x), ref(x), rtol=1e-5, atol=1e-6)
+    for (n, a), (_, b) in zip(m.named_buffers(), ref.named_buffers()):
+        assert torch.allclose(a.float(), b.float(), rtol=1e-5, atol=1e-7), n
+    m.eval(), ref.eval()
+    assert torch.allclose(m(x), ref(x), rtol=1e-5, atol=1e-6)
+    again = swap_efficientnet(m)
+    assert again["batchnorm"] == 0 and again["squeeze_excite"] == 0

@@ -1,0 +1,147 @@
+"""EfficientNet-B2 path (BASELINE config 5) on one B200: per-kernel timings of the
+BatchNorm+SiLU / squeeze-excite kernels at the network's shapes (CUDA events, L2 flushed between
+iterations, algorithmic bytes per csrc/bnse.cu) and the training step of the older reference loop
+(/root/reference/previous/V3-efb2/train_advanced_v3.0.py:72-153: autocast forward, hard-label CE,
+scaled backward, unscale, clip 1.0, AdamW, scaler update) on torchvision's efficientnet_b2 with the
+library modules swapped in, next to the same model on PyTorch's own bf16 channels_last kernels.
+
+Development / measurement tool: `python tools/effnet_bench.py [--batch 48] [--res 260] [--steps 10]`.
+Prints one JSON document.
+"""
+from __future__ import annotations
+
+import argparse
+import copy
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from image_classification_b200 import _lib, ops  # noqa: E402
+from image_classification_b200.efficientnet import swap_efficientnet  # noqa: E402
+
+
+def timeit(fn, iters=10, warmup=3, flush=None):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        if flush is not None:
+            flush.zero_()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        fn()
+        e.record()
+        torch.cuda.synchronize()
+        ts.append(s.elapsed_time(e))
+    ts.sort()
+    return ts[len(ts) // 2]
+
+
+def kernel_rows(B, dev, flush, hbm_peak):
+    rows = []
+    for C, H in [(96, 130), (144, 65), (288, 33), (528, 17), (720, 17), (1248, 9), (2112, 9)]:
+        E = B * H * H * C
+        x = torch.randn(B, H, H, C, device=dev).bfloat16()
+        g = torch.randn(B, H, H, C, device=dev).bfloat16()
+        w = torch.rand(C, device=dev) + 0.5
+        b = torch.randn(C, device=dev) * 0.1
+        gate = torch.rand(B, C, device=dev)
+        dpool = torch.randn(B, C, device=dev)
+        _, mean, rstd, _ = ops.bn_act_fwd(x, w, b, None, None, training=True, momentum=0.1,
+                                          eps=1e-5, act=1)
+        cases = {
+            "bn_silu_fwd(+pool)": (3 * E * 2, lambda: ops.bn_act_fwd(
+                x, w, b, None, None, training=True, momentum=0.1, eps=1e-5, act=1, want_pool=True)),
+            "bn_silu_bwd": (5 * E * 2, lambda: ops.bn_act_bwd(g, x, w, b, mean, rstd, 1)),
+            "se_scale_fwd": (2 * E * 2, lambda: ops.se_scale_fwd(x, gate)),
+            "se_bwd_reduce": (2 * E * 2, lambda: ops.se_scale_bwd_reduce(g, x)),
+            "se_bwd_apply": (2 * E * 2, lambda: ops.se_scale_bwd_apply(g, gate, dpool)),
+        }
+        for name, (nbytes, fn) in cases.items():
+            ms = timeit(fn, flush=flush)
+            gbs = nbytes / ms / 1e6
+            rows.append({"kernel": name, "C": C, "H": H, "MB": round(nbytes / 1e6, 1),
+                         "us": round(ms * 1e3, 1), "GBps": round(gbs, 1),
+                         "frac_hbm": round(gbs / hbm_peak, 3)})
+    return rows
+
+
+def train_step_ms(model, x, labels, steps, warmup):
+    """The reference V3 step (train_advanced_v3.0.py:96-113) with bf16 autocast."""
+    opt = torch.optim.AdamW(model.parameters(), lr=2e-4, weight_decay=1e-2)     # config.py:17-18
+    crit = torch.nn.CrossEntropyLoss()                                          # :449
+    scaler = torch.amp.GradScaler("cuda")
+
+    def step():
+        opt.zero_grad()
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            out = model(x)
+            loss = crit(out.float(), labels)
+        scaler.scale(loss).backward()
+        scaler.unscale_(opt)
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)                 # config.py:22
+        scaler.step(opt)
+        scaler.update()
+        return loss
+
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(steps):
+        loss = step()
+    e.record()
+    torch.cuda.synchronize()
+    return s.elapsed_time(e) / steps, float(loss)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--batch", type=int, default=48)          # previous/V3-efb2/config.py:14
+    ap.add_argument("--res", type=int, default=260)           # :12
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--skip-kernels", action="store_true")
+    args = ap.parse_args()
+    import torchvision
+    dev = torch.device("cuda:0")
+    peaks = {}
+    pk = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")
+    if os.path.exists(pk):
+        peaks = json.load(open(pk))
+    hbm = float(peaks.get("hbm_gbs", 6500.0))
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    out = {"batch": args.batch, "res": args.res, "hbm_peak_gbs": hbm,
+           "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback 6500"}
+    if not args.skip_kernels:
+        out["kernels"] = kernel_rows(args.batch, dev, flush, hbm)
+    torch.manual_seed(0)
+    base = torchvision.models.efficientnet_b2(weights=None, num_classes=44).to(dev).train()
+    for m in base.modules():                  # timm's create_model defaults: no drop-path
+        if isinstance(m, torchvision.ops.StochasticDepth):
+            m.p = 0.0
+    x = torch.randn(args.batch, 3, args.res, args.res, device=dev).contiguous(
+        memory_format=torch.channels_last)
+    labels = torch.randint(0, 44, (args.batch,), device=dev)
+    for arm in ("b200", "torch_bf16_channels_last"):
+        model = copy.deepcopy(base)
+        if arm == "b200":
+            out["swapped"] = swap_efficientnet(model)
+        model = model.to(memory_format=torch.channels_last)
+        n0 = _lib.launch_count
+        ms, loss = train_step_ms(model, x, labels, args.steps, args.warmup)
+        out[arm] = {"ms_per_step": round(ms, 3), "images_per_s": round(args.batch / ms * 1e3, 1),
+                    "loss": round(loss, 4),
+                    "lib_launches_per_step": (_lib.launch_count - n0) // (args.steps + args.warmup)}
+        del model
+        torch.cuda.empty_cache()
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()
