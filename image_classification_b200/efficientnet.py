@@ -189,14 +189,20 @@ class _BnActFn(torch.autograd.Function):
                 want_pool):
         xn = _nhwc_bf16(x)
         w, b = weight.detach().float().contiguous(), bias.detach().float().contiguous()
-        y, mean, rstd, pool = ops.bn_act_fwd(xn, w, b, running_mean, running_var, training=training,
-                                             momentum=momentum, eps=eps, act=act, want_pool=want_pool)
+        # the result is allocated as the [B,C,H,W] channels_last tensor the caller gets (not a view
+        # made inside this Function: torchvision's MBConv adds the shortcut to it in place)
+        B, H, W, C = xn.shape
+        y = torch.empty((B, C, H, W), device=xn.device, dtype=torch.bfloat16,
+                        memory_format=torch.channels_last)
+        _, mean, rstd, pool = ops.bn_act_fwd(xn, w, b, running_mean, running_var, training=training,
+                                             momentum=momentum, eps=eps, act=act, want_pool=want_pool,
+                                             out=y.permute(0, 2, 3, 1))
         ctx.save_for_backward(xn, w, b, mean, rstd)
         ctx.act, ctx.training, ctx.x_dtype = act, training, x.dtype
         if pool is None:
             pool = xn.new_empty(0)
         ctx.mark_non_differentiable(pool)
-        return y.permute(0, 3, 1, 2), pool
+        return y, pool
 
     @staticmethod
     def backward(ctx, g, _gpool):
@@ -244,8 +250,9 @@ class BatchNormActB200(nn.BatchNorm2d):
 # ----------------------------------------------------------------------- squeeze-excite
 def _se_gate(pooled, w1, b1, w2, b2):
     """[B,C] fp32 pooled means -> [B,C] fp32 gate (the two 1x1 convolutions on a 1x1 map)."""
-    h = torch.nn.functional.silu(torch.nn.functional.linear(pooled, w1, b1))
-    return torch.sigmoid(torch.nn.functional.linear(h, w2, b2))
+    with torch.autocast("cuda", enabled=False):       # fp32 whatever the ambient autocast says
+        h = torch.nn.functional.silu(torch.nn.functional.linear(pooled, w1, b1))
+        return torch.sigmoid(torch.nn.functional.linear(h, w2, b2))
 
 
 class _SqueezeExciteFn(torch.autograd.Function):

@@ -260,8 +260,9 @@ ACT_NONE, ACT_SILU = 0, 1
 
 
 def bn_act_fwd(x: torch.Tensor, weight, bias, running_mean, running_var, *, training: bool,
-               momentum: float, eps: float, act: int, want_pool: bool = False):
+               momentum: float, eps: float, act: int, want_pool: bool = False, out=None):
     """x [B,H,W,C] bf16 NHWC -> (y bf16 same shape, mean [C], rstd [C], pool_sum [B,C] fp32 | None).
+    out: optional preallocated NHWC result (e.g. the permuted view of a channels_last tensor).
     training: batch statistics (cnx_bn_stats), running buffers updated in place when given;
     otherwise the running statistics normalise.  pool_sum = sum over the pixels of y per image."""
     _chk(x, torch.bfloat16, "x")
@@ -279,7 +280,12 @@ def bn_act_fwd(x: torch.Tensor, weight, bias, running_mean, running_var, *, trai
     if training:
         sums = torch.empty(2 * C, device=dev, dtype=f32)
         _lib.call("cnx_bn_stats", _p(x), _p(sums), B * H * W, C, _stream(x))
-    y = torch.empty_like(x)
+    if out is None:
+        y = torch.empty_like(x)
+    else:
+        y = _chk(out, torch.bfloat16, "out")
+        if y.shape != x.shape:
+            raise _lib.CnxError(f"bn_act_fwd: out {tuple(y.shape)} vs x {tuple(x.shape)}")
     mean = torch.empty(C, device=dev, dtype=f32)
     rstd = torch.empty(C, device=dev, dtype=f32)
     pool = torch.empty(B, C, device=dev, dtype=f32) if want_pool else None

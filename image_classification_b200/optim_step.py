@@ -27,6 +27,12 @@ import torch
 from . import _lib
 
 
+def _same_layout(a: torch.Tensor, b: torch.Tensor) -> bool:
+    """Same memory order: equal strides on every dimension that has more than one element."""
+    return a.shape == b.shape and all(sa == sb for n, sa, sb in zip(a.shape, a.stride(), b.stride())
+                                      if n > 1)
+
+
 def _dense(t: torch.Tensor) -> bool:
     return t.is_contiguous() or (t.dim() == 4 and t.is_contiguous(memory_format=torch.channels_last))
 
@@ -152,10 +158,13 @@ class FusedOptimStep:
             for p in ps:
                 if p.dtype != torch.float32 or p.grad.dtype != torch.float32:
                     raise _lib.CnxError("FusedOptimStep: parameters and gradients must be float32")
-                if not _dense(p) or p.grad.stride() != p.stride():
-                    raise _lib.CnxError("FusedOptimStep: parameters must be dense and gradients "
-                                        f"laid out like them ({self._names.get(p, '?')}: "
-                                        f"{p.stride()} vs {p.grad.stride()})")
+                if not _dense(p):
+                    raise _lib.CnxError("FusedOptimStep: parameters must be dense "
+                                        f"({self._names.get(p, '?')}: strides {p.stride()})")
+                if not _same_layout(p, p.grad):
+                    # e.g. a channels_last convolution weight whose gradient came back contiguous:
+                    # element i of the gradient must be element i of the parameter in memory
+                    p.grad = torch.empty_like(p, memory_format=torch.preserve_format).copy_(p.grad)
                 st = opt.state[p]
                 if "exp_avg" not in st:
                     st["step"] = torch.zeros((), device=dev, dtype=torch.float32)

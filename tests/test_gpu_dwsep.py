@@ -229,7 +229,7 @@ def test_bn_act_vs_oracle_small(cnx_lib, B, H, W, C, silu):
     # the same call without the pooled sums takes the flat geometry: identical y
     y2, *_ = ops.bn_act_fwd(x.to(dev), w.to(dev), b.to(dev), None, None, training=True,
                             momentum=mom, eps=eps, act=act)
-    assert torch.equal(y2, y)
+    assert _rel(y2, y) < 2.0 ** -7        # statistics are atomic sums: a bf16 ulp may flip
     g = torch.from_numpy(rng.randn(B, H, W, C).astype(np.float32)).bfloat16()
     dx_ref, dw_ref, db_ref = dwsep_oracle.bn_act_bwd_ref(g.double().numpy().reshape(M, C), x2, w.numpy(),
                                                          b.numpy(), eps, silu)
@@ -302,6 +302,9 @@ def test_squeeze_excite_vs_oracle(cnx_lib, B, H, W, C, Cs):
     y_ref, _ = dwsep_oracle.se_fwd_ref(xn, w1, b1, w2, b2)
     dx_ref, dw1, db1, dw2, db2 = dwsep_oracle.se_bwd_ref(gn, xn, w1, b1, w2, b2)
     for handed in (False, True):
+        # without the hand-over the pooled mean comes from cnx_avgpool_nhwc_fwd as bf16 (what
+        # PyTorch's bf16 adaptive_avg_pool2d returns too): parameter gradients carry that rounding
+        ptol = 1e-3 if handed else 6e-3
         xa = x.clone().requires_grad_()
         if handed:
             xa._cnx_pool_sum = x.permute(0, 2, 3, 1).float().sum(dim=(1, 2))
@@ -312,10 +315,10 @@ def test_squeeze_excite_vs_oracle(cnx_lib, B, H, W, C, Cs):
         flat = lambda t: t.permute(0, 2, 3, 1).reshape(B, H * W, C).cpu()
         assert _rel(flat(y), torch.from_numpy(y_ref)) < 2.0 ** -7
         assert _rel(flat(xa.grad), torch.from_numpy(dx_ref)) < 2.0 ** -7
-        assert _rel(fc1.weight.grad.reshape(Cs, C).cpu(), torch.from_numpy(dw1)) < 1e-3
-        assert _rel(fc1.bias.grad.cpu(), torch.from_numpy(db1)) < 1e-3
-        assert _rel(fc2.weight.grad.reshape(C, Cs).cpu(), torch.from_numpy(dw2)) < 1e-3
-        assert _rel(fc2.bias.grad.cpu(), torch.from_numpy(db2)) < 1e-3
+        assert _rel(fc1.weight.grad.reshape(Cs, C).cpu(), torch.from_numpy(dw1)) < ptol
+        assert _rel(fc1.bias.grad.cpu(), torch.from_numpy(db1)) < ptol
+        assert _rel(fc2.weight.grad.reshape(C, Cs).cpu(), torch.from_numpy(dw2)) < ptol
+        assert _rel(fc2.bias.grad.cpu(), torch.from_numpy(db2)) < ptol
 
 
 def test_bn_se_reject_bad_arguments(cnx_lib):
@@ -386,10 +389,66 @@ def test_efficientnet_b2_fully_swapped_vs_fp32_model(cnx_lib):
     g_o, g_a, g_p = gnorm(ref), gnorm(amp), gnorm(prod)
     assert abs(g_p - g_o) < max(1.5 * abs(g_a - g_o), 5e-2 * g_o), (g_p, g_a, g_o)
     assert all(p.grad is not None and p.grad.dtype == torch.float32 for p in prod.parameters())
-    worst = 0.0
-    for (n, a), (_, b) in zip(prod.named_buffers(), ref.named_buffers()):
-        if n.endswith("num_batches_tracked"):
-            assert int(a) == int(b) == 1
-        else:
-            worst = max(worst, _rel(a, b))
-    assert worst < 0.1, worst            # bf16 activations under the statistics of 69 layers
+    # running statistics after one update (momentum 0.1): variances relative to their size, means
+    # against the layer's standard deviation (the expand convolutions see zero-mean inputs, so
+    # their batch means are ~1e-7 of the std: a relative measure of the mean itself is noise)
+    pm, rm = dict(prod.named_modules()), dict(ref.named_modules())
+    n_bn = 0
+    for name, bn in rm.items():
+        if not isinstance(bn, torch.nn.BatchNorm2d):
+            continue
+        n_bn += 1
+        assert int(pm[name].num_batches_tracked) == int(bn.num_batches_tracked) == 1
+        std = float(bn.running_var.sqrt().max())
+        assert float((pm[name].running_mean - bn.running_mean).abs().max()) < 2e-2 * std, name
+        assert _rel(pm[name].running_var, bn.running_var) < 5e-2, name
+    assert n_bn == 69
+
+
+def test_graphed_forward_backward_matches_eager(cnx_lib):
+    """graphed.GraphedForwardBackward on the fully swapped efficientnet_b2: the replayed
+    micro-step gives the eager loss / logits / gradients for each of two different batches (the
+    static input is refilled, the static gradients are overwritten, not accumulated) and advances
+    the BatchNorm buffers once per replay."""
+    import copy
+    import torchvision
+    from image_classification_b200.efficientnet import swap_efficientnet
+    from image_classification_b200.graphed import GraphedForwardBackward
+    from image_classification_b200.loss import SoftTargetCrossEntropyB200
+    dev = _dev()
+    torch.manual_seed(1)
+    base = torchvision.models.efficientnet_b2(weights=None, num_classes=44).to(dev).train()
+    for m in base.modules():
+        if isinstance(m, (torchvision.ops.StochasticDepth, torch.nn.Dropout)):
+            m.p = 0.0
+    swap_efficientnet(base)
+    eager, graphed = copy.deepcopy(base), copy.deepcopy(base)
+    crit = SoftTargetCrossEntropyB200(0.0)
+    scaler = torch.amp.GradScaler("cuda", init_scale=1024.0)
+    batches = [(torch.randn(8, 3, 160, 160, device=dev).contiguous(memory_format=torch.channels_last),
+                torch.randint(0, 44, (8,), device=dev)) for _ in range(2)]
+    warm = 3
+    gfb = GraphedForwardBackward(graphed, crit, scaler, *batches[0], warmup=warm)
+    bn_e = [m for m in eager.modules() if isinstance(m, torch.nn.BatchNorm2d)][0]
+    bn_g = [m for m in graphed.modules() if isinstance(m, torch.nn.BatchNorm2d)][0]
+    assert int(bn_g.num_batches_tracked) == warm + 1          # warm-up runs + the capture pass
+    for _ in range(warm + 1):                                 # bring the eager buffers level
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+            eager(batches[0][0])
+    for i, (x, y) in enumerate(batches):
+        for p in eager.parameters():
+            p.grad = None
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            out = eager(x)
+            loss = crit(out, y)
+        scaler.scale(loss).backward()
+        loss_g = gfb(x, y)
+        assert abs(float(loss_g) - float(loss)) < 2e-3 * abs(float(loss))
+        assert _rel(gfb.outputs.float(), out.float()) < BF16_REL
+        ge = torch.cat([p.grad.flatten() for p in eager.parameters()])
+        gg = torch.cat([p.grad.flatten() for p in graphed.parameters()])
+        assert float((ge - gg).norm() / ge.norm()) < BF16_REL, i      # atomics reorder fp32 sums
+        assert int(bn_g.num_batches_tracked) == int(bn_e.num_batches_tracked) == warm + 2 + i
+        assert _rel(bn_g.running_var, bn_e.running_var) < 1e-3
+    with pytest.raises(RuntimeError):
+        gfb(batches[0][0][:4], batches[0][1][:4])             # captured for a fixed batch shape

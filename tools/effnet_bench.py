@@ -3,7 +3,8 @@ BatchNorm+SiLU / squeeze-excite kernels at the network's shapes (CUDA events, L2
 iterations, algorithmic bytes per csrc/bnse.cu) and the training step of the older reference loop
 (/root/reference/previous/V3-efb2/train_advanced_v3.0.py:72-153: autocast forward, hard-label CE,
 scaled backward, unscale, clip 1.0, AdamW, scaler update) on torchvision's efficientnet_b2 with the
-library modules swapped in, next to the same model on PyTorch's own bf16 channels_last kernels.
+library modules swapped in (eager; with the fused optimizer step; with forward+backward replayed
+as one CUDA graph), next to the same model on PyTorch's own bf16 channels_last kernels.
 
 Development / measurement tool: `python tools/effnet_bench.py [--batch 48] [--res 260] [--steps 10]`.
 Prints one JSON document.
@@ -70,13 +71,33 @@ def kernel_rows(B, dev, flush, hbm_peak):
     return rows
 
 
-def train_step_ms(model, x, labels, steps, warmup):
-    """The reference V3 step (train_advanced_v3.0.py:96-113) with bf16 autocast."""
+def train_step_ms(model, x, labels, steps, warmup, fused=False, graphed=False):
+    """The reference V3 step (train_advanced_v3.0.py:96-113) with bf16 autocast.  fused: the same
+    sequence through train_step.TrainStep (accumulation 1, no EMA): library soft-CE kernel and
+    unscale + clip + AdamW as two launches (optim_step.FusedOptimStep)."""
     opt = torch.optim.AdamW(model.parameters(), lr=2e-4, weight_decay=1e-2)     # config.py:17-18
     crit = torch.nn.CrossEntropyLoss()                                          # :449
     scaler = torch.amp.GradScaler("cuda")
+    if fused:
+        from image_classification_b200.loss import SoftTargetCrossEntropyB200
+        from image_classification_b200.train_step import StepConfig, TrainStep
+        ts = TrainStep(model, SoftTargetCrossEntropyB200(0.0), opt, None, scaler, None,
+                       StepConfig(gradient_accumulation_steps=1, gradient_clip_val=1.0))
+
+    if graphed:
+        from image_classification_b200.graphed import GraphedForwardBackward
+        from image_classification_b200.loss import SoftTargetCrossEntropyB200
+        from image_classification_b200.optim_step import FusedOptimStep
+        gfb = GraphedForwardBackward(model, SoftTargetCrossEntropyB200(0.0), scaler, x, labels)
+        fo = FusedOptimStep(model, opt, scaler, None, 1.0)
 
     def step():
+        if graphed:                      # one graph launch + the two optimizer launches
+            loss = gfb(x, labels)
+            fo.step()
+            return loss
+        if fused:
+            return ts.micro_step(x, labels, 0)
         opt.zero_grad()
         with torch.autocast("cuda", dtype=torch.bfloat16):
             out = model(x)
@@ -97,7 +118,7 @@ def train_step_ms(model, x, labels, steps, warmup):
         loss = step()
     e.record()
     torch.cuda.synchronize()
-    return s.elapsed_time(e) / steps, float(loss)
+    return s.elapsed_time(e) / steps, float(loss.detach())
 
 
 def main():
@@ -128,13 +149,14 @@ def main():
     x = torch.randn(args.batch, 3, args.res, args.res, device=dev).contiguous(
         memory_format=torch.channels_last)
     labels = torch.randint(0, 44, (args.batch,), device=dev)
-    for arm in ("b200", "torch_bf16_channels_last"):
+    for arm in ("b200", "b200_fused_optim", "b200_graphed", "torch_bf16_channels_last"):
         model = copy.deepcopy(base)
-        if arm == "b200":
+        if arm.startswith("b200"):
             out["swapped"] = swap_efficientnet(model)
         model = model.to(memory_format=torch.channels_last)
         n0 = _lib.launch_count
-        ms, loss = train_step_ms(model, x, labels, args.steps, args.warmup)
+        ms, loss = train_step_ms(model, x, labels, args.steps, args.warmup,
+                                 fused=arm == "b200_fused_optim", graphed=arm == "b200_graphed")
         out[arm] = {"ms_per_step": round(ms, 3), "images_per_s": round(args.batch / ms * 1e3, 1),
                     "loss": round(loss, 4),
                     "lib_launches_per_step": (_lib.launch_count - n0) // (args.steps + args.warmup)}
