@@ -42,9 +42,11 @@ def timeit(fn, iters=10, warmup=3, flush=None):
     return ts[len(ts) // 2]
 
 
-def kernel_rows(B, dev, flush, hbm_peak):
+def kernel_rows(B, dev, flush, hbm_peak, once=False):
+    """once: every kernel exactly once at two shapes (the ncu --set full target)."""
     rows = []
-    for C, H in [(96, 130), (144, 65), (288, 33), (528, 17), (720, 17), (1248, 9), (2112, 9)]:
+    shapes = [(96, 130), (144, 65), (288, 33), (528, 17), (720, 17), (1248, 9), (2112, 9)]
+    for C, H in ([(96, 130), (528, 17)] if once else shapes):
         E = B * H * H * C
         x = torch.randn(B, H, H, C, device=dev).bfloat16()
         g = torch.randn(B, H, H, C, device=dev).bfloat16()
@@ -63,6 +65,10 @@ def kernel_rows(B, dev, flush, hbm_peak):
             "se_bwd_apply": (2 * E * 2, lambda: ops.se_scale_bwd_apply(g, gate, dpool)),
         }
         for name, (nbytes, fn) in cases.items():
+            if once:
+                fn()
+                torch.cuda.synchronize()
+                continue
             ms = timeit(fn, flush=flush)
             gbs = nbytes / ms / 1e6
             rows.append({"kernel": name, "C": C, "H": H, "MB": round(nbytes / 1e6, 1),
@@ -128,6 +134,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--skip-kernels", action="store_true")
+    ap.add_argument("--only-kernels", action="store_true", help="per-kernel table only")
+    ap.add_argument("--ncu", action="store_true", help="each kernel once at two shapes (ncu target)")
     args = ap.parse_args()
     import torchvision
     dev = torch.device("cuda:0")
@@ -139,8 +147,14 @@ def main():
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     out = {"batch": args.batch, "res": args.res, "hbm_peak_gbs": hbm,
            "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback 6500"}
+    if args.ncu:
+        kernel_rows(args.batch, dev, None, hbm, once=True)
+        return
     if not args.skip_kernels:
         out["kernels"] = kernel_rows(args.batch, dev, flush, hbm)
+    if args.only_kernels:
+        print(json.dumps(out))
+        return
     torch.manual_seed(0)
     base = torchvision.models.efficientnet_b2(weights=None, num_classes=44).to(dev).train()
     for m in base.modules():                  # timm's create_model defaults: no drop-path
