@@ -185,26 +185,31 @@ dwk_bwd_data_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restric
 // ---------------------------------------------------------------------------- backward, filter
 // dw[kh*K + kw, c] (+)= sum_{b, oy, ox} dy[b, oy, ox, c] * x[b, oy*S - P + kh, ox*S - P + kw, c]
 // Block = vpb channel vectors x (kThreads / vpb) strip lanes; grid.x = channel blocks,
-// grid.y = strip chunks.
+// grid.y = strip chunks, grid.z = kernel row kh.  One kernel row per CTA keeps K*VEC accumulators
+// per thread (40 registers at most) instead of K*K*VEC: the all-taps form needed 240 registers
+// (one CTA of 8 warps per SM, loads issued one by one) and ran at 0.2-0.3 TB/s on L2-resident
+// maps — a quarter of the EfficientNet-B2 step.  Here a strip costs TW dy loads and NC x loads,
+// all issued before the first FMA; dy and the x rows are re-read by the K rows' CTAs out of L2.
 template <int K, int S, int VEC>
 __global__ void __launch_bounds__(kThreads)
 dwk_bwd_weight_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                       float* __restrict__ dwt, Geo g, int vpb, long long strips_total,
                       long long strips_per_cta) {
   constexpr int P = K / 2, NC = (TW - 1) * S + K;
-  extern __shared__ float s_dw[];                       // [K*K][vpb * VEC]
+  extern __shared__ float s_dw[];                       // [K][vpb * VEC]
   const int nvec = g.C / VEC;
   const int vl = threadIdx.x % vpb, pl = threadIdx.x / vpb, npl = kThreads / vpb;
   const int v = blockIdx.x * vpb + vl;
   const int cw = vpb * VEC;
-  for (int i = threadIdx.x; i < K * K * cw; i += kThreads) s_dw[i] = 0.f;
+  const int kh = blockIdx.z;
+  for (int i = threadIdx.x; i < K * cw; i += kThreads) s_dw[i] = 0.f;
   __syncthreads();
   const bool active = pl < npl && v < nvec;
-  float acc[K * K][VEC];
+  float acc[K][VEC];
 #pragma unroll
-  for (int tp = 0; tp < K * K; ++tp)
+  for (int kw = 0; kw < K; ++kw)
 #pragma unroll
-    for (int i = 0; i < VEC; ++i) acc[tp][i] = 0.f;
+    for (int i = 0; i < VEC; ++i) acc[kw][i] = 0.f;
   if (active) {
     const int c0 = v * VEC;
     const int strips = (g.Wo + TW - 1) / TW;
@@ -215,9 +220,12 @@ dwk_bwd_weight_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16*
       long long r = sidx / strips;
       const int oy = static_cast<int>(r % g.Ho);
       const int b = static_cast<int>(r / g.Ho);
+      const int iy = oy * S - P + kh;
+      if (iy < 0 || iy >= g.H) continue;                 // this kernel row sees padding only
       const int ox0 = strip * TW, ix0 = ox0 * S - P;
-      float d[TW][VEC];
+      float d[TW][VEC], xv[NC][VEC];
       const __nv_bfloat16* drow = dy + ((static_cast<long long>(b) * g.Ho + oy) * g.Wo + ox0) * g.C + c0;
+      const __nv_bfloat16* xrow = x + ((static_cast<long long>(b) * g.H + iy) * g.W + ix0) * g.C + c0;
 #pragma unroll
       for (int t = 0; t < TW; ++t) {
         if (ox0 + t < g.Wo) {
@@ -228,38 +236,37 @@ dwk_bwd_weight_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16*
         }
       }
 #pragma unroll
-      for (int kh = 0; kh < K; ++kh) {
-        const int iy = oy * S - P + kh;
-        if (iy < 0 || iy >= g.H) continue;
-        const __nv_bfloat16* xrow = x + (static_cast<long long>(b) * g.H + iy) * g.W * g.C + c0;
+      for (int c = 0; c < NC; ++c) {
+        const int ix = ix0 + c;
+        if (ix >= 0 && ix < g.W) {
+          Vec<VEC>::load(xrow + static_cast<long long>(c) * g.C, xv[c]);
+        } else {
 #pragma unroll
-        for (int c = 0; c < NC; ++c) {
-          const int ix = ix0 + c;
-          if (ix < 0 || ix >= g.W) continue;
-          float xv[VEC];
-          Vec<VEC>::load(xrow + static_cast<long long>(ix) * g.C, xv);
+          for (int i = 0; i < VEC; ++i) xv[c][i] = 0.f;
+        }
+      }
 #pragma unroll
-          for (int t = 0; t < TW; ++t) {
-            const int kw = c - t * S;                    // compile-time
-            if (kw >= 0 && kw < K) {
+      for (int c = 0; c < NC; ++c) {
 #pragma unroll
-              for (int i = 0; i < VEC; ++i)
-                acc[kh * K + kw][i] = fmaf(d[t][i], xv[i], acc[kh * K + kw][i]);
-            }
+        for (int t = 0; t < TW; ++t) {
+          const int kw = c - t * S;                      // compile-time
+          if (kw >= 0 && kw < K) {
+#pragma unroll
+            for (int i = 0; i < VEC; ++i) acc[kw][i] = fmaf(d[t][i], xv[c][i], acc[kw][i]);
           }
         }
       }
     }
 #pragma unroll
-    for (int tp = 0; tp < K * K; ++tp)
+    for (int kw = 0; kw < K; ++kw)
 #pragma unroll
-      for (int i = 0; i < VEC; ++i) atomicAdd(&s_dw[tp * cw + vl * VEC + i], acc[tp][i]);
+      for (int i = 0; i < VEC; ++i) atomicAdd(&s_dw[kw * cw + vl * VEC + i], acc[kw][i]);
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < K * K * cw; i += kThreads) {
-    const int tp = i / cw, cc = i % cw;
+  for (int i = threadIdx.x; i < K * cw; i += kThreads) {
+    const int kw = i / cw, cc = i % cw;
     const int c = blockIdx.x * cw + cc;
-    if (c < g.C) atomicAdd(dwt + tp * g.C + c, s_dw[i]);
+    if (c < g.C) atomicAdd(dwt + (kh * K + kw) * g.C + c, s_dw[i]);
   }
 }
 
@@ -304,14 +311,14 @@ int launch_weight(const __nv_bfloat16* dy, const __nv_bfloat16* x, float* dwt, c
   const int npl = kThreads / vpb;
   const long long strips_total = static_cast<long long>(g.B) * g.Ho * ((g.Wo + TW - 1) / TW);
   const int gx = (nvec + vpb - 1) / vpb;
-  long long gy = (4LL * sm_count() + gx - 1) / gx;                  // ~4 CTAs per SM in total
+  long long gy = (8LL * sm_count() + gx * K - 1) / (gx * K);        // ~8 CTAs per SM in total
   const long long max_gy = (strips_total + npl - 1) / npl;
   if (gy > max_gy) gy = max_gy;
   if (gy < 1) gy = 1;
   if (gy > 65535) gy = 65535;
   const long long per = (strips_total + gy - 1) / gy;
-  const size_t smem = sizeof(float) * K * K * vpb * VEC;
-  dwk_bwd_weight_kernel<K, S, VEC><<<dim3(gx, static_cast<unsigned>(gy)), kThreads, smem, stream>>>(
+  const size_t smem = sizeof(float) * K * vpb * VEC;
+  dwk_bwd_weight_kernel<K, S, VEC><<<dim3(gx, static_cast<unsigned>(gy), K), kThreads, smem, stream>>>(
       dy, x, dwt, g, vpb, strips_total, per);
   return status("dwconv_kxk_bwd (filter)");
 }
@@ -357,8 +364,8 @@ int dwconv_kxk_bwd(const void* dy, const void* x, const float* wt, void* dx, flo
     if (!accumulate) cudaMemsetAsync(dwt, 0, sizeof(float) * k * k * C, stream);
     if (k == 3 && stride == 1) return launch_weight<3, 1, 8>(dyp, xp, dwt, g, stream);
     if (k == 3) return launch_weight<3, 2, 8>(dyp, xp, dwt, g, stream);
-    if (stride == 1) return launch_weight<5, 1, 4>(dyp, xp, dwt, g, stream);
-    return launch_weight<5, 2, 4>(dyp, xp, dwt, g, stream);
+    if (stride == 1) return launch_weight<5, 1, 8>(dyp, xp, dwt, g, stream);
+    return launch_weight<5, 2, 8>(dyp, xp, dwt, g, stream);
   }
   return CNX_OK;
 }

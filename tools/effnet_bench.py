@@ -136,6 +136,8 @@ def main():
     ap.add_argument("--skip-kernels", action="store_true")
     ap.add_argument("--only-kernels", action="store_true", help="per-kernel table only")
     ap.add_argument("--ncu", action="store_true", help="each kernel once at two shapes (ncu target)")
+    ap.add_argument("--profile", action="store_true",
+                    help="torch.profiler kernel table of 3 eager steps of the library arm (diagnosis)")
     args = ap.parse_args()
     import torchvision
     dev = torch.device("cuda:0")
@@ -163,6 +165,17 @@ def main():
     x = torch.randn(args.batch, 3, args.res, args.res, device=dev).contiguous(
         memory_format=torch.channels_last)
     labels = torch.randint(0, 44, (args.batch,), device=dev)
+    if args.profile:
+        from torch.profiler import ProfilerActivity, profile
+        model = copy.deepcopy(base)
+        swap_efficientnet(model)
+        model = model.to(memory_format=torch.channels_last)
+        train_step_ms(model, x, labels, 2, 2, fused=True)
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            train_step_ms(model, x, labels, 3, 0, fused=True)
+        print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=45,
+                                        max_name_column_width=70))
+        return
     for arm in ("b200", "b200_fused_optim", "b200_graphed", "torch_bf16_channels_last"):
         model = copy.deepcopy(base)
         if arm.startswith("b200"):
