@@ -227,6 +227,29 @@ int cnx_se_scale_bwd_apply(const void* g, const float* gate, const float* dpool,
   return se_scale_bwd_apply(g, gate, dpool, dx, B, HW, C, as_stream(stream));
 }
 
+int cnx_se_gate_fwd(const float* pool_sum, float pool_scale, const float* w1, const float* b1,
+                    const float* w2t, const float* b2, float* hidden, float* gate, int B, int C,
+                    int Cs, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(pool_sum); CNX_REQUIRE_PTR(w1); CNX_REQUIRE_PTR(b1); CNX_REQUIRE_PTR(w2t);
+  CNX_REQUIRE_PTR(b2); CNX_REQUIRE_PTR(hidden); CNX_REQUIRE_PTR(gate);
+  return se_gate_fwd(pool_sum, pool_scale, w1, b1, w2t, b2, hidden, gate, B, C, Cs,
+                     as_stream(stream));
+}
+
+int cnx_se_gate_bwd(const float* dgate, const float* gate, const float* hidden,
+                    const float* pool_sum, float pool_scale, const float* w1, const float* w2t,
+                    float* dz2, float* dh, float* dpool, float* dw1, float* db1, float* dw2t,
+                    float* db2, int B, int C, int Cs, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(dgate); CNX_REQUIRE_PTR(gate); CNX_REQUIRE_PTR(hidden); CNX_REQUIRE_PTR(pool_sum);
+  CNX_REQUIRE_PTR(w1); CNX_REQUIRE_PTR(w2t); CNX_REQUIRE_PTR(dz2); CNX_REQUIRE_PTR(dh);
+  CNX_REQUIRE_PTR(dpool); CNX_REQUIRE_PTR(dw1); CNX_REQUIRE_PTR(db1); CNX_REQUIRE_PTR(dw2t);
+  CNX_REQUIRE_PTR(db2);
+  return se_gate_bwd(dgate, gate, hidden, pool_sum, pool_scale, w1, w2t, dz2, dh, dpool, dw1, db1,
+                     dw2t, db2, B, C, Cs, as_stream(stream));
+}
+
 int cnx_layernorm_bwd(const void* dy, const void* x, const float* weight, const float* mean,
                       const float* rstd, void* dx, float* dweight, float* dbias, int64_t M, int C,
                       void* stream) {

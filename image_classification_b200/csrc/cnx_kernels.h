@@ -43,6 +43,14 @@ int se_scale_bwd_reduce(const void* g, const void* x, float* dgate, int B, int H
 int se_scale_bwd_apply(const void* g, const float* gate, const float* dpool, void* dx, int B,
                        int HW, int C, cudaStream_t stream);
 
+int se_gate_fwd(const float* pool_sum, float pool_scale, const float* w1, const float* b1,
+                const float* w2t, const float* b2, float* hidden, float* gate, int B, int C, int Cs,
+                cudaStream_t stream);
+int se_gate_bwd(const float* dgate, const float* gate, const float* hidden, const float* pool_sum,
+                float pool_scale, const float* w1, const float* w2t, float* dz2, float* dh,
+                float* dpool, float* dw1, float* db1, float* dw2t, float* db2, int B, int C, int Cs,
+                cudaStream_t stream);
+
 // ---- ln_rows.cu : LayerNorm with affine over [M, C] bf16 rows (stem / downsample LayerNorm2d)
 int ln_affine_fwd(const void* x, const float* w, const float* b, void* y, float* mean, float* rstd,
                   int64_t M, int C, float eps, int pH, int pW, int pk, cudaStream_t stream);

@@ -21,8 +21,8 @@ the convolutions is on the library too (csrc/bnse.cu):
 * `BatchNormActB200`     — `nn.BatchNorm2d` (+ the SiLU that follows it) -> `cnx_bn_stats` +
   `cnx_bn_act_fwd`, backward `cnx_bn_act_bwd`; running statistics updated like nn.BatchNorm2d;
 * `SqueezeExciteB200`    — x * sigmoid(fc2(silu(fc1(mean x)))): the pooled sums come out of the
-  preceding `BatchNormActB200` pass, the two [B,C] layers are fp32 PyTorch ops (a few kFLOP), the
-  scaling and its backward are `cnx_se_scale_*`;
+  preceding `BatchNormActB200` pass, the two [B,C] gate layers are `cnx_se_gate_fwd/bwd` (one CTA
+  per image, fp32), the scaling and its backward are `cnx_se_scale_*`;
 * `swap_efficientnet(model)` installs all four kinds.
 
 timm is not installable here; the
@@ -248,42 +248,36 @@ class BatchNormActB200(nn.BatchNorm2d):
 
 
 # ----------------------------------------------------------------------- squeeze-excite
-def _se_gate(pooled, w1, b1, w2, b2):
-    """[B,C] fp32 pooled means -> [B,C] fp32 gate (the two 1x1 convolutions on a 1x1 map)."""
-    with torch.autocast("cuda", enabled=False):       # fp32 whatever the ambient autocast says
-        h = torch.nn.functional.silu(torch.nn.functional.linear(pooled, w1, b1))
-        return torch.sigmoid(torch.nn.functional.linear(h, w2, b2))
-
-
 class _SqueezeExciteFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, pool_sum, w1, b1, w2, b2):
         xn = _nhwc_bf16(x)
         B, H, W, C = xn.shape
         if pool_sum is not None and pool_sum.numel() == B * C:
-            pooled = pool_sum * (1.0 / (H * W))
+            pool, scale = pool_sum, 1.0 / (H * W)          # sums handed over by the BatchNorm pass
         else:
-            pooled = ops.avgpool_nhwc_fwd(xn).float()
-        params = [t.detach().float().reshape(t.shape[0], -1) if t.dim() == 4 else t.detach().float()
-                  for t in (w1, b1, w2, b2)]
-        gate = _se_gate(pooled, *params).contiguous()
+            pool, scale = ops.avgpool_nhwc_fwd(xn).float(), 1.0
+        Cs = w1.shape[0]
+        w1m = w1.detach().float().reshape(Cs, C).contiguous()
+        w2t = w2.detach().float().reshape(C, Cs).t().contiguous()         # [Cs, C]
+        hidden, gate = ops.se_gate_fwd(pool, scale, w1m, b1.detach().float().contiguous(), w2t,
+                                       b2.detach().float().contiguous())
         y = ops.se_scale_fwd(xn, gate)
-        ctx.save_for_backward(xn, pooled, gate, *params)
-        ctx.x_dtype, ctx.w_shapes = x.dtype, (w1.shape, w2.shape)
+        ctx.save_for_backward(xn, pool, gate, hidden, w1m, w2t)
+        ctx.scale, ctx.x_dtype, ctx.w_shapes = scale, x.dtype, (w1.shape, w2.shape)
         return y.permute(0, 3, 1, 2)
 
     @staticmethod
     def backward(ctx, g):
-        xn, pooled, gate, w1, b1, w2, b2 = ctx.saved_tensors
+        xn, pool, gate, hidden, w1m, w2t = ctx.saved_tensors
         gn = _nhwc_bf16(g)
         dgate = ops.se_scale_bwd_reduce(gn, xn)
-        with torch.enable_grad():                 # the [B,C] gate layers: a few kFLOP of PyTorch
-            leaves = [t.detach().requires_grad_() for t in (pooled, w1, b1, w2, b2)]
-            dpool, dw1, db1, dw2, db2 = torch.autograd.grad(_se_gate(*leaves), leaves, dgate)
-        dx = ops.se_scale_bwd_apply(gn, gate, dpool.contiguous()).permute(0, 3, 1, 2)
+        dpool, dw1, db1, dw2t, db2 = ops.se_gate_bwd(dgate, gate, hidden, pool, ctx.scale, w1m, w2t)
+        dx = ops.se_scale_bwd_apply(gn, gate, dpool).permute(0, 3, 1, 2)
         if ctx.x_dtype != torch.bfloat16:
             dx = dx.to(ctx.x_dtype)
-        return dx, None, dw1.reshape(ctx.w_shapes[0]), db1, dw2.reshape(ctx.w_shapes[1]), db2
+        return (dx, None, dw1.reshape(ctx.w_shapes[0]), db1,
+                dw2t.t().contiguous().reshape(ctx.w_shapes[1]), db2)
 
 
 class SqueezeExciteB200(nn.Module):

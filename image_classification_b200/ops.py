@@ -350,6 +350,45 @@ def se_scale_bwd_apply(g: torch.Tensor, gate: torch.Tensor, dpool: torch.Tensor)
     return dx
 
 
+def se_gate_fwd(pool: torch.Tensor, pool_scale: float, w1, b1, w2t, b2):
+    """pool [B,C] fp32 (pooled sums; pooled = pool * pool_scale), w1 [Cs,C], b1 [Cs], w2t [Cs,C]
+    (expand weight transposed), b2 [C] -> (hidden [B,Cs] pre-activation, gate [B,C]), fp32."""
+    for n, t in (("pool", pool), ("w1", w1), ("b1", b1), ("w2t", w2t), ("b2", b2)):
+        _chk(t, torch.float32, n)
+    B, C = pool.shape
+    Cs = w1.shape[0]
+    if tuple(w1.shape) != (Cs, C) or tuple(w2t.shape) != (Cs, C) or b1.numel() != Cs or b2.numel() != C:
+        raise _lib.CnxError(f"se_gate_fwd: w1 / w2t must be [{Cs}, {C}], b1 [{Cs}], b2 [{C}]")
+    hidden = torch.empty(B, Cs, device=pool.device, dtype=torch.float32)
+    gate = torch.empty(B, C, device=pool.device, dtype=torch.float32)
+    _lib.call("cnx_se_gate_fwd", _p(pool), float(pool_scale), _p(w1), _p(b1), _p(w2t), _p(b2),
+              _p(hidden), _p(gate), B, C, Cs, _stream(pool))
+    return hidden, gate
+
+
+def se_gate_bwd(dgate, gate, hidden, pool, pool_scale: float, w1, w2t):
+    """-> (dpool [B,C] gradient at the pooled vector, dw1 [Cs,C], db1 [Cs], dw2t [Cs,C], db2 [C])."""
+    for n, t in (("dgate", dgate), ("gate", gate), ("hidden", hidden), ("pool", pool), ("w1", w1),
+                 ("w2t", w2t)):
+        _chk(t, torch.float32, n)
+    B, C = pool.shape
+    Cs = w1.shape[0]
+    if tuple(dgate.shape) != (B, C) or tuple(gate.shape) != (B, C) or tuple(hidden.shape) != (B, Cs):
+        raise _lib.CnxError(f"se_gate_bwd: dgate / gate must be [{B}, {C}], hidden [{B}, {Cs}]")
+    dev, f32 = pool.device, torch.float32
+    dz2 = torch.empty(B, C, device=dev, dtype=f32)
+    dh = torch.empty(B, Cs, device=dev, dtype=f32)
+    dpool = torch.empty(B, C, device=dev, dtype=f32)
+    dw1 = torch.empty(Cs, C, device=dev, dtype=f32)
+    db1 = torch.empty(Cs, device=dev, dtype=f32)
+    dw2t = torch.empty(Cs, C, device=dev, dtype=f32)
+    db2 = torch.empty(C, device=dev, dtype=f32)
+    _lib.call("cnx_se_gate_bwd", _p(dgate), _p(gate), _p(hidden), _p(pool), float(pool_scale),
+              _p(w1), _p(w2t), _p(dz2), _p(dh), _p(dpool), _p(dw1), _p(db1), _p(dw2t), _p(db2),
+              B, C, Cs, _stream(pool))
+    return dpool, dw1, db1, dw2t, db2
+
+
 # ------------------------------------------------------------------ MLP GEMMs
 EPI_STORE_BF16, EPI_BIAS_GELU, EPI_BIAS_RESIDUAL, EPI_GELU_GRAD, EPI_STORE_F32 = range(5)
 EPI_BIAS = 6

@@ -207,6 +207,22 @@ int cnx_se_scale_bwd_reduce(const void* g, const void* x, float* dgate, int B, i
                             void* stream);
 int cnx_se_scale_bwd_apply(const void* g, const float* gate, const float* dpool, void* dx, int B,
                            int HW, int C, void* stream);
+/* The two gate layers of the squeeze-excite block on the pooled [B,C] vector (fp32):
+ *   pooled = pool_sum * pool_scale;  hidden = w1 pooled + b1  ([B,Cs], saved);
+ *   gate = sigmoid(w2 silu(hidden) + b2)  ([B,C]).
+ * w1 [Cs,C] is the reduce convolution's weight, w2t [Cs,C] the expand convolution's weight
+ * TRANSPOSED (so that all reads are coalesced along C).  One CTA per image.
+ * cnx_se_gate_bwd: from dgate [B,C] (cnx_se_scale_bwd_reduce) -> dpool [B,C] (gradient at the
+ * pooled vector, for cnx_se_scale_bwd_apply), dw1 [Cs,C], db1 [Cs], dw2t [Cs,C], db2 [C] (all
+ * overwritten); dz2 [B,C] and dh [B,Cs] are caller-owned scratch.  (C + Cs) * 4 B and
+ * B * 64 B of shared memory must fit 48 KB. */
+int cnx_se_gate_fwd(const float* pool_sum, float pool_scale, const float* w1, const float* b1,
+                    const float* w2t, const float* b2, float* hidden, float* gate, int B, int C,
+                    int Cs, void* stream);
+int cnx_se_gate_bwd(const float* dgate, const float* gate, const float* hidden,
+                    const float* pool_sum, float pool_scale, const float* w1, const float* w2t,
+                    float* dz2, float* dh, float* dpool, float* dw1, float* db1, float* dw2t,
+                    float* db2, int B, int C, int Cs, void* stream);
 
 /* Generic tensor-core GEMM: D[M,N] = epilogue(A[M,K] * B[N,K]^T), bf16 in, fp32 accumulate.
  * a_mn_major / b_mn_major != 0: the operand is stored [K, rows] (row-major) instead. */
