@@ -132,8 +132,8 @@ LAUNCHES_PER_CALL = {
     "cnx_softce_fwd_bwd": 1, "cnx_ema_lerp_multi": 1, "cnx_optim_grad_norm": 1, "cnx_optim_adamw_ema": 1, "cnx_nchw_f32_to_nhwc_bf16": 1,
     "cnx_nhwc_bf16_to_nchw_f32": 1,
     "cnx_bn_stats": 1, "cnx_bn_act_fwd": 1, "cnx_bn_act_bwd": 2, "cnx_se_scale_fwd": 1,
-    "cnx_se_scale_bwd_reduce": 1, "cnx_se_scale_bwd_apply": 1, "cnx_se_gate_fwd": 1,
-    "cnx_se_gate_bwd": 2,
+    "cnx_se_scale_bwd_reduce": 1, "cnx_se_scale_bwd_apply": 1, "cnx_se_gate_fwd": 2,
+    "cnx_se_gate_bwd": 3,
 }
 launch_count = 0          # total kernels launched through this binding
 call_hook = None          # optional callable(name, phase, args), phase in {"pre", "post"} (profiling)

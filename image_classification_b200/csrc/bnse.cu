@@ -416,82 +416,99 @@ se_bwd_apply_kernel(const __nv_bfloat16* __restrict__ g, const float* __restrict
 // gate[b,c] = sigmoid(b2[c] + sum_j w2t[j,c] * silu(b1[j] + sum_c' w1[j,c'] * pooled[b,c'])),
 // pooled = pool_sum * pool_scale.  Two [B,C]-sized layers (Cs <= C/4 hidden units): as PyTorch ops
 // they were ~30 launches per block (SIMT sgemm + bias + activations, forward / recompute /
-// backward), 2 ms of a 15.5 ms EfficientNet-B2 step; here one CTA per image does both layers out
-// of shared memory.  w2t is the expand weight transposed to [Cs, C] so that every global read is
-// coalesced along c in all three kernels.
+// backward), 2 ms of a 15.5 ms EfficientNet-B2 step.  w2t is the expand weight transposed to
+// [Cs, C] so that every global read is coalesced along c.  Two kernel shapes serve forward and
+// backward; both tile (hidden units or channels) x kSeB images per CTA, so a weight element is
+// read once per kSeB images (one CTA per image re-read both matrices per image and was bound by
+// one SM's L2 port: 26-31 us per launch):
+//   rowdot: out[b,j] = f(sum_c W[j,c] * V[b,c])          warp = image, lanes stride c
+//           FWD: V = pool_sum*scale, f = +b1 (hidden);   BWD: V = dgate*gate*(1-gate) (also written
+//           out as dz2), f = * silu'(hidden[b,j]) (dh)
+//   coldot: out[b,c] = f(sum_j W[j,c] * U[b,j])          thread = channel
+//           FWD: U = silu(hidden), f = sigmoid(. + b2);  BWD: U = dh, f = identity (dpool)
+constexpr int kSeB = 8;     // images per CTA (= warps per CTA in rowdot)
+constexpr int kSeJ = 8;     // hidden units per CTA in rowdot / weight-gradient kernels
+
+template <bool BWD>
 __global__ void __launch_bounds__(kThreads)
-se_gate_fwd_kernel(const float* __restrict__ pool_sum, float pool_scale,
-                   const float* __restrict__ w1, const float* __restrict__ b1,
-                   const float* __restrict__ w2t, const float* __restrict__ b2,
-                   float* __restrict__ hidden, float* __restrict__ gate, int C, int Cs) {
-  extern __shared__ float s_se[];                 // [C] pooled, [Cs] activations
-  float* s_p = s_se;
-  float* s_a = s_se + C;
-  const int b = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int c = threadIdx.x; c < C; c += kThreads) s_p[c] = pool_sum[static_cast<int64_t>(b) * C + c] * pool_scale;
-  __syncthreads();
-  for (int j = warp; j < Cs; j += kThreads / 32) {
-    const float* wr = w1 + static_cast<int64_t>(j) * C;
-    float t = 0.f;
-    for (int c = lane; c < C; c += 32) t = fmaf(wr[c], s_p[c], t);
-    t = warp_sum(t);
-    if (lane == 0) {
-      const float h = t + b1[j];
-      hidden[static_cast<int64_t>(b) * Cs + j] = h;
-      s_a[j] = h * sigmoidf_(h);
+se_rowdot_kernel(const float* __restrict__ W, const float* __restrict__ v0,
+                 const float* __restrict__ v1, float v_scale, const float* __restrict__ bias,
+                 const float* __restrict__ hidden_in, float* __restrict__ out,
+                 float* __restrict__ dz2_out, int B, int C, int Cs) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int b = blockIdx.y * kSeB + warp, j0 = blockIdx.x * kSeJ;
+  if (b >= B) return;
+  float acc[kSeJ];
+#pragma unroll
+  for (int k = 0; k < kSeJ; ++k) acc[k] = 0.f;
+  const int64_t vb = static_cast<int64_t>(b) * C;
+  for (int c = lane; c < C; c += 32) {
+    float v;
+    if (BWD) {
+      const float g = v1[vb + c];
+      v = v0[vb + c] * g * (1.f - g);
+      if (blockIdx.x == 0) dz2_out[vb + c] = v;
+    } else {
+      v = v0[vb + c] * v_scale;
     }
+#pragma unroll
+    for (int k = 0; k < kSeJ; ++k)
+      if (j0 + k < Cs) acc[k] = fmaf(W[static_cast<int64_t>(j0 + k) * C + c], v, acc[k]);
   }
-  __syncthreads();
-  for (int c = threadIdx.x; c < C; c += kThreads) {
-    float z = b2[c];
-    for (int j = 0; j < Cs; ++j) z = fmaf(w2t[static_cast<int64_t>(j) * C + c], s_a[j], z);
-    gate[static_cast<int64_t>(b) * C + c] = sigmoidf_(z);
+#pragma unroll
+  for (int k = 0; k < kSeJ; ++k) acc[k] = warp_sum(acc[k]);
+  if (lane < kSeJ && j0 + lane < Cs) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < kSeJ; ++k) t = lane == k ? acc[k] : t;
+    const int64_t o = static_cast<int64_t>(b) * Cs + j0 + lane;
+    if (BWD) {
+      const float h = hidden_in[o];
+      const float sg = sigmoidf_(h);
+      out[o] = t * sg * fmaf(h, 1.f - sg, 1.f);
+    } else {
+      out[o] = t + bias[j0 + lane];
+    }
   }
 }
 
-// Per image: dz2 = dgate * gate * (1 - gate); da = w2t dz2; dh = da * silu'(hidden);
-// dpool = w1^T dh.  dz2 / dh are also written out for the weight-gradient kernel.
+template <bool BWD>
 __global__ void __launch_bounds__(kThreads)
-se_gate_bwd_kernel(const float* __restrict__ dgate, const float* __restrict__ gate,
-                   const float* __restrict__ hidden, const float* __restrict__ w1,
-                   const float* __restrict__ w2t, float* __restrict__ dz2, float* __restrict__ dh,
-                   float* __restrict__ dpool, int C, int Cs) {
-  extern __shared__ float s_se[];                 // [C] dz2, [Cs] dh
-  float* s_dz = s_se;
-  float* s_dh = s_se + C;
-  const int b = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int c = threadIdx.x; c < C; c += kThreads) {
-    const float g = gate[static_cast<int64_t>(b) * C + c];
-    const float d = dgate[static_cast<int64_t>(b) * C + c] * g * (1.f - g);
-    s_dz[c] = d;
-    dz2[static_cast<int64_t>(b) * C + c] = d;
-  }
-  __syncthreads();
-  for (int j = warp; j < Cs; j += kThreads / 32) {
-    const float* wr = w2t + static_cast<int64_t>(j) * C;
+se_coldot_kernel(const float* __restrict__ W, const float* __restrict__ u,
+                 const float* __restrict__ bias, float* __restrict__ out, int B, int C, int Cs) {
+  extern __shared__ float s_se[];                 // [kSeB][Cs]: silu(hidden) or dh of the CTA's images
+  const int b0 = blockIdx.y * kSeB;
+  for (int i = threadIdx.x; i < kSeB * Cs; i += kThreads) {
+    const int bb = b0 + i / Cs;
     float t = 0.f;
-    for (int c = lane; c < C; c += 32) t = fmaf(wr[c], s_dz[c], t);
-    t = warp_sum(t);
-    if (lane == 0) {
-      const float h = hidden[static_cast<int64_t>(b) * Cs + j];
-      const float sg = sigmoidf_(h);
-      const float d = t * sg * fmaf(h, 1.f - sg, 1.f);
-      s_dh[j] = d;
-      dh[static_cast<int64_t>(b) * Cs + j] = d;
+    if (bb < B) {
+      t = u[static_cast<int64_t>(bb) * Cs + i % Cs];
+      if (!BWD) t = t * sigmoidf_(t);
     }
+    s_se[i] = t;
   }
   __syncthreads();
-  for (int c = threadIdx.x; c < C; c += kThreads) {
-    float t = 0.f;
-    for (int j = 0; j < Cs; ++j) t = fmaf(w1[static_cast<int64_t>(j) * C + c], s_dh[j], t);
-    dpool[static_cast<int64_t>(b) * C + c] = t;
+  const int c = blockIdx.x * kThreads + threadIdx.x;
+  if (c >= C) return;
+  float acc[kSeB];
+#pragma unroll
+  for (int k = 0; k < kSeB; ++k) acc[k] = 0.f;
+#pragma unroll 4
+  for (int j = 0; j < Cs; ++j) {
+    const float w = W[static_cast<int64_t>(j) * C + c];
+#pragma unroll
+    for (int k = 0; k < kSeB; ++k) acc[k] = fmaf(w, s_se[k * Cs + j], acc[k]);
   }
+  const float bc = BWD ? 0.f : bias[c];
+#pragma unroll
+  for (int k = 0; k < kSeB; ++k)
+    if (b0 + k < B)
+      out[static_cast<int64_t>(b0 + k) * C + c] = BWD ? acc[k] : sigmoidf_(acc[k] + bc);
 }
 
 // dw1[j,c] = sum_b dh[b,j] * pooled[b,c];  dw2t[j,c] = sum_b silu(hidden[b,j]) * dz2[b,c];
 // db1[j] = sum_b dh[b,j];  db2[c] = sum_b dz2[b,c].   grid = (C / 256, Cs / kSeJ); a thread owns one
 // channel and kSeJ hidden units, the per-image [kSeJ] vectors sit in shared memory.
-constexpr int kSeJ = 8;
 __global__ void __launch_bounds__(kThreads)
 se_gate_wgrad_kernel(const float* __restrict__ pool_sum, float pool_scale,
                      const float* __restrict__ hidden, const float* __restrict__ dz2,
@@ -716,10 +733,13 @@ bool se_gate_shape_ok(const char* who, int B, int C, int Cs, size_t smem) {
 int se_gate_fwd(const float* pool_sum, float pool_scale, const float* w1, const float* b1,
                 const float* w2t, const float* b2, float* hidden, float* gate, int B, int C, int Cs,
                 cudaStream_t stream) {
-  const size_t smem = sizeof(float) * (static_cast<size_t>(C) + Cs);
+  const size_t smem = sizeof(float) * kSeB * static_cast<size_t>(Cs);
   if (!se_gate_shape_ok("se_gate_fwd", B, C, Cs, smem)) return CNX_ERR_BAD_SHAPE;
-  se_gate_fwd_kernel<<<B, kThreads, smem, stream>>>(pool_sum, pool_scale, w1, b1, w2t, b2, hidden,
-                                                    gate, C, Cs);
+  const unsigned gb = (B + kSeB - 1) / kSeB;
+  se_rowdot_kernel<false><<<dim3((Cs + kSeJ - 1) / kSeJ, gb), kThreads, 0, stream>>>(
+      w1, pool_sum, nullptr, pool_scale, b1, nullptr, hidden, nullptr, B, C, Cs);
+  se_coldot_kernel<false><<<dim3((C + kThreads - 1) / kThreads, gb), kThreads, smem, stream>>>(
+      w2t, hidden, b2, gate, B, C, Cs);
   return status("se_gate_fwd");
 }
 
@@ -727,10 +747,14 @@ int se_gate_bwd(const float* dgate, const float* gate, const float* hidden, cons
                 float pool_scale, const float* w1, const float* w2t, float* dz2, float* dh,
                 float* dpool, float* dw1, float* db1, float* dw2t, float* db2, int B, int C, int Cs,
                 cudaStream_t stream) {
-  const size_t smem = sizeof(float) * (static_cast<size_t>(C) + Cs);
+  const size_t smem = sizeof(float) * kSeB * static_cast<size_t>(Cs);
   const size_t smem_w = sizeof(float) * 2 * static_cast<size_t>(B) * kSeJ;
   if (!se_gate_shape_ok("se_gate_bwd", B, C, Cs, smem > smem_w ? smem : smem_w)) return CNX_ERR_BAD_SHAPE;
-  se_gate_bwd_kernel<<<B, kThreads, smem, stream>>>(dgate, gate, hidden, w1, w2t, dz2, dh, dpool, C, Cs);
+  const unsigned gb = (B + kSeB - 1) / kSeB;
+  se_rowdot_kernel<true><<<dim3((Cs + kSeJ - 1) / kSeJ, gb), kThreads, 0, stream>>>(
+      w2t, dgate, gate, 1.f, nullptr, hidden, dh, dz2, B, C, Cs);
+  se_coldot_kernel<true><<<dim3((C + kThreads - 1) / kThreads, gb), kThreads, smem, stream>>>(
+      w1, dh, nullptr, dpool, B, C, Cs);
   dim3 grid((C + kThreads - 1) / kThreads, (Cs + kSeJ - 1) / kSeJ);
   se_gate_wgrad_kernel<<<grid, kThreads, smem_w, stream>>>(pool_sum, pool_scale, hidden, dz2, dh, dw1,
                                                            db1, dw2t, db2, B, C, Cs);

@@ -211,11 +211,11 @@ int cnx_se_scale_bwd_apply(const void* g, const float* gate, const float* dpool,
  *   pooled = pool_sum * pool_scale;  hidden = w1 pooled + b1  ([B,Cs], saved);
  *   gate = sigmoid(w2 silu(hidden) + b2)  ([B,C]).
  * w1 [Cs,C] is the reduce convolution's weight, w2t [Cs,C] the expand convolution's weight
- * TRANSPOSED (so that all reads are coalesced along C).  One CTA per image.
+ * TRANSPOSED (so that all reads are coalesced along C).
  * cnx_se_gate_bwd: from dgate [B,C] (cnx_se_scale_bwd_reduce) -> dpool [B,C] (gradient at the
  * pooled vector, for cnx_se_scale_bwd_apply), dw1 [Cs,C], db1 [Cs], dw2t [Cs,C], db2 [C] (all
- * overwritten); dz2 [B,C] and dh [B,Cs] are caller-owned scratch.  (C + Cs) * 4 B and
- * B * 64 B of shared memory must fit 48 KB. */
+ * overwritten); dz2 [B,C] and dh [B,Cs] are caller-owned scratch.  Cs * 32 B and B * 64 B of
+ * shared memory must fit 48 KB. */
 int cnx_se_gate_fwd(const float* pool_sum, float pool_scale, const float* w1, const float* b1,
                     const float* w2t, const float* b2, float* hidden, float* gate, int B, int C,
                     int Cs, void* stream);
