@@ -429,32 +429,48 @@ se_bwd_apply_kernel(const __nv_bfloat16* __restrict__ g, const float* __restrict
 constexpr int kSeB = 8;     // images per CTA (= warps per CTA in rowdot)
 constexpr int kSeJ = 8;     // hidden units per CTA in rowdot / weight-gradient kernels
 
+constexpr int kSeChunk = 1024;   // channels of the CTA's kSeJ weight rows staged per pass (32 KB)
 template <bool BWD>
 __global__ void __launch_bounds__(kThreads)
 se_rowdot_kernel(const float* __restrict__ W, const float* __restrict__ v0,
                  const float* __restrict__ v1, float v_scale, const float* __restrict__ bias,
                  const float* __restrict__ hidden_in, float* __restrict__ out,
                  float* __restrict__ dz2_out, int B, int C, int Cs) {
+  __shared__ __align__(16) float s_w[kSeJ][kSeChunk];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int b = blockIdx.y * kSeB + warp, j0 = blockIdx.x * kSeJ;
-  if (b >= B) return;
+  const bool live = b < B;
   float acc[kSeJ];
 #pragma unroll
   for (int k = 0; k < kSeJ; ++k) acc[k] = 0.f;
-  const int64_t vb = static_cast<int64_t>(b) * C;
-  for (int c = lane; c < C; c += 32) {
-    float v;
-    if (BWD) {
-      const float g = v1[vb + c];
-      v = v0[vb + c] * g * (1.f - g);
-      if (blockIdx.x == 0) dz2_out[vb + c] = v;
-    } else {
-      v = v0[vb + c] * v_scale;
+  const int64_t vb = static_cast<int64_t>(live ? b : 0) * C;
+  for (int c0 = 0; c0 < C; c0 += kSeChunk) {
+    const int n = min(kSeChunk, C - c0);          // multiple of 8 (C % 8 == 0)
+    __syncthreads();
+    for (int i = threadIdx.x * 4; i < kSeJ * n; i += kThreads * 4) {
+      const int k = i / n, c = i % n;
+      float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (j0 + k < Cs) w = *reinterpret_cast<const float4*>(W + static_cast<int64_t>(j0 + k) * C + c0 + c);
+      *reinterpret_cast<float4*>(&s_w[k][c]) = w;
     }
+    __syncthreads();
+    if (live) {
+#pragma unroll 4
+      for (int c = lane; c < n; c += 32) {
+        float v;
+        if (BWD) {
+          const float g = v1[vb + c0 + c];
+          v = v0[vb + c0 + c] * g * (1.f - g);
+          if (blockIdx.x == 0) dz2_out[vb + c0 + c] = v;
+        } else {
+          v = v0[vb + c0 + c] * v_scale;
+        }
 #pragma unroll
-    for (int k = 0; k < kSeJ; ++k)
-      if (j0 + k < Cs) acc[k] = fmaf(W[static_cast<int64_t>(j0 + k) * C + c], v, acc[k]);
+        for (int k = 0; k < kSeJ; ++k) acc[k] = fmaf(s_w[k][c], v, acc[k]);
+      }
+    }
   }
+  if (!live) return;
 #pragma unroll
   for (int k = 0; k < kSeJ; ++k) acc[k] = warp_sum(acc[k]);
   if (lane < kSeJ && j0 + lane < Cs) {
