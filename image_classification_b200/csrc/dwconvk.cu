@@ -57,6 +57,21 @@ template <> struct Vec<4> {
   }
 };
 
+// packed 16-byte load (zeros when the pixel is padding) and its unpack: the conv kernels issue all
+// loads of a kernel row before the first FMA (a load per tap interleaved with its FMAs left one or
+// two loads in flight per thread)
+__device__ __forceinline__ uint4 ldg_or_zero(const __nv_bfloat16* p, bool ok) {
+  return ok ? __ldg(reinterpret_cast<const uint4*>(p)) : make_uint4(0u, 0u, 0u, 0u);
+}
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = bf16x2_to_f32x2(w[i]);
+    f[2 * i] = t.x; f[2 * i + 1] = t.y;
+  }
+}
+
 template <int VEC>
 __device__ __forceinline__ void load_w(const float* __restrict__ p, float (&w)[VEC]) {
 #pragma unroll
@@ -79,10 +94,12 @@ dwk_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ wt
   constexpr int P = K / 2, NC = (TW - 1) * S + K;
   const int nvec = g.C >> 3;
   const int strips = (g.Wo + TW - 1) / TW;
-  for (long long idx = static_cast<long long>(blockIdx.x) * kThreads + threadIdx.x; idx < total;
-       idx += static_cast<long long>(gridDim.x) * kThreads) {
+  // 32-bit work-item arithmetic (the launcher rejects total >= 2^31): six 64-bit div / mod per
+  // strip cost more instructions than the strip's FMAs
+  const unsigned utotal = static_cast<unsigned>(total), ustep = gridDim.x * kThreads;
+  for (unsigned idx = blockIdx.x * kThreads + threadIdx.x; idx < utotal; idx += ustep) {
     const int v = static_cast<int>(idx % nvec);
-    long long r = idx / nvec;
+    unsigned r = idx / nvec;
     const int strip = static_cast<int>(r % strips); r /= strips;
     const int oy = static_cast<int>(r % g.Ho);
     const int b = static_cast<int>(r / g.Ho);
@@ -101,12 +118,16 @@ dwk_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ wt
       float w[K][8];
 #pragma unroll
       for (int kw = 0; kw < K; ++kw) load_w<8>(wt + (kh * K + kw) * g.C + c0, w[kw]);
+      uint4 xr[NC];
 #pragma unroll
       for (int c = 0; c < NC; ++c) {
         const int ix = ix0 + c;
-        if (ix < 0 || ix >= g.W) continue;
+        xr[c] = ldg_or_zero(xrow + static_cast<long long>(ix) * g.C, ix >= 0 && ix < g.W);
+      }
+#pragma unroll
+      for (int c = 0; c < NC; ++c) {
         float xv[8];
-        Vec<8>::load(xrow + static_cast<long long>(ix) * g.C, xv);
+        unpack8(xr[c], xv);
 #pragma unroll
         for (int t = 0; t < TW; ++t) {
           const int kw = c - t * S;                      // compile-time after unrolling
@@ -135,10 +156,10 @@ dwk_bwd_data_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restric
   constexpr int LO = ceil_div(P - K + 1, S), HI = floor_div(TW - 1 + P, S), NC = HI - LO + 1;
   const int nvec = g.C >> 3;
   const int strips = (g.W + TW - 1) / TW;
-  for (long long idx = static_cast<long long>(blockIdx.x) * kThreads + threadIdx.x; idx < total;
-       idx += static_cast<long long>(gridDim.x) * kThreads) {
+  const unsigned utotal = static_cast<unsigned>(total), ustep = gridDim.x * kThreads;
+  for (unsigned idx = blockIdx.x * kThreads + threadIdx.x; idx < utotal; idx += ustep) {
     const int v = static_cast<int>(idx % nvec);
-    long long r = idx / nvec;
+    unsigned r = idx / nvec;
     const int strip = static_cast<int>(r % strips); r /= strips;
     const int iy = static_cast<int>(r % g.H);
     const int b = static_cast<int>(r / g.H);
@@ -159,12 +180,16 @@ dwk_bwd_data_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restric
       float w[K][8];
 #pragma unroll
       for (int kw = 0; kw < K; ++kw) load_w<8>(wt + (kh * K + kw) * g.C + c0, w[kw]);
+      uint4 dr[NC];
 #pragma unroll
       for (int j = 0; j < NC; ++j) {
         const int ox = oxb + j;
-        if (ox < 0 || ox >= g.Wo) continue;
+        dr[j] = ldg_or_zero(drow + static_cast<long long>(ox) * g.C, ox >= 0 && ox < g.Wo);
+      }
+#pragma unroll
+      for (int j = 0; j < NC; ++j) {
         float dv[8];
-        Vec<8>::load(drow + static_cast<long long>(ox) * g.C, dv);
+        unpack8(dr[j], dv);
 #pragma unroll
         for (int t = 0; t < TW; ++t) {
           const int kw = t + P - (LO + j) * S;           // compile-time
@@ -213,11 +238,12 @@ dwk_bwd_weight_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16*
   if (active) {
     const int c0 = v * VEC;
     const int strips = (g.Wo + TW - 1) / TW;
-    const long long s_begin = static_cast<long long>(blockIdx.y) * strips_per_cta;
-    const long long s_end = min(s_begin + strips_per_cta, strips_total);
-    for (long long sidx = s_begin + pl; sidx < s_end; sidx += npl) {
+    const unsigned s_begin = blockIdx.y * static_cast<unsigned>(strips_per_cta);
+    const unsigned s_end = min(s_begin + static_cast<unsigned>(strips_per_cta),
+                               static_cast<unsigned>(strips_total));
+    for (unsigned sidx = s_begin + pl; sidx < s_end; sidx += npl) {
       const int strip = static_cast<int>(sidx % strips);
-      long long r = sidx / strips;
+      const unsigned r = sidx / strips;
       const int oy = static_cast<int>(r % g.Ho);
       const int b = static_cast<int>(r / g.Ho);
       const int iy = oy * S - P + kh;
@@ -310,8 +336,12 @@ int launch_weight(const __nv_bfloat16* dy, const __nv_bfloat16* x, float* dwt, c
   const int vpb = nvec < 32 ? nvec : 32;
   const int npl = kThreads / vpb;
   const long long strips_total = static_cast<long long>(g.B) * g.Ho * ((g.Wo + TW - 1) / TW);
+  if (strips_total >= (1LL << 31) - (1LL << 24)) {
+    set_last_error("dwconv_kxk_bwd: %lld strips exceed the 32-bit index range", strips_total);
+    return CNX_ERR_BAD_SHAPE;
+  }
   const int gx = (nvec + vpb - 1) / vpb;
-  long long gy = (8LL * sm_count() + gx * K - 1) / (gx * K);        // ~8 CTAs per SM in total
+  long long gy = (12LL * sm_count() + gx * K - 1) / (gx * K);       // ~12 CTAs per SM in total
   const long long max_gy = (strips_total + npl - 1) / npl;
   if (gy > max_gy) gy = max_gy;
   if (gy < 1) gy = 1;
@@ -330,6 +360,10 @@ int dwconv_kxk_fwd(const void* x, const float* wt, void* y, int B, int H, int W,
   if (int rc = check_geo("dwconv_kxk_fwd", B, H, W, C, k, stride)) return rc;
   const Geo g = make_geo(B, H, W, C, k, stride);
   const long long total = static_cast<long long>(B) * g.Ho * ((g.Wo + TW - 1) / TW) * (C >> 3);
+  if (total >= (1LL << 31) - (1LL << 24)) {
+    set_last_error("dwconv_kxk_fwd: %lld work items exceed the 32-bit index range", total);
+    return CNX_ERR_BAD_SHAPE;
+  }
   const unsigned grid = grid_for(total);
   const __nv_bfloat16* xp = static_cast<const __nv_bfloat16*>(x);
   __nv_bfloat16* yp = static_cast<__nv_bfloat16*>(y);
@@ -350,6 +384,10 @@ int dwconv_kxk_bwd(const void* dy, const void* x, const float* wt, void* dx, flo
   const __nv_bfloat16* xp = static_cast<const __nv_bfloat16*>(x);
   if (dx != nullptr) {
     const long long total = static_cast<long long>(B) * H * ((W + TW - 1) / TW) * (C >> 3);
+    if (total >= (1LL << 31) - (1LL << 24)) {
+      set_last_error("dwconv_kxk_bwd: %lld work items exceed the 32-bit index range", total);
+      return CNX_ERR_BAD_SHAPE;
+    }
     const unsigned grid = grid_for(total);
     __nv_bfloat16* dxp = static_cast<__nv_bfloat16*>(dx);
 #define CNX_DWK_BD(KK, SS) dwk_bwd_data_kernel<KK, SS><<<grid, kThreads, 0, stream>>>(dyp, wt, dxp, g, total)
@@ -362,10 +400,10 @@ int dwconv_kxk_bwd(const void* dy, const void* x, const float* wt, void* dx, flo
   }
   if (dwt != nullptr) {
     if (!accumulate) cudaMemsetAsync(dwt, 0, sizeof(float) * k * k * C, stream);
-    if (k == 3 && stride == 1) return launch_weight<3, 1, 8>(dyp, xp, dwt, g, stream);
-    if (k == 3) return launch_weight<3, 2, 8>(dyp, xp, dwt, g, stream);
-    if (stride == 1) return launch_weight<5, 1, 8>(dyp, xp, dwt, g, stream);
-    return launch_weight<5, 2, 8>(dyp, xp, dwt, g, stream);
+    if (k == 3 && stride == 1) return launch_weight<3, 1, 4>(dyp, xp, dwt, g, stream);
+    if (k == 3) return launch_weight<3, 2, 4>(dyp, xp, dwt, g, stream);
+    if (stride == 1) return launch_weight<5, 1, 4>(dyp, xp, dwt, g, stream);
+    return launch_weight<5, 2, 4>(dyp, xp, dwt, g, stream);
   }
   return CNX_OK;
 }
