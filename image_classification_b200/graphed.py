@@ -8,7 +8,9 @@ the caller's stream with no host synchronisation and no library-owned memory, so
 micro-step can be recorded once and replayed: `GraphedForwardBackward` follows PyTorch's
 whole-network capture recipe (side-stream warm-up, static input / output tensors, gradients living
 in the graph's private pool).  The optimizer half of the step stays outside the graph
-(`optim_step.FusedOptimStep`: two launches, learning rate free to change every step).
+(`optim_step.FusedOptimStep`: two launches, learning rate free to change every step).  With
+`grad_reducer=` the data-parallel gradient all-reduce (ddp.BucketedGradReducer, NCCL) is captured
+inside the same graph.
 
 Contract: fixed batch shape; parameters are not re-allocated after capture; after `__call__` the
 `.grad` of every parameter that received a gradient is the graph's static buffer holding THIS
@@ -23,10 +25,14 @@ import torch
 class GraphedForwardBackward:
     def __init__(self, model: torch.nn.Module, criterion, scaler, example_images: torch.Tensor,
                  example_labels: torch.Tensor, amp_dtype: torch.dtype = torch.bfloat16,
-                 warmup: int = 3):
+                 warmup: int = 3, grad_reducer=None):
         if not example_images.is_cuda:
             raise RuntimeError("GraphedForwardBackward needs CUDA tensors (no CPU path)")
         self.model, self.criterion, self.scaler, self.amp_dtype = model, criterion, scaler, amp_dtype
+        # ddp.BucketedGradReducer or None: its bucket all-reduces are issued from the gradient
+        # hooks DURING the captured backward and joined at its end, so a replay overlaps NCCL
+        # with the remaining backward kernels exactly like the eager loop does
+        self.reducer = grad_reducer
         self.images = example_images.clone(memory_format=torch.preserve_format)
         self.labels = example_labels.clone()
         self.params = [p for p in model.parameters() if p.requires_grad]
@@ -46,12 +52,16 @@ class GraphedForwardBackward:
         self.grads = [p.grad for p in self.params]          # static buffers in the graph's pool
 
     def _fwd_bwd(self):
+        if self.reducer is not None:
+            self.reducer.set_sync(True)
         with torch.autocast("cuda", dtype=self.amp_dtype):
             outputs = self.model(self.images)
             if isinstance(outputs, (list, tuple)):
                 outputs = outputs[0]
             loss = self.criterion(outputs, self.labels)
         (self.scaler.scale(loss) if self.scaler is not None else loss).backward()
+        if self.reducer is not None:
+            self.reducer.finish()
         return loss.detach(), outputs.detach()
 
     def __call__(self, images: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:

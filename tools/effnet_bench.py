@@ -77,7 +77,7 @@ def kernel_rows(B, dev, flush, hbm_peak, once=False):
     return rows
 
 
-def train_step_ms(model, x, labels, steps, warmup, fused=False, graphed=False):
+def train_step_ms(model, x, labels, steps, warmup, fused=False, graphed=False, world=1):
     """The reference V3 step (train_advanced_v3.0.py:96-113) with bf16 autocast.  fused: the same
     sequence through train_step.TrainStep (accumulation 1, no EMA): library soft-CE kernel and
     unscale + clip + AdamW as two launches (optim_step.FusedOptimStep)."""
@@ -94,12 +94,20 @@ def train_step_ms(model, x, labels, steps, warmup, fused=False, graphed=False):
         from image_classification_b200.graphed import GraphedForwardBackward
         from image_classification_b200.loss import SoftTargetCrossEntropyB200
         from image_classification_b200.optim_step import FusedOptimStep
-        gfb = GraphedForwardBackward(model, SoftTargetCrossEntropyB200(0.0), scaler, x, labels)
+        reducer = None
+        if world > 1:        # data parallel: bucketed NCCL all-reduce captured inside the graph
+            from image_classification_b200.ddp import BucketedGradReducer
+            reducer = BucketedGradReducer(list(model.parameters()), bucket_bytes=8 << 20)
+        gfb = GraphedForwardBackward(model, SoftTargetCrossEntropyB200(0.0), scaler, x, labels,
+                                     grad_reducer=reducer if os.environ.get("EFFNET_NCCL_OUTSIDE") is None else None)
         fo = FusedOptimStep(model, opt, scaler, None, 1.0)
 
     def step():
         if graphed:                      # one graph launch + the two optimizer launches
             loss = gfb(x, labels)
+            if reducer is not None and gfb.reducer is None:     # A/B: all-reduce after the replay
+                reducer.set_sync(True)
+                reducer.finish()         # hooks do not fire in a replay: finish() sends every bucket
             fo.step()
             return loss
         if fused:
@@ -118,13 +126,19 @@ def train_step_ms(model, x, labels, steps, warmup, fused=False, graphed=False):
     for _ in range(warmup):
         step()
     torch.cuda.synchronize()
+    if world > 1:
+        torch.distributed.barrier()
+        torch.cuda.synchronize()
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     s.record()
     for _ in range(steps):
         loss = step()
     e.record()
     torch.cuda.synchronize()
-    return s.elapsed_time(e) / steps, float(loss.detach())
+    ms = torch.tensor([s.elapsed_time(e) / steps], device=x.device)
+    if world > 1:
+        torch.distributed.all_reduce(ms, op=torch.distributed.ReduceOp.MAX)     # slowest rank
+    return float(ms), float(loss.detach())
 
 
 def main():
@@ -140,7 +154,13 @@ def main():
                     help="torch.profiler kernel table of 3 eager steps of the library arm (diagnosis)")
     args = ap.parse_args()
     import torchvision
-    dev = torch.device("cuda:0")
+    world, rank = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:            # torchrun: one process per GPU, NCCL over NVLink
+        torch.distributed.init_process_group("nccl", device_id=dev)
+        args.skip_kernels = True
     peaks = {}
     pk = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")
     if os.path.exists(pk):
@@ -162,9 +182,11 @@ def main():
     for m in base.modules():                  # timm's create_model defaults: no drop-path
         if isinstance(m, torchvision.ops.StochasticDepth):
             m.p = 0.0
+    torch.manual_seed(1 + rank)               # same weights on every rank, different batches
     x = torch.randn(args.batch, 3, args.res, args.res, device=dev).contiguous(
         memory_format=torch.channels_last)
     labels = torch.randint(0, 44, (args.batch,), device=dev)
+    out["n_gpus"] = world
     if args.profile:
         from torch.profiler import ProfilerActivity, profile
         model = copy.deepcopy(base)
@@ -176,20 +198,27 @@ def main():
         print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=45,
                                         max_name_column_width=70))
         return
-    for arm in ("b200", "b200_fused_optim", "b200_graphed", "torch_bf16_channels_last"):
+    arms = ("b200_graphed",) if world > 1 else ("b200", "b200_fused_optim", "b200_graphed",
+                                                "torch_bf16_channels_last")
+    for arm in arms:
         model = copy.deepcopy(base)
         if arm.startswith("b200"):
             out["swapped"] = swap_efficientnet(model)
         model = model.to(memory_format=torch.channels_last)
         n0 = _lib.launch_count
         ms, loss = train_step_ms(model, x, labels, args.steps, args.warmup,
-                                 fused=arm == "b200_fused_optim", graphed=arm == "b200_graphed")
-        out[arm] = {"ms_per_step": round(ms, 3), "images_per_s": round(args.batch / ms * 1e3, 1),
+                                 fused=arm == "b200_fused_optim", graphed=arm == "b200_graphed",
+                                 world=world)
+        out[arm] = {"ms_per_step": round(ms, 3),
+                    "images_per_s": round(world * args.batch / ms * 1e3, 1),
                     "loss": round(loss, 4),
                     "lib_launches_per_step": (_lib.launch_count - n0) // (args.steps + args.warmup)}
         del model
         torch.cuda.empty_cache()
-    print(json.dumps(out))
+    if rank == 0:
+        print(json.dumps(out))
+    if world > 1:
+        torch.distributed.destroy_process_group()
 
 
 if __name__ == "__main__":
