@@ -313,43 +313,74 @@ def _rebind_bn(bn: nn.BatchNorm2d, act: str | None) -> BatchNormActB200:
     return new.train(bn.training)
 
 
-def _is_se(m: nn.Module) -> bool:
-    return (all(hasattr(m, a) for a in ("fc1", "fc2", "activation", "scale_activation"))
-            and isinstance(m.activation, nn.SiLU) and isinstance(m.scale_activation, nn.Sigmoid)
-            and isinstance(m.fc1, nn.Conv2d) and isinstance(m.fc2, nn.Conv2d)
-            and m.fc1.bias is not None and m.fc2.bias is not None)
+def _se_names(m: nn.Module):
+    """(reduce, expand) attribute names if `m` is a SiLU / sigmoid squeeze-excite block in
+    torchvision's (`fc1`, `fc2`, `activation`, `scale_activation`) or timm's (`conv_reduce`,
+    `conv_expand`, `act1`, `gate`) layout, else None."""
+    for red, exp, act, gate in (("fc1", "fc2", "activation", "scale_activation"),
+                                ("conv_reduce", "conv_expand", "act1", "gate")):
+        if (all(hasattr(m, a) for a in (red, exp, act, gate)) and not isinstance(m, SqueezeExciteB200)
+                and isinstance(getattr(m, act), nn.SiLU) and isinstance(getattr(m, gate), nn.Sigmoid)
+                and isinstance(getattr(m, red), nn.Conv2d) and isinstance(getattr(m, exp), nn.Conv2d)
+                and getattr(m, red).bias is not None and getattr(m, exp).bias is not None):
+            return red, exp
+    return None
+
+
+def _fused_bn_act(m: nn.Module):
+    """timm's `BatchNormAct2d` layout: an nn.BatchNorm2d subclass carrying its activation in
+    `.act` (SiLU or Identity) and a no-op `.drop`.  Returns (True, act) when it can be rebound."""
+    if (isinstance(m, nn.BatchNorm2d) and type(m) is not nn.BatchNorm2d
+            and not isinstance(m, BatchNormActB200) and hasattr(m, "act")
+            and isinstance(getattr(m, "drop", nn.Identity()), nn.Identity)):
+        if isinstance(m.act, nn.SiLU):
+            return True, "silu"
+        if isinstance(m.act, nn.Identity):
+            return True, None
+    return False, None
 
 
 def swap_efficientnet(model: nn.Module) -> dict:
-    """Install the library modules in an EfficientNet built from conv -> BatchNorm2d -> SiLU
-    sequences and squeeze-excite blocks (torchvision's layout; timm's un-fused layout alike):
-    depthwise / 1x1 convolutions (`swap_depthwise_separable`), every `nn.BatchNorm2d` inside an
-    `nn.Sequential` (the `nn.SiLU` after it is absorbed and replaced by `nn.Identity`), and every
-    SiLU / sigmoid squeeze-excite block; the BatchNorm right before a squeeze-excite block also
-    emits its pooled sums.  Parameters and buffers are the same objects.  Returns the counts."""
+    """Install the library modules in an EfficientNet: depthwise / 1x1 convolutions
+    (`swap_depthwise_separable`); every `nn.BatchNorm2d` inside an `nn.Sequential` (torchvision's
+    conv -> BatchNorm2d -> SiLU layout: the `nn.SiLU` after it is absorbed and replaced by
+    `nn.Identity`) and every BatchNorm-with-activation module of timm's `BatchNormAct2d` layout;
+    every SiLU / sigmoid squeeze-excite block in either library's naming.  The BatchNorm right
+    before a squeeze-excite block also emits its pooled sums.  Parameters and buffers are the same
+    objects, state_dict keys do not change.  Returns the counts."""
     n_dw, n_pw = swap_depthwise_separable(model)
     n_bn = n_se = 0
     for parent in list(model.modules()):
-        if not isinstance(parent, nn.Sequential):
-            continue
         kids = list(parent.named_children())
         for i, (name, child) in enumerate(kids):
-            if type(child) is nn.BatchNorm2d and child.affine and child.num_features % 8 == 0:
+            if child.__class__ is nn.BatchNorm2d and isinstance(parent, nn.Sequential):
+                if not (child.affine and child.num_features % 8 == 0):
+                    continue
                 nxt = kids[i + 1] if i + 1 < len(kids) else None
                 act = "silu" if nxt is not None and type(nxt[1]) is nn.SiLU else None
                 setattr(parent, name, _rebind_bn(child, act))
                 if act:
                     setattr(parent, nxt[0], nn.Identity())
                 n_bn += 1
+            else:
+                ok, act = _fused_bn_act(child)
+                if ok and child.affine and child.num_features % 8 == 0:
+                    setattr(parent, name, _rebind_bn(child, act))
+                    n_bn += 1
     for parent in list(model.modules()):
         kids = list(parent.named_children())
         for i, (name, child) in enumerate(kids):
-            if not _is_se(child):
+            names = _se_names(child)
+            if names is None:
                 continue
-            setattr(parent, name, SqueezeExciteB200(child.fc1, child.fc2).train(child.training))
+            se = SqueezeExciteB200(getattr(child, names[0]), getattr(child, names[1]), names)
+            setattr(parent, name, se.train(child.training))
             n_se += 1
-            if i > 0 and isinstance(kids[i - 1][1], nn.Sequential):
-                tail = [m for m in kids[i - 1][1].children() if not isinstance(m, nn.Identity)]
-                if tail and isinstance(tail[-1], BatchNormActB200):
-                    tail[-1].emit_pool = True      # its output is exactly what this block pools
+            if i > 0:                              # the module whose output this block pools
+                prev = getattr(parent, kids[i - 1][0])      # as rebound by the loop above
+                if isinstance(prev, nn.Sequential):
+                    tail = [m for m in prev.children() if not isinstance(m, nn.Identity)]
+                    prev = tail[-1] if tail else None
+                if isinstance(prev, BatchNormActB200):
+                    prev.emit_pool = True
     return {"depthwise": n_dw, "pointwise": n_pw, "batchnorm": n_bn, "squeeze_excite": n_se}

@@ -458,3 +458,44 @@ def test_graphed_forward_backward_matches_eager(cnx_lib):
         assert _rel(bn_g.running_var, bn_e.running_var) < 1e-3
     with pytest.raises(RuntimeError):
         gfb(batches[0][0][:4], batches[0][1][:4])             # captured for a fixed batch shape
+
+
+def test_timm_layout_efficientnet_swapped_vs_fp32(cnx_lib):
+    """The timm-layout stand-in (tests/_foreign.py: BatchNormAct2d, conv_reduce / conv_expand
+    squeeze-excite, DepthwiseSeparableConv / InvertedResidual) fully swapped under bf16 autocast,
+    one training forward/backward against the untouched fp32 model: logits, loss, every parameter
+    gradient as one vector, running statistics."""
+    import copy
+    from _foreign import TimmLikeEfficientNet
+    from image_classification_b200 import _lib
+    from image_classification_b200.efficientnet import swap_efficientnet
+    dev = _dev()
+    torch.manual_seed(2)
+    ref = TimmLikeEfficientNet().to(dev).train()
+    prod = copy.deepcopy(ref)
+    assert swap_efficientnet(prod)["batchnorm"] == 18
+    prod = prod.to(memory_format=torch.channels_last)
+    x = torch.randn(16, 3, 192, 192, device=dev)
+    labels = torch.randint(0, 44, (16,), device=dev)
+    crit = torch.nn.CrossEntropyLoss()
+    lo = ref(x)
+    loss_o = crit(lo, labels)
+    loss_o.backward()
+    n0 = _lib.launch_count
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        lp = prod(x.contiguous(memory_format=torch.channels_last))
+        loss_p = crit(lp.float(), labels)
+    loss_p.backward()
+    # 6 depthwise x 3 + 18 BatchNorm x 4 + 6 squeeze-excite x (2 + 1 + 1 + 3 + 1) at least
+    assert _lib.launch_count - n0 >= 6 * 3 + 18 * 4 + 6 * 8
+    assert _rel(lp.float(), lo) < 5e-2                       # 18 bf16 layers with batch statistics
+    assert abs(loss_p.item() - loss_o.item()) < BF16_REL * abs(loss_o.item())
+    go = torch.cat([p.grad.flatten() for p in ref.parameters()])
+    gp = torch.cat([p.grad.flatten() for p in prod.parameters()])
+    assert float((go - gp).norm() / go.norm()) < 5e-2
+    pm = dict(prod.named_modules())
+    for name, bn in ref.named_modules():
+        if isinstance(bn, torch.nn.BatchNorm2d):
+            std = float(bn.running_var.sqrt().max())
+            assert float((pm[name].running_mean - bn.running_mean).abs().max()) < 2e-2 * std, name
+            assert _rel(pm[name].running_var, bn.running_var) < 5e-2, name

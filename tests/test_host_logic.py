@@ -327,3 +327,40 @@ def test_swap_efficientnet_on_cpu_keeps_parameters_buffers_and_results():
     assert torch.allclose(m(x), ref(x), rtol=1e-5, atol=1e-6)
     again = swap_efficientnet(m)
     assert again["batchnorm"] == 0 and again["squeeze_excite"] == 0
+
+
+def test_swap_efficientnet_timm_layout_on_cpu():
+    """timm's layout (BatchNormAct2d modules outside nn.Sequential, conv_reduce / conv_expand
+    squeeze-excite, DepthwiseSeparableConv / InvertedResidual blocks; stand-ins in tests/_foreign.py
+    since timm is not installable): everything is swapped, state_dict keys / Parameter / buffer
+    objects are kept, and off the fast path the model computes what it did before."""
+    import copy
+    from _foreign import TimmLikeEfficientNet
+    from image_classification_b200.efficientnet import (BatchNormActB200, SqueezeExciteB200,
+                                                        swap_efficientnet)
+    torch.manual_seed(0)
+    m = TimmLikeEfficientNet()
+    ref = copy.deepcopy(m)
+    keys = list(m.state_dict())
+    params = {n: p for n, p in m.named_parameters()}
+    bufs = {n: b for n, b in m.named_buffers()}
+    counts = swap_efficientnet(m)
+    assert counts == {"depthwise": 6, "pointwise": 13, "batchnorm": 18, "squeeze_excite": 6}
+    assert not any(isinstance(c, torch.nn.BatchNorm2d) and not isinstance(c, BatchNormActB200)
+                   for c in m.modules())
+    assert sum(isinstance(c, SqueezeExciteB200) for c in m.modules()) == 6
+    # the BatchNorm feeding each squeeze-excite block (bn1 of DepthwiseSeparableConv, bn2 of
+    # InvertedResidual) hands over its pooled sums
+    assert m.blocks[0][0].bn1.emit_pool and m.blocks[1][0].bn2.emit_pool
+    assert not m.blocks[1][0].bn1.emit_pool and not m.blocks[1][0].bn3.emit_pool
+    assert m.blocks[1][0].bn3.act is None and m.blocks[1][0].bn2.act == "silu"
+    assert list(m.state_dict()) == keys
+    assert all(p is params[n] for n, p in m.named_parameters())
+    assert all(b is bufs[n] for n, b in m.named_buffers())
+    x = torch.randn(2, 3, 64, 64)
+    m.train(), ref.train()
+    assert torch.allclose(m(x), ref(x), rtol=1e-5, atol=1e-6)
+    for (n, a), (_, b) in zip(m.named_buffers(), ref.named_buffers()):
+        assert torch.allclose(a.float(), b.float(), rtol=1e-5, atol=1e-7), n
+    m.eval(), ref.eval()
+    assert torch.allclose(m(x), ref(x), rtol=1e-5, atol=1e-6)
