@@ -107,7 +107,8 @@ __device__ __forceinline__ void slab_reduce_atomic(const float (&acc)[8], float*
 }
 
 // ------------------------------------------------------------------ BatchNorm statistics
-// sums[0..C) += sum_m x[m,c], sums[C..2C) += sum_m x[m,c]^2   (sums zeroed by the launcher)
+// sums[0..C) += sum_m d[m,c], sums[C..2C) += sum_m d[m,c]^2 with d = x - x[0,c]   (sums zeroed
+// by the launcher)
 __global__ void __launch_bounds__(kThreads)
 bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums, int C, int HW,
                 int rows_per_cta, int lw) {
@@ -117,18 +118,24 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums, i
 #pragma unroll
   for (int k = 0; k < 8; ++k) a1[k] = a2[k] = 0.f;
   if (s.live) {
+    // sums of (x - pivot), pivot = row 0 of the matrix: E[d^2] - E[d]^2 then cancels only if the
+    // mean is many standard deviations away from a SAMPLE of the channel, not from zero
+    float pv[8];
+    unpack8(ldv(x + s.c0), pv);
     const __nv_bfloat16* xp = x + s.row0 * C + s.c0;
     for (int r = s.r_begin + s.rl; r < s.r_end; r += kBatch * s.nrl) {
       uint4 v[kBatch];
-      load_rows(v, xp, r, s, C);                  // rows past the end load zeros: they add nothing
+      load_rows(v, xp, r, s, C);
 #pragma unroll
       for (int j = 0; j < kBatch; ++j) {
+        if (r + j * s.nrl >= s.r_end) break;      // rows past the end loaded zeros, not the pivot
         float f[8];
         unpack8(v[j], f);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-          a1[k] += f[k];
-          a2[k] = fmaf(f[k], f[k], a2[k]);
+          const float d = f[k] - pv[k];
+          a1[k] += d;
+          a2[k] = fmaf(d, d, a2[k]);
         }
       }
     }
@@ -143,6 +150,7 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums, i
 // way nn.BatchNorm2d does.  Eval: from the running statistics.
 struct BnArgs {
   const float* sums;          // [2C] or nullptr (eval)
+  const __nv_bfloat16* pivot; // row 0 of x: the shift bn_stats subtracted
   const float* weight;        // [C]
   const float* bias;          // [C]
   float* running_mean;        // [C] or nullptr
@@ -158,8 +166,9 @@ __device__ __forceinline__ void bn_channel_consts(const BnArgs& p, int C, int c0
     const int c = c0 + k;
     float mean, var;
     if (p.sums != nullptr) {
-      mean = p.sums[c] * p.inv_m;
-      var = fmaxf(p.sums[C + c] * p.inv_m - mean * mean, 0.f);
+      const float dm = p.sums[c] * p.inv_m;
+      mean = __bfloat162float(p.pivot[c]) + dm;
+      var = fmaxf(p.sums[C + c] * p.inv_m - dm * dm, 0.f);
     } else {
       mean = p.running_mean[c];
       var = p.running_var[c];
@@ -659,7 +668,7 @@ int bn_act_fwd(const void* x, const float* sums, const float* weight, const floa
   if (!ok) return CNX_ERR_BAD_SHAPE;
   if (pool_sum != nullptr) cudaMemsetAsync(pool_sum, 0, sizeof(float) * B * C, stream);
   BnArgs p;
-  p.sums = sums; p.weight = weight; p.bias = bias;
+  p.sums = sums; p.pivot = static_cast<const __nv_bfloat16*>(x); p.weight = weight; p.bias = bias;
   p.running_mean = running_mean; p.running_var = running_var;
   p.mean_out = mean_out; p.rstd_out = rstd_out;
   p.inv_m = 1.0f / static_cast<float>(M);

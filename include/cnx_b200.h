@@ -175,7 +175,9 @@ int cnx_avgpool_nhwc_bwd(const void* g, void* dx, int B, int HW, int C, void* st
  * (timm BatchNormAct2d) of efficientnet_b2's MBConv blocks (model built at
  * /root/reference/previous/V3-efb2/train_advanced_v3.0.py:330; forward / backward :100-104;
  * SURVEY.md §8 f-4).  Replaces F.batch_norm(training) -> F.silu and their autograd backward.
- *   cnx_bn_stats   : sums[0..C) = sum_m x[m,c], sums[C..2C) = sum_m x[m,c]^2 (fp32, overwritten).
+ *   cnx_bn_stats   : sums[0..C) = sum_m d[m,c], sums[C..2C) = sum_m d[m,c]^2 with d = x - x[0,c]
+ *                    (fp32, overwritten; shifted sums: no cancellation for channels whose mean is
+ *                    far from zero).  cnx_bn_act_fwd must be given the same x, and y must not alias x.
  *   cnx_bn_act_fwd : y = act((x - mean) * rstd * weight + bias), act 0 = identity, 1 = SiLU.
  *                    sums != NULL: training (mean / biased var from sums over M = B*HW rows;
  *                    running_mean / running_var, when given, are updated with `momentum` and the

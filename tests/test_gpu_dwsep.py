@@ -499,3 +499,24 @@ def test_timm_layout_efficientnet_swapped_vs_fp32(cnx_lib):
             std = float(bn.running_var.sqrt().max())
             assert float((pm[name].running_mean - bn.running_mean).abs().max()) < 2e-2 * std, name
             assert _rel(pm[name].running_var, bn.running_var) < 5e-2, name
+
+
+def test_bn_statistics_of_channels_far_from_zero(cnx_lib):
+    """Channel means 60 standard deviations from zero over 10^5 rows: the statistics are shifted
+    sums (x - x[0,c]), so E[d^2] - E[d]^2 does not cancel; mean, rstd and the normalised output
+    stay at the fp32 / bf16 level of the float64 oracle."""
+    from image_classification_b200 import ops
+    dev = _dev()
+    torch.manual_seed(11)
+    B, H, W, C = 32, 56, 56, 24
+    offs = torch.linspace(-60.0, 60.0, C, device=dev)
+    x = (offs + 0.5 * torch.randn(B, H, W, C, device=dev)).bfloat16()
+    w = torch.rand(C, device=dev) + 0.5
+    b = torch.randn(C, device=dev) * 0.1
+    y, mean, rstd, _ = ops.bn_act_fwd(x, w, b, None, None, training=True, momentum=0.1, eps=1e-5,
+                                      act=ops.ACT_NONE)
+    y_ref, mean_ref, var_ref = dwsep_oracle.bn_act_fwd_ref(
+        x.double().cpu().numpy().reshape(-1, C), w.cpu().numpy(), b.cpu().numpy(), 1e-5, False)
+    assert _rel(mean.cpu(), torch.from_numpy(mean_ref)) < 1e-6
+    assert float((rstd.cpu().double() * torch.from_numpy(np.sqrt(var_ref + 1e-5)) - 1).abs().max()) < 1e-4
+    assert _rel(y.cpu().reshape(-1, C), torch.from_numpy(y_ref)) < 2.0 ** -7
