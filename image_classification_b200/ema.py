@@ -92,3 +92,48 @@ class EMAB200:
         to_dev = lambda a: torch.from_numpy(a).to(dev)
         self._table = (to_dev(pp), to_dev(sp), to_dev(numel), to_dev(prefix), len(params),
                        int(prefix[-1]))
+
+
+class AveragedModelB200(torch.nn.Module):
+    """`torch.optim.swa_utils.AveragedModel(model)` with its default equal-weight average, as the
+    older reference loop uses it for SWA (/root/reference/previous/V3-efb2/train_advanced_v3.0.py:445
+    construction, :505-507 `swa_model.update_parameters(model)` once per epoch after `swa_start`):
+    same attributes (`module`, `n_averaged`), same state_dict keys, same result
+    `avg <- avg + (p - avg) / (n + 1)`  (the first call copies), but ONE `cnx_ema_lerp_multi` launch
+    over all parameters instead of a foreach pass per call.  Buffers (BatchNorm statistics) are not
+    averaged, as with torch's default `use_buffers=False`."""
+
+    def __init__(self, model: torch.nn.Module):
+        super().__init__()
+        import copy
+        self.module = copy.deepcopy(model)
+        dev = next(model.parameters()).device
+        self.register_buffer("n_averaged", torch.tensor(0, dtype=torch.long, device=dev))
+        self._n = 0                        # host mirror of n_averaged: no device read per update
+        self._lerp = EMAB200.__new__(EMAB200)
+        self._lerp._table, self._lerp._table_key = None, None
+
+    def forward(self, *args, **kwargs):
+        return self.module(*args, **kwargs)
+
+    def update_parameters(self, model: torch.nn.Module) -> None:
+        params = [p.data for p in model.parameters()]
+        avgs = [p.data for p in self.module.parameters()]
+        if len(params) != len(avgs):
+            raise _lib.CnxError("AveragedModelB200: the model does not match the averaged copy")
+        dev = params[0].device
+        if dev.type != "cuda":
+            raise _lib.CnxError("AveragedModelB200.update_parameters: parameters must live on a "
+                                "CUDA device (no CPU path)")
+        key = tuple(p.data_ptr() for p in params) + tuple(s.data_ptr() for s in avgs)
+        if self._lerp._table is None or self._lerp._table_key != key:
+            self._lerp._build_table(params, avgs, dev)
+            self._lerp._table_key = key
+        pp, sp, numels, prefix, T, total = self._lerp._table
+        n = self._n
+        w = 1.0 if n == 0 else 1.0 / (n + 1)               # weight of the new parameters
+        _lib.call("cnx_ema_lerp_multi", pp.data_ptr(), sp.data_ptr(), numels.data_ptr(),
+                  prefix.data_ptr(), T, total, float(np.float32(w)), float(np.float32(1.0 - w)),
+                  torch.cuda.current_stream(dev).cuda_stream)
+        self._n += 1
+        self.n_averaged += 1

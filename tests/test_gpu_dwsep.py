@@ -520,3 +520,30 @@ def test_bn_statistics_of_channels_far_from_zero(cnx_lib):
     assert _rel(mean.cpu(), torch.from_numpy(mean_ref)) < 1e-6
     assert float((rstd.cpu().double() * torch.from_numpy(np.sqrt(var_ref + 1e-5)) - 1).abs().max()) < 1e-4
     assert _rel(y.cpu().reshape(-1, C), torch.from_numpy(y_ref)) < 2.0 ** -7
+
+
+def test_averaged_model_matches_torch_swa(cnx_lib):
+    """ema.AveragedModelB200 vs torch.optim.swa_utils.AveragedModel (the reference's SWA,
+    previous/V3-efb2/train_advanced_v3.0.py:445, :505-507) over four updates of a drifting model:
+    same state_dict keys, parameters equal to fp32 rounding, n_averaged counts."""
+    import copy
+    from torch.optim.swa_utils import AveragedModel
+    from _foreign import TimmLikeEfficientNet
+    from image_classification_b200.ema import AveragedModelB200
+    dev = _dev()
+    torch.manual_seed(4)
+    model = TimmLikeEfficientNet().to(dev)
+    ref, swa = AveragedModel(copy.deepcopy(model)), AveragedModelB200(model)
+    assert list(swa.state_dict()) == list(ref.state_dict())
+    for step in range(4):
+        with torch.no_grad():
+            for p in model.parameters():
+                p.add_(torch.randn_like(p) * 0.05)
+        ref.update_parameters(model)
+        swa.update_parameters(model)
+        assert int(swa.n_averaged) == int(ref.n_averaged) == step + 1
+        for (n, a), (_, b) in zip(swa.module.named_parameters(), ref.module.named_parameters()):
+            assert torch.allclose(a, b, rtol=1e-5, atol=1e-7), (step, n)
+    x = torch.randn(2, 3, 64, 64, device=dev)
+    swa.eval(), ref.eval()
+    assert torch.allclose(swa(x), ref(x), rtol=1e-4, atol=1e-5)
