@@ -112,6 +112,13 @@ for r in range(world):
 for a, p in zip(ref, model.parameters()):
     assert torch.allclose(a, p.grad, atol=1e-6), (rank, (a - p.grad).abs().max())
 assert all(p.grad is None for p in unused.parameters())
+# gradients that appear WITHOUT the hooks firing (what a CUDA-graph replay leaves in the static
+# .grad buffers, graphed.GraphedForwardBackward): finish() sends every bucket itself
+local = [torch.full_like(p, float(rank + 1)) for p in model.parameters()]
+for p, gl in zip(model.parameters(), local): p.grad = gl.clone()
+red.set_sync(True); red.finish()
+for p in model.parameters():
+    assert torch.allclose(p.grad, torch.full_like(p, 1.5)), rank      # mean of 1 and 2
 dist.barrier(); dist.destroy_process_group()
 print("rank", rank, "ok")
 '''
