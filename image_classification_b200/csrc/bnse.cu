@@ -6,8 +6,10 @@
 // (/root/reference/previous/V3-efb2/train_advanced_v3.0.py:330 model, :100-104 forward/backward):
 //   conv -> BatchNorm2d -> SiLU            => bn_stats + bn_act_fwd          (2 passes over x)
 //   its autograd backward (5 ATen kernels) => bn_act_bwd_reduce + _apply     (2 passes over g, x)
-//   x * sigmoid(fc2(silu(fc1(avgpool(x))))) => pooled sums come out of bn_act_fwd for free,
-//                                             se_scale_fwd; backward se_bwd_reduce + se_bwd_apply
+//   x * sigmoid(fc2(silu(fc1(avgpool(x))))) => pooled sums come out of bn_act_fwd for free, the
+//                                             two [B,C] gate layers are se_rowdot / se_coldot /
+//                                             se_gate_wgrad, the scaling se_scale_fwd; backward
+//                                             se_bwd_reduce + se_bwd_apply
 //
 // One thread mapping for every kernel: a CTA owns a channel slab of LW 16-byte vectors (LW = 1, 2,
 // 4 or 8, i.e. 8..64 channels) and a range of rows of ONE image; its 256 threads are LW vector

@@ -21,13 +21,18 @@ the convolutions is on the library too (csrc/bnse.cu):
 * `BatchNormActB200`     — `nn.BatchNorm2d` (+ the SiLU that follows it) -> `cnx_bn_stats` +
   `cnx_bn_act_fwd`, backward `cnx_bn_act_bwd`; running statistics updated like nn.BatchNorm2d;
 * `SqueezeExciteB200`    — x * sigmoid(fc2(silu(fc1(mean x)))): the pooled sums come out of the
-  preceding `BatchNormActB200` pass, the two [B,C] gate layers are `cnx_se_gate_fwd/bwd` (one CTA
-  per image, fp32), the scaling and its backward are `cnx_se_scale_*`;
+  preceding `BatchNormActB200` pass, the two [B,C] gate layers are `cnx_se_gate_fwd/bwd` (fp32),
+  the scaling and its backward are `cnx_se_scale_*`;
 * `swap_efficientnet(model)` installs all four kinds.
 
-timm is not installable here; the
-swap is written against `nn.Conv2d` attributes only, so it applies to timm's and torchvision's
-EfficientNets alike (the parity tests use torchvision's `efficientnet_b2`, same architecture).
+timm is not installable here; the swap recognises modules by structure (torchvision's
+conv -> BatchNorm2d -> SiLU sequences and `SqueezeExcitation`, timm's `BatchNormAct2d` and
+`SqueezeExcite` layouts), so it applies to both libraries' EfficientNets: the parity tests use
+torchvision's `efficientnet_b2` (same architecture) and timm-layout stand-ins (tests/_foreign.py).
+A CUDA activation that misses the library path because autocast is off or not bf16 (the
+reference's own default is fp16, train_advanced_v3.0.py:103) is reported once with a warning —
+the modules then behave like the torch modules they subclass, they never route through a CPU or
+oracle path, and on the library path a missing `libcnx_b200.so` raises.
 """
 from __future__ import annotations
 
@@ -35,6 +40,19 @@ import torch
 from torch import nn
 
 from . import _lib, ops
+
+
+_warned: set[str] = set()
+
+
+def _note_off_path(who: str, x: torch.Tensor) -> None:
+    """One warning per module kind when a CUDA activation runs on torch's kernels instead."""
+    if x.is_cuda and who not in _warned:
+        _warned.add(who)
+        import warnings
+        warnings.warn(f"{who}: CUDA input of dtype {x.dtype} is not on the libcnx_b200 path "
+                      "(needs bf16 activations or torch.autocast('cuda', dtype=torch.bfloat16)); "
+                      "running the torch module it subclasses", stacklevel=3)
 
 
 def _autocast_bf16() -> bool:
@@ -90,6 +108,8 @@ class DepthwiseConv2dB200(nn.Conv2d):
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if self._fast(x):
             return _DepthwiseFn.apply(x, self.weight, self.kernel_size[0], self.stride[0])
+        if x.dtype != torch.bfloat16 and not _autocast_bf16():
+            _note_off_path("DepthwiseConv2dB200", x)
         return super().forward(x)
 
 
@@ -147,6 +167,8 @@ class PointwiseConv2dB200(nn.Conv2d):
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if self._fast(x):
             return _PointwiseFn.apply(x, self.weight, self.bias)
+        if not _autocast_bf16():
+            _note_off_path("PointwiseConv2dB200", x)
         return super().forward(x)
 
 
@@ -233,6 +255,8 @@ class BatchNormActB200(nn.BatchNorm2d):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if not self._fast(x):
+            if x.dtype != torch.bfloat16 and not _autocast_bf16():
+                _note_off_path("BatchNormActB200", x)
             y = super().forward(x)
             return torch.nn.functional.silu(y) if self.act == "silu" else y
         training = self.training or self.running_mean is None
