@@ -264,13 +264,15 @@ bn_act_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat1
 #pragma unroll
   for (int k = 0; k < 8; ++k) a1[k] = a2[k] = 0.f;
   if (s.live) {
-    float mu[8], rs[8], w[8], b[8];
+    // per channel: xhat = x * rs + nmr, u = x * A + Bc  (one FMA each, four constants instead of
+    // mean / rstd / weight / bias kept apart)
+    float rs[8], nmr[8], A[8], Bc[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      mu[k] = p.mean[s.c0 + k];
       rs[k] = p.rstd[s.c0 + k];
-      w[k] = p.weight[s.c0 + k];
-      b[k] = p.bias[s.c0 + k];
+      nmr[k] = -p.mean[s.c0 + k] * rs[k];
+      A[k] = p.weight[s.c0 + k] * rs[k];
+      Bc[k] = fmaf(nmr[k], p.weight[s.c0 + k], p.bias[s.c0 + k]);
     }
     const int64_t base = s.row0 * C + s.c0;
     for (int r = s.r_begin + s.rl; r < s.r_end; r += 2 * s.nrl) {
@@ -284,8 +286,8 @@ bn_act_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat1
         unpack8(vx[j], fx);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-          const float xh = (fx[k] - mu[k]) * rs[k];
-          const float du = act_grad<ACT>(fg[k], fmaf(xh, w[k], b[k]));
+          const float xh = fmaf(fx[k], rs[k], nmr[k]);
+          const float du = act_grad<ACT>(fg[k], fmaf(fx[k], A[k], Bc[k]));
           a1[k] += du;
           a2[k] = fmaf(du, xh, a2[k]);
         }
@@ -304,15 +306,18 @@ bn_act_bwd_apply_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16
                         int rows_per_cta, int lw) {
   const Slot s = make_slot(lw, C, HW, rows_per_cta);
   if (!s.live) return;
-  float mu[8], rs[8], w[8], b[8], k1[8], k2[8];
+  // dx = A * du + x * P + Q with A = w * rstd, P = -A * k2 * rstd, Q = -A * (k1 + k2 * nmr),
+  // k1 = dbias / M, k2 = dweight / M, nmr = -mean * rstd; u = x * A + Bc as in the reduce pass
+  float A[8], Bc[8], P[8], Q[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
-    mu[k] = p.mean[s.c0 + k];
-    rs[k] = p.rstd[s.c0 + k];
-    w[k] = p.weight[s.c0 + k];
-    b[k] = p.bias[s.c0 + k];
-    k1[k] = p.dbias[s.c0 + k] * p.inv_m;
-    k2[k] = p.dweight[s.c0 + k] * p.inv_m;
+    const float rs = p.rstd[s.c0 + k], w = p.weight[s.c0 + k];
+    const float nmr = -p.mean[s.c0 + k] * rs;
+    const float k1 = p.dbias[s.c0 + k] * p.inv_m, k2 = p.dweight[s.c0 + k] * p.inv_m;
+    A[k] = w * rs;
+    Bc[k] = fmaf(nmr, w, p.bias[s.c0 + k]);
+    P[k] = -A[k] * k2 * rs;
+    Q[k] = -A[k] * fmaf(k2, nmr, k1);
   }
   const int64_t base = s.row0 * C + s.c0;
   for (int r = s.r_begin + s.rl; r < s.r_end; r += 2 * s.nrl) {
@@ -328,9 +333,8 @@ bn_act_bwd_apply_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16
       unpack8(vx[j], fx);
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
-        const float xh = (fx[k] - mu[k]) * rs[k];
-        const float du = act_grad<ACT>(fg[k], fmaf(xh, w[k], b[k]));
-        fx[k] = w[k] * rs[k] * (du - k1[k] - xh * k2[k]);
+        const float du = act_grad<ACT>(fg[k], fmaf(fx[k], A[k], Bc[k]));
+        fx[k] = fmaf(A[k], du, fmaf(fx[k], P[k], Q[k]));
       }
       stv(dx + base + static_cast<int64_t>(rr) * C, pack8(fx));
     }
