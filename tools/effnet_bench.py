@@ -126,6 +126,32 @@ def train_step_ms(model, x, labels, steps, warmup, fused=False, graphed=False, w
     for _ in range(warmup):
         step()
     torch.cuda.synchronize()
+    e2e = None
+    if graphed and world == 1:
+        # end to end: every step's batch comes from pinned host memory (H2D on the copy stream, one
+        # batch ahead) and every step's loss travels back to the host, inside the timed region
+        from image_classification_b200.prefetch import AsyncScalarReader, DevicePrefetcher
+        hx = [torch.randn(x.shape).contiguous(memory_format=torch.channels_last).pin_memory()
+              for _ in range(2)]
+        hy = [torch.randint(0, 44, labels.shape).pin_memory() for _ in range(2)]
+        reader, losses = AsyncScalarReader(x.device), []
+        torch.cuda.synchronize()
+        s0, e0 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        nwarm = max(warmup, 3)       # the copy stream's staging blocks are allocated in these
+        feed = ((hx[i % 2], hy[i % 2]) for i in range(nwarm + steps))
+        for i, (xb, yb) in enumerate(DevicePrefetcher(feed, x.device)):
+            if i == nwarm:
+                s0.record()
+            l = gfb(xb, yb)
+            fo.step()
+            if i >= nwarm:
+                losses += reader.push(l)
+        losses += reader.drain()
+        e0.record()
+        torch.cuda.synchronize()
+        e2e = {"ms_per_step": round(s0.elapsed_time(e0) / steps, 3),
+               "h2d_bytes_per_step": hx[0].numel() * 4 + hy[0].numel() * 8, "d2h_bytes_per_step": 4,
+               "losses_read": len(losses)}
     if world > 1:
         torch.distributed.barrier()
         torch.cuda.synchronize()
@@ -138,7 +164,7 @@ def train_step_ms(model, x, labels, steps, warmup, fused=False, graphed=False, w
     ms = torch.tensor([s.elapsed_time(e) / steps], device=x.device)
     if world > 1:
         torch.distributed.all_reduce(ms, op=torch.distributed.ReduceOp.MAX)     # slowest rank
-    return float(ms), float(loss.detach())
+    return float(ms), float(loss.detach()), e2e
 
 
 def main():
@@ -194,7 +220,7 @@ def main():
         model = model.to(memory_format=torch.channels_last)
         train_step_ms(model, x, labels, 2, 2, fused=True)
         with profile(activities=[ProfilerActivity.CUDA]) as prof:
-            train_step_ms(model, x, labels, 3, 0, fused=True)
+            train_step_ms(model, x, labels, 3, 0, fused=True)      # (ms, loss, e2e) unused
         print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=45,
                                         max_name_column_width=70))
         return
@@ -206,13 +232,17 @@ def main():
             out["swapped"] = swap_efficientnet(model)
         model = model.to(memory_format=torch.channels_last)
         n0 = _lib.launch_count
-        ms, loss = train_step_ms(model, x, labels, args.steps, args.warmup,
+        ms, loss, e2e = train_step_ms(model, x, labels, args.steps, args.warmup,
                                  fused=arm == "b200_fused_optim", graphed=arm == "b200_graphed",
                                  world=world)
         out[arm] = {"ms_per_step": round(ms, 3),
                     "images_per_s": round(world * args.batch / ms * 1e3, 1),
                     "loss": round(loss, 4),
-                    "lib_launches_per_step": (_lib.launch_count - n0) // (args.steps + args.warmup)}
+                    "lib_launches_per_step": (_lib.launch_count - n0) // (
+                        args.steps * (2 if e2e is not None else 1) + args.warmup * (2 if e2e is not None else 1))}
+        if e2e is not None:
+            e2e["images_per_s"] = round(args.batch / e2e["ms_per_step"] * 1e3, 1)
+            out[arm]["e2e"] = e2e
         del model
         torch.cuda.empty_cache()
     if rank == 0:
