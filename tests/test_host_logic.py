@@ -371,3 +371,23 @@ def test_swap_efficientnet_timm_layout_on_cpu():
         assert torch.allclose(a.float(), b.float(), rtol=1e-5, atol=1e-7), n
     m.eval(), ref.eval()
     assert torch.allclose(m(x), ref(x), rtol=1e-5, atol=1e-6)
+
+
+def test_averaged_model_b200_interface_on_cpu():
+    """AveragedModelB200 mirrors torch.optim.swa_utils.AveragedModel (the reference's SWA object,
+    previous/V3-efb2/train_advanced_v3.0.py:445): same state_dict keys and forward; the update has
+    no CPU path and says so."""
+    import copy
+    from torch.optim.swa_utils import AveragedModel
+    from image_classification_b200 import _lib
+    from image_classification_b200.ema import AveragedModelB200
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.SiLU(), torch.nn.Linear(16, 4))
+    ours, ref = AveragedModelB200(model), AveragedModel(copy.deepcopy(model))
+    assert list(ours.state_dict()) == list(ref.state_dict())
+    assert int(ours.n_averaged) == 0
+    x = torch.randn(3, 8)
+    assert torch.equal(ours(x), ref(x))
+    assert all(a is not b for a, b in zip(ours.module.parameters(), model.parameters()))
+    with pytest.raises(_lib.CnxError):
+        ours.update_parameters(model)
