@@ -49,6 +49,7 @@ SIGNATURES = {
     "cnx_last_error_string": (c_char_p, []),
     "cnx_check_device": (I, []),
     "cnx_debug_timeout_flag": (I, []),
+    "cnx_debug_set_timeout_flag": (None, [I]),
     "cnx_debug_gemm_tuning": (None, [I, I, I, I]),
     "cnx_debug_max_clusters": (I, [I]),
     "cnx_workspace_bytes": (c_size_t, [I, I, I, I, I]),

@@ -16,6 +16,19 @@ from torch import nn
 from . import _lib, ops
 
 
+# Bumped by every writer that changes parameter VALUES behind autograd's back (the fused optimizer
+# step updates parameters from a ctypes-launched kernel through raw pointers, so `p._version` does
+# not move): part of the folded-weight cache key of every block.
+_weight_epoch = 0
+
+
+def notify_weights_changed() -> None:
+    """Invalidate the folded-weight caches of all ConvNeXtBlockB200 modules.  Call after writing
+    parameter storage with anything that is not a torch in-place op (raw-pointer kernels)."""
+    global _weight_epoch
+    _weight_epoch += 1
+
+
 class _Mlp(nn.Module):
     """Parameter container named like timm's `Mlp` (fc1 / act / fc2)."""
 
@@ -129,8 +142,13 @@ class ConvNeXtBlockB200(nn.Module):
 
     # -- folded bf16 weights, cached per weight version -------------------------------------
     def _folded(self, *params) -> ops.FoldedWeights:
-        key = tuple((p.data_ptr(), p._version) for p in params)
-        if self._fold is None or key != self._fold_key:
+        # key: storage + torch's version counter (in-place torch ops, optimizer.step of torch's own
+        # optimizers) + the global epoch raw-pointer writers bump (optim_step.FusedOptimStep).
+        # Inside a CUDA-graph capture the fold is always recorded, so a replay refolds the weights
+        # of that replay instead of baking a stale copy into the graph.
+        key = (_weight_epoch,) + tuple((p.data_ptr(), p._version) for p in params)
+        if (self._fold is None or key != self._fold_key
+                or torch.cuda.is_current_stream_capturing()):
             self._fold = ops.prep_block_weights(*[p.detach() for p in params])
             self._fold_key = key
         return self._fold
@@ -223,9 +241,13 @@ class GradWindow:
             b._window = _WindowSlot(self, acc)
 
     def begin(self):
-        """Start a window: zero all accumulators (one memset)."""
+        """Start a window: zero all accumulators (one memset).  A window that never reached its
+        boundary (an odd trailing micro-batch: the reference leaves those gradients in `.grad` and
+        they join the next optimizer step, /root/reference/train_advanced_v4.py:225-231) is
+        continued, not zeroed."""
         if self.flat is not None:
-            self.flat.zero_()
+            if not self.active:
+                self.flat.zero_()
             self.active = True
             self.boundary = False
 
@@ -233,12 +255,36 @@ class GradWindow:
         self.boundary = bool(boundary)
 
     def end(self):
+        """Close the window (called after the boundary micro-batch): later backward passes outside
+        a window take the plain per-call path instead of adding stale accumulators."""
         self.active = False
         self.boundary = True
 
+    @torch.no_grad()
+    def flush(self):
+        """Emit what an unfinished window holds into the parameters' `.grad` (adding to what is
+        there), exactly where the reference's plain accumulation would have left it, and close."""
+        if self.flat is None or not self.active:
+            return
+        for b in self.blocks:
+            a = b._window.acc
+            d_conv_w, d_norm_w, d_norm_b, d_fc1_w, d_fc2_w, d_fc2_b, d_gamma = ops.unfold_block_grads(
+                a["dw1f"], a["db1f"], a["dw2f"], a["db2f"], a["dwt"], b.norm.weight.detach(),
+                b.norm.bias.detach(), b.mlp.fc1.weight.detach(), b.mlp.fc2.weight.detach(),
+                b.mlp.fc2.bias.detach(), b.gamma.detach())
+            for prm, g in ((b.conv_dw.weight, d_conv_w), (b.conv_dw.bias, a["dbias"].clone()),
+                           (b.norm.weight, d_norm_w), (b.norm.bias, d_norm_b),
+                           (b.mlp.fc1.weight, d_fc1_w), (b.mlp.fc1.bias, a["db1f"].clone()),
+                           (b.mlp.fc2.weight, d_fc2_w), (b.mlp.fc2.bias, d_fc2_b),
+                           (b.gamma, d_gamma)):
+                if prm.requires_grad:
+                    prm.grad = g if prm.grad is None else prm.grad + g
+        self.end()
+
     def detach(self):
         for b in self.blocks:
-            b._window = None
+            if b._window is not None and b._window.owner is self:
+                b._window = None
         self.active = False
 
 

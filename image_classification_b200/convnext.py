@@ -5,7 +5,8 @@ num_classes=44)` returns (/root/reference/train_advanced_v4.py:488-492) is re-st
 same attribute layout the reference touches: `stem`, `stages[i].downsample`, `stages[i].blocks[j]`,
 `head.{global_pool,norm,flatten,drop,fc}` (:106-111, :131-143).  The 36 blocks, the stem, the
 stage downsamples and the head's pool + norm run on libcnx_b200 kernels; only
-the 44-way `head.fc` / auxiliary Linear layers on [B, C] stay `nn.Linear`.  The residual stream is
+the 44-way `head.fc` / auxiliary Linear layers on [B, C] stay `nn.Linear`.  A CUDA activation that
+misses a library path warns once (and raises under CNX_STRICT=1) — see `_off_path`.  The residual stream is
 kept channels_last so the NHWC kernels are zero-copy between blocks.  `DeepSupervisionModelB200`
 mirrors the wrapper the reference puts around the backbone (:96-152).
 """
@@ -15,8 +16,38 @@ import torch
 import torch.nn.functional as F
 from torch import nn
 
-from . import ops
+import os
+import warnings
+
+from . import _lib, ops
 from .block import ConvNeXtBlockB200
+
+_warned: set[str] = set()
+
+
+def _off_path(who: str, why: str, x: torch.Tensor) -> None:
+    """A CUDA activation that misses the libcnx_b200 path of a trunk module is never silent
+    ("unsupported shape/dtype => error, not a silent fallback"): under
+    CNX_STRICT=1 (bench.py and the GPU tests run that way) it raises; otherwise it warns once per
+    module kind, naming the failed condition, and the torch module it subclasses runs.  CPU
+    tensors (the oracle side of the tests) take the torch ops without comment."""
+    if not x.is_cuda:
+        return
+    msg = (f"{who}: CUDA input (dtype {x.dtype}, shape {tuple(x.shape)}) is not on the libcnx_b200 "
+           f"path: {why}")
+    if os.environ.get("CNX_STRICT") == "1":
+        raise _lib.CnxError(msg + " (CNX_STRICT=1)")
+    if who not in _warned:
+        _warned.add(who)
+        warnings.warn(msg + "; running the torch module it subclasses", stacklevel=3)
+
+
+def _first_failed(conds) -> str | None:
+    """conds: iterable of (ok, description); -> description of the first failed one or None."""
+    for ok, why in conds:
+        if not ok:
+            return why
+    return None
 
 CONVNEXT_CFGS = {
     "convnext_tiny": dict(depths=(3, 3, 9, 3), dims=(96, 192, 384, 768)),
@@ -55,10 +86,19 @@ class LayerNorm2d(nn.LayerNorm):
     oracle on CPU) takes the PyTorch op."""
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        C = x.shape[1]
-        if (x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 4 and C % 8 == 0 and C <= 1024
-                and x.permute(0, 2, 3, 1).is_contiguous() and self.weight.dtype == torch.float32):
+        why = _first_failed((
+            (x.is_cuda, "not a CUDA tensor"),
+            (x.dim() == 4, "input is not [B,C,H,W]"),
+            (x.dtype == torch.bfloat16, "activations are not bf16 (run the model under "
+                                        "torch.autocast('cuda', dtype=torch.bfloat16))"),
+            (x.dim() == 4 and x.shape[1] % 8 == 0 and x.shape[1] <= 1024,
+             "channel count must be a multiple of 8 and <= 1024"),
+            (x.dim() == 4 and x.permute(0, 2, 3, 1).is_contiguous(), "input is not channels_last"),
+            (self.weight.dtype == torch.float32, "parameters are not float32"),
+        ))
+        if why is None:
             return _LayerNorm2dFn.apply(x, self.weight, self.bias, self.eps)
+        _off_path("LayerNorm2d", why, x)
         y = x.permute(0, 2, 3, 1)
         y = F.layer_norm(y, self.normalized_shape, self.weight, self.bias, self.eps)
         # autocast runs layer_norm in fp32; hand the stream back in the dtype it came in so the
@@ -66,51 +106,11 @@ class LayerNorm2d(nn.LayerNorm):
         return y.to(x.dtype).permute(0, 3, 1, 2)
 
 
-class _PatchConvFn(torch.autograd.Function):
-    """conv2d(kernel = stride, no padding) + bias on bf16 channels_last activations.  Forward and
-    the input / weight gradients are cuDNN's; the bias gradient (sum of grad_output over batch and
-    space, which PyTorch computes with a slow strided reduction over NHWC: 73 us per layer measured)
-    is one cnx_colsum_bf16 launch."""
-
-    @staticmethod
-    def forward(ctx, x, weight, bias, stride):
-        wq = weight.to(torch.bfloat16)          # what autocast would hand to conv2d
-        ctx.save_for_backward(x, wq)
-        ctx.stride = stride
-        ctx.w_like = weight.detach()
-        return F.conv2d(x, wq, bias.to(torch.bfloat16), stride=stride)
-
-    @staticmethod
-    def backward(ctx, g):
-        x, wq = ctx.saved_tensors
-        s = ctx.stride
-        if not g.is_contiguous(memory_format=torch.channels_last):
-            g = g.contiguous(memory_format=torch.channels_last)
-        dx, dw, _ = torch.ops.aten.convolution_backward(
-            g, x, wq, None, [s, s], [0, 0], [1, 1], False, [0, 0], 1,
-            [ctx.needs_input_grad[0], True, False])
-        B, C, H, W = g.shape
-        db = ops.colsum_bf16(g.permute(0, 2, 3, 1).reshape(B * H * W, C))
-        dw32 = torch.empty_like(ctx.w_like, dtype=torch.float32)     # the parameter's own layout
-        dw32.copy_(dw)
-        return dx, dw32, db, None
-
-
 class PatchConv2d(nn.Conv2d):
-    """The stem (4x4 stride 4) and downsample (2x2 stride 2) convolutions of timm's ConvNeXt:
-    an `nn.Conv2d` (same parameters, same state_dict keys) whose bf16 channels_last CUDA path takes
-    its bias gradient from libcnx_b200; any other input goes through `nn.Conv2d.forward`."""
-
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
-        k = self.kernel_size[0]
-        if (x.is_cuda and x.dim() == 4 and self.bias is not None and self.groups == 1
-                and self.kernel_size == (k, k) and self.stride == (k, k) and self.padding == (0, 0)
-                and self.dilation == (1, 1) and self.out_channels % 8 == 0
-                and self.out_channels <= 2048 and torch.is_autocast_enabled()
-                and torch.get_autocast_dtype("cuda") == torch.bfloat16
-                and x.is_contiguous(memory_format=torch.channels_last)):
-            return _PatchConvFn.apply(x.to(torch.bfloat16), self.weight, self.bias, k)
-        return super().forward(x)
+    """The stem (4x4 stride 4) and downsample (2x2 stride 2) convolutions of timm's ConvNeXt: a
+    plain `nn.Conv2d` (same parameters, same state_dict keys) that marks the convolution the
+    containers below (`StemB200`, `DownsampleB200`) run as a patchify + tcgen05 GEMM.  Called on
+    its own it IS `nn.Conv2d` — there is no second library-backed implementation of this op."""
 
 
 def _w2d(weight: torch.Tensor) -> torch.Tensor:
@@ -184,17 +184,31 @@ class DownsampleB200(nn.Sequential):
 
     def forward(self, x):
         norm, conv = self[0], self[1]
-        B, C, H, W = x.shape
         k = conv.kernel_size[0]
-        if (x.is_cuda and x.dtype == torch.bfloat16 and _autocast_bf16() and C % 8 == 0 and C <= 1024
-                and conv.kernel_size == (k, k) and conv.stride == (k, k) and conv.padding == (0, 0)
-                and conv.groups == 1 and conv.bias is not None and H % k == 0 and W % k == 0
-                and conv.out_channels % 8 == 0 and x.permute(0, 2, 3, 1).is_contiguous()
-                and norm.weight.dtype == torch.float32):
+        why = _first_failed((
+            (x.is_cuda, "not a CUDA tensor"),
+            (x.dim() == 4, "input is not [B,C,H,W]"),
+            (x.dtype == torch.bfloat16, "activations are not bf16"),
+            (_autocast_bf16(), "torch.autocast('cuda', dtype=torch.bfloat16) is not active"),
+            (x.dim() == 4 and x.shape[1] % 8 == 0 and x.shape[1] <= 1024,
+             "channel count must be a multiple of 8 and <= 1024"),
+            (conv.kernel_size == (k, k) and conv.stride == (k, k) and conv.padding == (0, 0)
+             and conv.groups == 1 and conv.bias is not None,
+             "the convolution is not a k x k stride-k patchify convolution with bias"),
+            (x.dim() == 4 and x.shape[2] % k == 0 and x.shape[3] % k == 0,
+             "spatial size is not a multiple of the patch"),
+            (conv.out_channels % 8 == 0, "output channels must be a multiple of 8"),
+            (x.dim() == 4 and x.permute(0, 2, 3, 1).is_contiguous(), "input is not channels_last"),
+            (norm.weight.dtype == torch.float32, "parameters are not float32"),
+        ))
+        if why is None:
+            B, C, H, W = x.shape
             yp = _LayerNormPatchFn.apply(x, norm.weight, norm.bias, norm.eps, k)
             z = _PatchGemmFn.apply(yp, conv.weight, conv.bias)
             return z.view(B, H // k, W // k, conv.out_channels).permute(0, 3, 1, 2)
-        return super().forward(x)
+        _off_path("DownsampleB200", why, x)
+        return conv(F.layer_norm(x.permute(0, 2, 3, 1), norm.normalized_shape, norm.weight,
+                                 norm.bias, norm.eps).permute(0, 3, 1, 2))
 
 
 class StemB200(nn.Sequential):
@@ -205,17 +219,30 @@ class StemB200(nn.Sequential):
     def forward(self, x):
         conv, norm = self[0], self[1]
         k = conv.kernel_size[0]
-        if (x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and x.is_contiguous()
-                and _autocast_bf16() and not x.requires_grad
-                and conv.kernel_size == (k, k) and conv.stride == (k, k) and conv.padding == (0, 0)
-                and conv.groups == 1 and conv.bias is not None and x.shape[2] % k == 0
-                and x.shape[3] % k == 0 and (k * k * x.shape[1]) % 8 == 0
-                and conv.out_channels % 8 == 0):
+        why = _first_failed((
+            (x.is_cuda, "not a CUDA tensor"),
+            (x.dim() == 4, "input is not [B,C,H,W]"),
+            (x.dtype == torch.float32 and x.is_contiguous(),
+             "the image batch is not contiguous float32 NCHW"),
+            (_autocast_bf16(), "torch.autocast('cuda', dtype=torch.bfloat16) is not active"),
+            (not x.requires_grad, "the image batch requires a gradient"),
+            (conv.kernel_size == (k, k) and conv.stride == (k, k) and conv.padding == (0, 0)
+             and conv.groups == 1 and conv.bias is not None,
+             "the convolution is not a k x k stride-k patchify convolution with bias"),
+            (x.dim() == 4 and x.shape[2] % k == 0 and x.shape[3] % k == 0,
+             "spatial size is not a multiple of the patch"),
+            (x.dim() == 4 and (k * k * x.shape[1]) % 8 == 0 and conv.out_channels % 8 == 0,
+             "patch size / output channels must be multiples of 8"),
+        ))
+        if why is None:
             B, _, H, W = x.shape
             P = ops.patchify_nchw_f32(x, k)
             z = _PatchGemmFn.apply(P, conv.weight, conv.bias)
             return norm(z.view(B, H // k, W // k, conv.out_channels).permute(0, 3, 1, 2))
-        return super().forward(x)
+        _off_path("StemB200", why, x)
+        y = conv(x)
+        return F.layer_norm(y.permute(0, 2, 3, 1), norm.normalized_shape, norm.weight, norm.bias,
+                            norm.eps).permute(0, 3, 1, 2)
 
 
 class ConvNeXtStage(nn.Module):
@@ -260,10 +287,18 @@ class GlobalAvgPoolB200(nn.AdaptiveAvgPool2d):
         super().__init__(output_size)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        if (self.output_size in (1, (1, 1)) and x.is_cuda and x.dtype == torch.bfloat16
-                and x.dim() == 4 and x.shape[1] % 8 == 0 and x.shape[0] <= 65535
-                and x.permute(0, 2, 3, 1).is_contiguous()):
+        why = _first_failed((
+            (x.is_cuda, "not a CUDA tensor"),
+            (self.output_size in (1, (1, 1)), "output size is not 1"),
+            (x.dim() == 4, "input is not [B,C,H,W]"),
+            (x.dtype == torch.bfloat16, "activations are not bf16"),
+            (x.dim() == 4 and x.shape[1] % 8 == 0 and x.shape[0] <= 65535,
+             "channel count must be a multiple of 8 and the batch <= 65535"),
+            (x.dim() == 4 and x.permute(0, 2, 3, 1).is_contiguous(), "input is not channels_last"),
+        ))
+        if why is None:
             return _GlobalAvgPoolFn.apply(x)
+        _off_path("GlobalAvgPoolB200", why, x)
         return super().forward(x)
 
 

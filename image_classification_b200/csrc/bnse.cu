@@ -649,7 +649,7 @@ int status(const char* who) {
 int bn_stats(const void* x, float* sums, int64_t M, int C, cudaStream_t stream) {
   Geo g;
   if (!make_geo_flat("bn_stats", M, C, &g)) return CNX_ERR_BAD_SHAPE;
-  cudaMemsetAsync(sums, 0, sizeof(float) * 2 * C, stream);
+  if (int rc = zero_async(sums, sizeof(float) * 2 * C, stream, "bn_stats")) return rc;
   bn_stats_kernel<<<g.grid, kThreads, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), sums, C,
                                                    static_cast<int>(M), g.rows_per_cta, g.lw);
   return status("bn_stats");
@@ -672,7 +672,8 @@ int bn_act_fwd(const void* x, const float* sums, const float* weight, const floa
   const bool ok = pool_sum != nullptr ? make_geo("bn_act_fwd", B, HW, C, &g)
                                       : make_geo_flat("bn_act_fwd", M, C, &g);
   if (!ok) return CNX_ERR_BAD_SHAPE;
-  if (pool_sum != nullptr) cudaMemsetAsync(pool_sum, 0, sizeof(float) * B * C, stream);
+  if (pool_sum != nullptr)
+    if (int rc = zero_async(pool_sum, sizeof(float) * B * C, stream, "bn_act_fwd")) return rc;
   BnArgs p;
   p.sums = sums; p.pivot = static_cast<const __nv_bfloat16*>(x); p.weight = weight; p.bias = bias;
   p.running_mean = running_mean; p.running_var = running_var;
@@ -699,8 +700,8 @@ int bn_act_bwd(const void* g, const void* x, const float* weight, const float* b
   }
   Geo geo;
   if (!make_geo_flat("bn_act_bwd", M, C, &geo)) return CNX_ERR_BAD_SHAPE;
-  cudaMemsetAsync(dweight, 0, sizeof(float) * C, stream);
-  cudaMemsetAsync(dbias, 0, sizeof(float) * C, stream);
+  if (int rc = zero_async(dweight, sizeof(float) * C, stream, "bn_act_bwd")) return rc;
+  if (int rc = zero_async(dbias, sizeof(float) * C, stream, "bn_act_bwd")) return rc;
   BnBwdArgs p;
   p.weight = weight; p.bias = bias; p.mean = mean; p.rstd = rstd;
   p.dweight = dweight; p.dbias = dbias;
@@ -733,7 +734,7 @@ int se_scale_bwd_reduce(const void* g, const void* x, float* dgate, int B, int H
                         cudaStream_t stream) {
   Geo geo;
   if (!make_geo("se_scale_bwd_reduce", B, HW, C, &geo)) return CNX_ERR_BAD_SHAPE;
-  cudaMemsetAsync(dgate, 0, sizeof(float) * B * C, stream);
+  if (int rc = zero_async(dgate, sizeof(float) * B * C, stream, "se_scale_bwd_reduce")) return rc;
   se_bwd_reduce_kernel<<<geo.grid, kThreads, 0, stream>>>(
       static_cast<const __nv_bfloat16*>(g), static_cast<const __nv_bfloat16*>(x), dgate, C, HW,
       geo.rows_per_cta, geo.lw);

@@ -12,6 +12,8 @@ using namespace cnx;
   do {                                    \
     int rc__ = check_device_sm100();      \
     if (rc__ != CNX_OK) return rc__;      \
+    rc__ = check_sticky_timeout();        \
+    if (rc__ != CNX_OK) return rc__;      \
   } while (0)
 
 #define CNX_REQUIRE_PTR(p)                                         \
@@ -33,6 +35,7 @@ const char* cnx_last_error_string(void) { return last_error(); }
 int cnx_check_device(void) { return check_device_sm100(); }
 
 int cnx_debug_timeout_flag(void) { return read_and_clear_timeout_flag(); }
+void cnx_debug_set_timeout_flag(int value) { debug_set_timeout_flag(value); }
 int cnx_debug_max_clusters(int cluster_size) { return gemm_debug_max_clusters(cluster_size); }
 void cnx_debug_gemm_tuning(int stages, int pair, int bn, int splits) {
   gemm_debug_tuning(stages, pair, bn, splits);

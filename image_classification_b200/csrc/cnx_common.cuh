@@ -17,6 +17,11 @@ void set_last_error(const char* fmt, ...);
 const char* last_error();
 int* timeout_flag_ptr();             // device-visible mapped host int set by a timed-out wait
 int read_and_clear_timeout_flag();   // host side; call after synchronising the stream
+void debug_set_timeout_flag(int v);  // test hook
+int  check_sticky_timeout();         // CNX_ERR_LAUNCH once any earlier kernel timed out on an mbarrier
+// cudaMemsetAsync(p, 0, bytes) with the return code checked
+int  zero_async(void* p, size_t bytes, cudaStream_t stream, const char* who);
+int  current_device_slot();          // cudaGetDevice() clamped to [0, 64)
 int  check_device_sm100();           // CNX_OK or CNX_ERR_NOT_SM100 (cached per device)
 int  sm_count();
 bool pdl_enabled();                // false when CNX_NO_PDL is set (A/B switch)
@@ -29,6 +34,25 @@ int make_tensor_map(CUtensorMap* map, const void* base, int elem_bytes, int rank
                     const uint32_t* box, int swizzle);
 
 #ifdef __CUDACC__
+// cudaFuncAttributeMaxDynamicSharedMemorySize once per (kernel instantiation, device); safe to call
+// from the forward and the autograd thread at the same time and with several devices per process.
+template <typename K>
+inline int ensure_dyn_smem(K kernel, size_t bytes, const char* who) {
+  static unsigned long long done = 0ull;        // bit d = attribute set on device d
+  const int dev = current_device_slot();
+  if (__atomic_load_n(&done, __ATOMIC_ACQUIRE) & (1ull << dev)) return CNX_OK;
+  // setting the attribute twice (two racing threads) is harmless; losing the bit is not possible
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       static_cast<int>(bytes));
+  if (e != cudaSuccess) {
+    set_last_error("%s: cudaFuncSetAttribute(dynamic shared memory %zu B): %s", who, bytes,
+                   cudaGetErrorString(e));
+    return CNX_ERR_LAUNCH;
+  }
+  __atomic_fetch_or(&done, 1ull << dev, __ATOMIC_RELEASE);
+  return CNX_OK;
+}
+
 // Launch with an optional cluster width and, unless CNX_NO_PDL is set, programmatic stream
 // serialization (see pdl_wait() below): only for kernels that call pdl_wait() before their first
 // global-memory access.

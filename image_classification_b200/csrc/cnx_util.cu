@@ -69,6 +69,36 @@ int read_and_clear_timeout_flag() {
   return v;
 }
 
+void debug_set_timeout_flag(int v) {
+  if (timeout_flag_ptr() != nullptr) *reinterpret_cast<volatile int*>(g_flag_host) = v;
+}
+
+int check_sticky_timeout() {
+  // the flag page exists only once a TMA / tcgen05 kernel has been launched
+  if (g_flag_host != nullptr && *reinterpret_cast<volatile int*>(g_flag_host) != 0) {
+    set_last_error("an earlier libcnx_b200 kernel timed out waiting on an mbarrier: its results "
+                   "and those of every launch since are invalid (cnx_debug_timeout_flag() reads "
+                   "and clears the condition)");
+    return CNX_ERR_LAUNCH;
+  }
+  return CNX_OK;
+}
+
+int zero_async(void* p, size_t bytes, cudaStream_t stream, const char* who) {
+  cudaError_t e = cudaMemsetAsync(p, 0, bytes, stream);
+  if (e != cudaSuccess) {
+    set_last_error("%s: cudaMemsetAsync(%zu B): %s", who, bytes, cudaGetErrorString(e));
+    return CNX_ERR_LAUNCH;
+  }
+  return CNX_OK;
+}
+
+int current_device_slot() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0) dev = 0;
+  return dev & 63;
+}
+
 int check_device_sm100() {
   std::call_once(g_dev_once, query_device);
   if (g_cc_major != 10) {

@@ -401,17 +401,6 @@ int make_nhwc_map(CUtensorMap* map, const void* base, int B, int H, int W, int C
   return make_tensor_map(map, base, 2, 4, dims, strides, box, 0);
 }
 
-template <typename K>
-int set_smem_attr(K kernel, size_t bytes, const char* who) {
-  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       static_cast<int>(bytes));
-  if (e != cudaSuccess) {
-    set_last_error("%s: cudaFuncSetAttribute(%zu B): %s", who, bytes, cudaGetErrorString(e));
-    return CNX_ERR_LAUNCH;
-  }
-  return CNX_OK;
-}
-
 template <int TW>
 int launch_fwd(const void* x, ConvParams& p, int B, int H, int W, int C, cudaStream_t stream) {
   fill_geometry(p, B, H, W, C, TW);
@@ -419,12 +408,8 @@ int launch_fwd(const void* x, ConvParams& p, int B, int H, int W, int C, cudaStr
   int rc = make_nhwc_map(&map, x, B, H, W, C, TW + 6, kTH + 6);
   if (rc != CNX_OK) return rc;
   const size_t smem = 2ull * (kTH + 6) * (TW + 6) * kWords * 4 + 128;
-  static bool attr_set = false;
-  if (!attr_set) {
-    rc = set_smem_attr(dwconv7_fwd_kernel<TW>, smem, "dwconv7_fwd");
-    if (rc != CNX_OK) return rc;
-    attr_set = true;
-  }
+  rc = ensure_dyn_smem(dwconv7_fwd_kernel<TW>, smem, "dwconv7_fwd");
+  if (rc != CNX_OK) return rc;
   cudaError_t e = launch_pdl(dwconv7_fwd_kernel<TW>, grid_size(p), kThreads, smem, stream, 1u, map, p);
   if (e != cudaSuccess) {
     set_last_error("dwconv7_fwd launch: %s", cudaGetErrorString(e));
@@ -443,12 +428,8 @@ int launch_bwd(const void* dconv, const void* x, ConvParams& p, int B, int H, in
   rc = make_nhwc_map(&map_x, x, B, H, W, C, TW, kTH);
   if (rc != CNX_OK) return rc;
   const size_t smem = 2ull * ((kTH + 6) * (TW + 6) + kTH * TW) * kWords * 4 + 49 * kWords * 8 + 128;
-  static bool attr_set = false;
-  if (!attr_set) {
-    rc = set_smem_attr(dwconv7_bwd_kernel<TW>, smem, "dwconv7_bwd");
-    if (rc != CNX_OK) return rc;
-    attr_set = true;
-  }
+  rc = ensure_dyn_smem(dwconv7_bwd_kernel<TW>, smem, "dwconv7_bwd");
+  if (rc != CNX_OK) return rc;
   cudaError_t e = launch_pdl(dwconv7_bwd_kernel<TW>, grid_size(p), kThreads, smem, stream, 1u, map_d,
                              map_x, p);
   if (e != cudaSuccess) {
@@ -518,9 +499,9 @@ int dwconv_bwd(const void* dconv, const void* x, const void* dy, const float* wt
   p.dy = static_cast<const __nv_bfloat16*>(dy);
   p.dwt = dwt; p.dbias = dbias; p.dy_colsum = dy_colsum;
   if (!accumulate) {
-    cudaMemsetAsync(dwt, 0, sizeof(float) * 49 * C, stream);
-    cudaMemsetAsync(dbias, 0, sizeof(float) * C, stream);
-    cudaMemsetAsync(dy_colsum, 0, sizeof(float) * C, stream);
+    if ((rc = zero_async(dwt, sizeof(float) * 49 * C, stream, "dwconv_bwd")) != CNX_OK) return rc;
+    if ((rc = zero_async(dbias, sizeof(float) * C, stream, "dwconv_bwd")) != CNX_OK) return rc;
+    if ((rc = zero_async(dy_colsum, sizeof(float) * C, stream, "dwconv_bwd")) != CNX_OK) return rc;
   }
   return (W > 7) ? launch_bwd<14>(dconv, x, p, B, H, W, C, stream)
                  : launch_bwd<7>(dconv, x, p, B, H, W, C, stream);

@@ -408,7 +408,8 @@ int dwconv_kxk_bwd(const void* dy, const void* x, const float* wt, void* dx, flo
     if (int rc = status("dwconv_kxk_bwd (data)")) return rc;
   }
   if (dwt != nullptr) {
-    if (!accumulate) cudaMemsetAsync(dwt, 0, sizeof(float) * k * k * C, stream);
+    if (!accumulate)
+      if (int rc = zero_async(dwt, sizeof(float) * k * k * C, stream, "dwconv_kxk_bwd")) return rc;
     if (k == 3 && stride == 1) return launch_weight<3, 1, 4>(dyp, xp, dwt, g, stream);
     if (k == 3) return launch_weight<3, 2, 4>(dyp, xp, dwt, g, stream);
     if (stride == 1) return launch_weight<5, 1, 4>(dyp, xp, dwt, g, stream);

@@ -567,16 +567,8 @@ int launch2(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md0
   using L = Cfg<BN, PAIR, !(EPI == EPI_STORE_F32 || EPI == EPI_ATOMIC_F32)>;
   Gemm2Params p = p_in;
   p.stages = (g_tune.stages >= 2 && g_tune.stages < L::kStages) ? g_tune.stages : L::kStages;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm2_kernel<BN, EPI, PAIR>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
-    if (e != cudaSuccess) {
-      set_last_error("gemm_bf16: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-      return CNX_ERR_LAUNCH;
-    }
-    attr_set = true;
-  }
+  const int rc_attr = ensure_dyn_smem(gemm2_kernel<BN, EPI, PAIR>, L::kTotal, "gemm_bf16");
+  if (rc_attr != CNX_OK) return rc_attr;
   cudaError_t e = launch_pdl(gemm2_kernel<BN, EPI, PAIR>, grid, kThreads, L::kTotal, stream,
                              PAIR ? 2u : 1u, ma, mb, md0, md1, mr, p);
   if (e != cudaSuccess) {

@@ -518,8 +518,8 @@ int ln_affine_bwd(const void* g, const void* x, const float* w, const float* mea
   if (rc != CNX_OK) return rc;
   rc = check_patch("ln_affine_bwd", M, pH, pW, pk);
   if (rc != CNX_OK) return rc;
-  cudaMemsetAsync(dw, 0, sizeof(float) * C, stream);
-  cudaMemsetAsync(db, 0, sizeof(float) * C, stream);
+  if ((rc = zero_async(dw, sizeof(float) * C, stream, "ln_affine_bwd")) != CNX_OK) return rc;
+  if ((rc = zero_async(db, sizeof(float) * C, stream, "ln_affine_bwd")) != CNX_OK) return rc;
   // ~4 CTAs per SM, each walking a contiguous run of rows (multiple of the rows in flight)
   const int slots = kRowThreads / cfg.lpr;
   int64_t rpc = (M + 4 * sm_count() - 1) / (4 * sm_count());
@@ -546,7 +546,7 @@ int colsum_bf16(const void* x, float* out, int64_t M, int C, cudaStream_t stream
                    (long long)M, C);
     return CNX_ERR_BAD_SHAPE;
   }
-  cudaMemsetAsync(out, 0, sizeof(float) * C, stream);
+  if (int rc = zero_async(out, sizeof(float) * C, stream, "colsum_bf16")) return rc;
   const int rows_in_flight = kColsumThreads / (C >> 3);
   int64_t rpc = (M + 8 * sm_count() - 1) / (8 * sm_count());     // ~8 CTAs per SM
   rpc = (rpc + rows_in_flight - 1) / rows_in_flight * rows_in_flight;

@@ -7,9 +7,14 @@ gradients), each bucket's all-reduce is issued asynchronously the moment its las
 been accumulated — NCCL runs it on its own stream over NVLink 5 / NVSwitch while the remaining
 backward kernels keep the SMs busy — and `finish()` joins before unscale/clip/step.  On
 non-boundary accumulation micro-steps nothing is sent (the `no_sync` of the reference's
-accumulate-2 loop, /root/reference/train_advanced_v4.py:225).  Parameters that never receive a
-gradient (the reference's three discarded aux heads, :146-149/:219-220) are left out of the
-buckets by `discover_unused`.
+accumulate-2 loop, /root/reference/train_advanced_v4.py:225).
+
+Parameters that never receive a gradient (the reference's three discarded aux heads,
+:146-149/:219-220) are found on the FIRST synchronised backward: `finish()` reduces an incomplete
+bucket with zeros in the place of the missing gradients (every rank runs the same model, so every
+rank sees the same set) and then rebuilds the buckets without those parameters.  A parameter that
+was dropped this way and later does receive a gradient on a synchronised step raises — ranks must
+never diverge silently.
 """
 from __future__ import annotations
 
@@ -22,13 +27,19 @@ class BucketedGradReducer:
         self.pg = process_group
         self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
         self.params = [p for p in params if p.requires_grad]
+        if not self.params:
+            raise ValueError("BucketedGradReducer: no parameter requires a gradient")
+        self.bucket_bytes = bucket_bytes
         self.sync = True
+        self.discovered = False        # set once the unused-parameter set is known
+        self.dropped = []              # parameters found unused (no gradient on a sync backward)
+        self.reduced_steps = 0         # synchronised steps joined by finish() (bench asserts > 0)
         self._handles = []
         self._hooks = []
-        self._build(bucket_bytes)
+        self._build()
 
     # ---- construction -------------------------------------------------------------------
-    def _build(self, bucket_bytes: int):
+    def _build(self):
         for h in self._hooks:
             h.remove()
         self._hooks = []
@@ -38,13 +49,15 @@ class BucketedGradReducer:
         for p in reversed(self.params):
             cur.append(p)
             cur_bytes += p.numel() * p.element_size()
-            if cur_bytes >= bucket_bytes:
+            if cur_bytes >= self.bucket_bytes:
                 self._add_bucket(cur)
                 cur, cur_bytes = [], 0
         if cur:
             self._add_bucket(cur)
         for p in self.params:
             self._hooks.append(p.register_post_accumulate_grad_hook(self._on_grad))
+        for p in self.dropped:
+            self._hooks.append(p.register_post_accumulate_grad_hook(self._on_dropped_grad))
 
     def _add_bucket(self, plist):
         p0 = plist[0]
@@ -59,13 +72,25 @@ class BucketedGradReducer:
             self._where[p] = len(self.buckets)
         self.buckets.append(b)
 
-    def discover_unused(self, bucket_bytes: int = 32 << 20):
-        """Call after one backward: parameters whose .grad is still None are dropped from the
-        buckets (they would otherwise stall a bucket forever)."""
+    def discover_unused(self):
+        """Explicit form of what the first synchronised `finish()` does on its own: call right
+        after a backward that produced every gradient of an optimizer step (i.e. on the boundary
+        micro-batch, BEFORE `optimizer.zero_grad()`); parameters whose `.grad` is None are dropped
+        from the buckets.  Raises if that would drop every parameter (a call after zero_grad)."""
         used = [p for p in self.params if p.grad is not None]
-        if len(used) != len(self.params):
-            self.params = used
-            self._build(bucket_bytes)
+        if not used:
+            raise RuntimeError("BucketedGradReducer.discover_unused: no parameter holds a gradient "
+                               "— call it after backward of the boundary micro-batch and before "
+                               "optimizer.zero_grad()")
+        self._drop([p for p in self.params if p.grad is None])
+        self.discovered = True
+
+    def _drop(self, unused):
+        if unused:
+            gone = set(unused)
+            self.dropped += unused
+            self.params = [p for p in self.params if p not in gone]
+            self._build()
 
     # ---- per step -----------------------------------------------------------------------
     def set_sync(self, sync: bool):
@@ -83,8 +108,24 @@ class BucketedGradReducer:
         if b["pending"] == 0:
             self._launch(b)
 
+    def _on_dropped_grad(self, p):
+        if self.sync and self.world > 1:
+            raise RuntimeError("BucketedGradReducer: a parameter that had no gradient when the "
+                               "buckets were built received one on a synchronised step; it would "
+                               "not be all-reduced (rebuild the reducer)")
+
     def _launch(self, b):
         torch._foreach_copy_(b["views"], [p.grad for p in b["params"]])
+        h = dist.all_reduce(b["flat"], op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
+        self._handles.append((h, b))
+
+    def _launch_partial(self, b):
+        """A bucket some of whose parameters hold no gradient: zeros stand in for them, so the
+        collective keeps the same size on every rank."""
+        b["flat"].zero_()
+        have = [(v, p.grad) for v, p in zip(b["views"], b["params"]) if p.grad is not None]
+        if have:
+            torch._foreach_copy_([v for v, _ in have], [g for _, g in have])
         h = dist.all_reduce(b["flat"], op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
         self._handles.append((h, b))
 
@@ -92,13 +133,27 @@ class BucketedGradReducer:
         """Join all in-flight bucket reductions and write the averaged gradients back."""
         if self.world == 1 or not self.sync:
             return
-        for b in self.buckets:      # buckets whose hooks did not all fire (defensive)
-            if b["pending"] > 0 and all(p.grad is not None for p in b["params"]):
+        unused = []
+        for b in self.buckets:
+            if b["pending"] > 0:
+                missing = [p for p in b["params"] if p.grad is None]
+                if missing and self.discovered:
+                    raise RuntimeError(
+                        f"BucketedGradReducer.finish: {len(missing)} parameter(s) of a bucket have "
+                        "no gradient on a synchronised step although they had one when the buckets "
+                        "were built; the step would leave ranks out of sync")
+                unused += missing
                 b["pending"] = 0
-                self._launch(b)
+                self._launch_partial(b) if missing else self._launch(b)
         inv = 1.0 / self.world
         for h, b in self._handles:
             h.wait()
             b["flat"].mul_(inv)
-            torch._foreach_copy_([p.grad for p in b["params"]], b["views"])
+            have = [(p.grad, v) for v, p in zip(b["views"], b["params"]) if p.grad is not None]
+            torch._foreach_copy_([g for g, _ in have], [v for _, v in have])
         self._handles = []
+        self.reduced_steps += 1
+        if not self.discovered:
+            # first synchronised backward: the parameters without a gradient are the unused ones
+            self.discovered = True
+            self._drop(unused)

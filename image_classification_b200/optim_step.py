@@ -25,6 +25,7 @@ import numpy as np
 import torch
 
 from . import _lib
+from .block import notify_weights_changed
 
 
 def _same_layout(a: torch.Tensor, b: torch.Tensor) -> bool:
@@ -49,6 +50,7 @@ class _Table:
         host = np.concatenate([numel, prefix] +
                               [np.array([t.data_ptr() for t in col], dtype=np.int64) for col in columns])
         self._pinned = torch.from_numpy(host).pin_memory()        # kept alive with the table
+        self._refs = [list(col) for col in columns]               # the tensors the pointers name
         self.flat = self._pinned.to(dev, non_blocking=True)
         T = len(first)
         self.T, self.total = T, int(prefix[-1])
@@ -61,6 +63,7 @@ class _Table:
         """Re-point one column (gradients are re-allocated by autograd after zero_grad())."""
         host = torch.from_numpy(np.array([t.data_ptr() for t in tensors], dtype=np.int64)).pin_memory()
         self.cols[i].copy_(host, non_blocking=True)
+        self._refs[i] = list(tensors)
         self._staged = self._staged[-3:] + [host]      # keep the source alive until the copy ran
 
 
@@ -106,11 +109,12 @@ class FusedOptimStep:
         if self._state is None:
             self._state = torch.zeros(8, device=dev, dtype=torch.float32)
         self._ensure_state(groups, dev)
-        key = tuple(p.data_ptr() for _, ps in groups for p in ps)
+        key = self._pointer_key(groups)
         gkey = tuple(p.grad.data_ptr() for _, ps in groups for p in ps)
         if key != self._key:
             self._build(groups, dev)
-            self._key, self._gkey = key, gkey
+            # _build re-homes the step counters: take the key of what the tables now point at
+            self._key, self._gkey = self._pointer_key(groups), gkey
         all_t, group_ts, rest_t, partials, steps_flat = self._tables
         if gkey != self._gkey:                   # same parameters, gradients moved: pointers only
             all_t.update_col(0, [p.grad for _, ps in groups for p in ps])
@@ -145,6 +149,9 @@ class FusedOptimStep:
                       omd, d, stream)
         steps_flat.copy_(self._state[3].expand_as(steps_flat))     # torch keeps a count per tensor
         opt._opt_called = True          # what Optimizer.step() records for the LR scheduler's check
+        # the parameters were written through raw pointers: torch's version counters did not move,
+        # so the blocks' folded-weight caches are invalidated explicitly
+        notify_weights_changed()
         if scale_ptr:
             torch._amp_update_scale_(scale, growth_tracker, self._state[2:3],
                                      self.scaler.get_growth_factor(),
@@ -152,6 +159,18 @@ class FusedOptimStep:
                                      self.scaler.get_growth_interval())
 
     # ----------------------------------------------------------------------------- helpers
+    def _pointer_key(self, groups):
+        """Every pointer the tables hold: parameters, both moments, the step counters and the EMA
+        shadows (optimizer.load_state_dict(), ema.register() or a shadow loaded from a checkpoint
+        re-allocate them behind a live FusedOptimStep; the tables must follow)."""
+        st = self.optimizer.state
+        key = tuple((p.data_ptr(), st[p]["exp_avg"].data_ptr(), st[p]["exp_avg_sq"].data_ptr(),
+                     st[p]["step"].data_ptr() if torch.is_tensor(st[p]["step"]) else -1)
+                    for _, ps in groups for p in ps)
+        if self.ema is not None:
+            key += tuple(s.data_ptr() for s in self.ema.shadow.values())
+        return key
+
     def _ensure_state(self, groups, dev):
         opt = self.optimizer
         for _, ps in groups:

@@ -109,6 +109,8 @@ class TrainStep:
                     self.scheduler.step()                                      # :233-234
                 if self.ema is not None and self.fused is None:
                     self.ema.update()                                          # :236-237
+                if self.window is not None:
+                    self.window.end()
         else:
             outputs = self.model(images)
             if isinstance(outputs, (list, tuple)):
@@ -130,7 +132,18 @@ class TrainStep:
                     self.scheduler.step()
                 if self.ema is not None and self.fused is None:
                     self.ema.update()
+                if self.window is not None:
+                    self.window.end()
         return loss.detach()
+
+    def close(self) -> None:
+        """End of the loop: gradients of an odd trailing micro-batch still held by the
+        accumulation window go to `.grad` (where the reference leaves them, :225-231), the blocks
+        are released from the window."""
+        if self.window is not None:
+            self.window.flush()
+            self.window.detach()
+            self.window = None
 
 
 def train_one_epoch(model, train_loader, criterion, optimizer, scheduler, device, cfg,
@@ -150,4 +163,5 @@ def train_one_epoch(model, train_loader, criterion, optimizer, scheduler, device
         loss = step.micro_step(images, labels, batch_idx)
         loss_sum += loss.float() * images.size(0)                              # AverageMeter, :268
         count += images.size(0)
+    step.close()
     return (float(loss_sum.item()) / max(1, count)), 0.0

@@ -68,9 +68,14 @@ int cnx_version(void);
 const char* cnx_last_error_string(void);
 /* 0 if the current CUDA device is sm_100, CNX_ERR_NOT_SM100 otherwise. */
 int cnx_check_device(void);
-/* Debug: 1 if a kernel gave up waiting on an mbarrier since the last call (then that launch's
- * results are garbage), 0 otherwise; clears the flag.  Call after synchronising the stream. */
+/* 1 if a kernel gave up waiting on an mbarrier since the last call (then that launch's results
+ * are garbage), 0 otherwise; clears the condition.  Call after synchronising the stream.
+ * The condition is STICKY: from the moment a kernel has recorded a timeout, every cnx_* entry
+ * point that launches work returns CNX_ERR_LAUNCH (cnx_last_error_string() says why) until this
+ * call clears it, so a training loop cannot keep stepping on garbage. */
 int cnx_debug_timeout_flag(void);
+/* Test hook: set (1) or clear (0) the timeout condition by hand. */
+void cnx_debug_set_timeout_flag(int value);
 /* Debug / tuning: override the GEMM's tiling heuristics for the following calls (development tool
  * behind tools/gemm_sweep.py; -1 = automatic).  stages: operand-ring depth actually used (<= the
  * compiled depth); pair: 0/1 CTA-pair kernel; bn: 128/256 column tile; splits: split-K count of the

@@ -146,12 +146,78 @@ def gen_block_torchvision():
     np.savez_compressed(os.path.join(GOLDEN, "block_torchvision.npz"), **out)
 
 
+def loop_fixture_inputs(n_micro=6, batch=4, num_classes=10, seed=11):
+    """Seeded inputs of the loop fixture: [(images [b,3,8,8], soft labels [b,NC])] * n_micro."""
+    g = torch.Generator().manual_seed(seed)
+    out = []
+    for _ in range(n_micro):
+        x = torch.randn(batch, 3, 8, 8, generator=g)
+        t = torch.softmax(torch.randn(batch, num_classes, generator=g) * 2, dim=1)
+        out.append((x, t))
+    return out
+
+
+def gen_loop(tr_mod):
+    """The reference's OWN `train_one_epoch` (train_advanced_v4.py:193-281) with its `EMA`
+    (:62-94) and `get_cosine_schedule_with_warmup` (:183-191), 6 (and 5: odd tail) micro-batches of
+    soft labels on CPU over a tiny model that returns a list (hits :219-220 / :241-242), once with
+    scaler=None (plain branch, :238-258) and once with a disabled GradScaler (AMP branch, :215-237:
+    un-divided loss at :223).  Parameters after every micro-batch, final EMA shadows, the LR trace
+    and the returned mean loss are stored."""
+    import types
+    from .loop_oracle import TinyListModel
+    out = {}
+    cfg = types.SimpleNamespace(num_classes=10, gradient_accumulation_steps=2, gradient_clip_val=1.0)
+    torch.manual_seed(3)
+    init = TinyListModel().state_dict()
+    for k, v in init.items():
+        out[f"init_{k}"] = v.numpy().copy()
+    for case, (amp, n_micro) in {"plain": (False, 6), "amp": (True, 6), "plain_odd": (False, 5)}.items():
+        model = TinyListModel()
+        model.load_state_dict(init)
+        opt = torch.optim.AdamW(model.parameters(), lr=5e-3, weight_decay=1e-2)
+        sched = tr_mod.get_cosine_schedule_with_warmup(opt, 1, 3, min_lr=1e-6)
+        ema = tr_mod.EMA(model, 0.9)
+        crit = torch.nn.CrossEntropyLoss(label_smoothing=0.1)
+        scaler = torch.amp.GradScaler("cpu", enabled=False) if amp else None
+        batches = loop_fixture_inputs(n_micro)
+        snaps, lrs = [], []
+
+        def snap():
+            snaps.append({k: v.detach().numpy().copy() for k, v in model.named_parameters()})
+            lrs.append(opt.param_groups[0]["lr"])
+
+        def loader():
+            for i, b in enumerate(batches):
+                if i > 0:
+                    snap()              # state after micro-batch i-1
+                yield b
+
+        mean_loss, _ = tr_mod.train_one_epoch(model, loader(), crit, opt, sched, "cpu", cfg,
+                                              scaler=scaler, ema=ema)
+        snap()
+        assert len(snaps) == n_micro
+        for i, sn in enumerate(snaps):
+            for k, v in sn.items():
+                out[f"{case}_m{i}_{k}"] = v
+        out[f"{case}_lrs"] = np.array(lrs)
+        out[f"{case}_mean_loss"] = np.array(mean_loss)
+        out[f"{case}_n_micro"] = np.array(n_micro)
+        for k, v in ema.shadow.items():
+            out[f"{case}_shadow_{k}"] = v.numpy().copy()
+        for k, p in model.named_parameters():      # leftover gradients of the odd tail (:225-231)
+            if p.grad is not None:
+                out[f"{case}_grad_{k}"] = p.grad.numpy().copy()
+    np.savez_compressed(os.path.join(GOLDEN, "loop_reference.npz"), **out)
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
     ds_mod, tr_mod = load_reference()
     gen_mix(ds_mod)
     gen_ema(tr_mod)
     gen_schedule(tr_mod)
+    gen_loop(tr_mod)
     gen_softce()
     gen_block_torchvision()
     for f in sorted(os.listdir(GOLDEN)):

@@ -9,6 +9,10 @@ if ROOT not in sys.path:
 
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
+# the trunk modules raise instead of warning when a CUDA activation misses a library path
+# (convnext._off_path); CPU tensors — the oracle side of the tests — are unaffected
+os.environ.setdefault("CNX_STRICT", "1")
+
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a real B200 (run with -m gpu on the GPU box)")

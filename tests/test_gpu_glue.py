@@ -369,35 +369,67 @@ def test_fused_optim_step_rejects_unsupported(cnx_lib):
 
 
 # ----------------------------------------------------------------- stem / downsample conv
-@pytest.mark.parametrize("cfg", [(3, 128, 4, 32), (128, 256, 2, 28), (512, 1024, 2, 14)])
-def test_patch_conv_bias_grad_from_library(cnx_lib, cfg):
-    """PatchConv2d (cuDNN conv + cnx_colsum_bf16 bias gradient) vs nn.Conv2d under the same
-    autocast; column sums also against fp64."""
+def test_colsum_kernel_and_lone_patch_conv_is_plain_conv2d(cnx_lib):
+    """cnx_colsum_bf16 (bias gradient of the patchify GEMMs) vs fp64; a PatchConv2d called on its
+    own is nn.Conv2d (the second, cuDNN-backed implementation of round 1 is gone)."""
     from image_classification_b200 import ops
     from image_classification_b200.convnext import PatchConv2d
-    cin, cout, k, hw = cfg
     dev = _dev()
-    torch.manual_seed(cin + cout)
-    mine = PatchConv2d(cin, cout, kernel_size=k, stride=k).to(dev).to(memory_format=torch.channels_last)
-    ref = torch.nn.Conv2d(cin, cout, kernel_size=k, stride=k).to(dev).to(memory_format=torch.channels_last)
-    ref.load_state_dict(mine.state_dict())
-    x = torch.randn(4, cin, hw, hw, device=dev).contiguous(memory_format=torch.channels_last)
-    xm, xr = x.clone().requires_grad_(), x.clone().requires_grad_()
+    assert PatchConv2d.forward is torch.nn.Conv2d.forward
+    for M, C in ((1000, 96), (4 * 14 * 14, 1024), (7, 8)):
+        t = torch.randn(M, C, device=dev).bfloat16()
+        cs = ops.colsum_bf16(t)
+        assert float((cs.double() - t.double().sum(0)).abs().max()) < 1e-3
+
+
+def test_trunk_modules_off_path_is_loud(cnx_lib, monkeypatch):
+    """a CUDA activation that misses a library path of the ConvNeXt trunk raises
+    under CNX_STRICT=1 and warns once (naming the failed condition) otherwise — never silent."""
+    import warnings
+    from image_classification_b200 import _lib, convnext
+    from image_classification_b200.convnext import (DownsampleB200, GlobalAvgPoolB200, LayerNorm2d,
+                                                    PatchConv2d, StemB200)
+    dev = _dev()
+    stem = StemB200(PatchConv2d(3, 64, kernel_size=4, stride=4), LayerNorm2d(64, eps=1e-6)).to(dev)
+    down = DownsampleB200(LayerNorm2d(64, eps=1e-6), PatchConv2d(64, 128, kernel_size=2, stride=2)).to(dev)
+    ln, pool = LayerNorm2d(64, eps=1e-6).to(dev), GlobalAvgPoolB200(1)
+    img = torch.randn(2, 3, 32, 32, device=dev)
+    f32 = torch.randn(2, 64, 8, 8, device=dev).contiguous(memory_format=torch.channels_last)
+    bf = f32.bfloat16()
+    cases = [
+        ("StemB200", lambda: stem(img), "autocast"),                               # no autocast
+        ("DownsampleB200", lambda: down(bf), "autocast"),                          # no autocast
+        ("LayerNorm2d", lambda: ln(f32), "not bf16"),                              # fp32 stream
+        ("GlobalAvgPoolB200", lambda: pool(f32), "not bf16"),
+        ("LayerNorm2d", lambda: ln(bf.contiguous()), "channels_last"),             # NCHW-contiguous
+    ]
+    monkeypatch.setenv("CNX_STRICT", "1")
+    for who, fn, frag in cases:
+        with pytest.raises(_lib.CnxError) as ei:
+            fn()
+        assert who in str(ei.value) and frag in str(ei.value), str(ei.value)
+    with torch.autocast("cuda", dtype=torch.float16):                             # fp16 autocast
+        with pytest.raises(_lib.CnxError):
+            stem(img)
+        with pytest.raises(_lib.CnxError):
+            down(bf)
+    monkeypatch.setenv("CNX_STRICT", "0")
+    convnext._warned.clear()
+    for who, fn, frag in (cases[0], cases[2], cases[3]):   # (bf16 input + fp32 conv needs autocast)
+        with warnings.catch_warnings(record=True) as rec:
+            warnings.simplefilter("always")
+            y = fn()
+            fn()
+        msgs = [str(w.message) for w in rec if who in str(w.message)]
+        assert len(msgs) == 1 and frag in msgs[0], (who, msgs)     # once, with the reason
+        assert torch.isfinite(y.float()).all()
+    # the same modules on the path: no warning, library launches
+    monkeypatch.setenv("CNX_STRICT", "1")
+    n0 = _lib.launch_count
     with torch.autocast("cuda", dtype=torch.bfloat16):
-        ym, yr = mine(xm), ref(xr)
-    assert ym.dtype == torch.bfloat16 and torch.equal(ym, yr)
-    g = torch.randn_like(ym)
-    ym.backward(g)
-    yr.backward(g)
-    assert mine.weight.grad.stride() == mine.weight.stride()
-    assert torch.allclose(mine.weight.grad, ref.weight.grad, rtol=2e-2, atol=1e-3)
-    assert torch.allclose(xm.grad, xr.grad, rtol=2e-2, atol=1e-3)
-    exact = g.double().sum((0, 2, 3))
-    assert float((mine.bias.grad.double() - exact).abs().max() / exact.abs().max()) < 1e-5
-    # the kernel alone, ragged channel count
-    t = torch.randn(1000, 96, device=dev).bfloat16()
-    cs = ops.colsum_bf16(t)
-    assert float((cs.double() - t.double().sum(0)).abs().max()) < 1e-3
+        y = down(stem(img))
+        pool(ln(bf))
+    assert _lib.launch_count - n0 >= 6 and y.shape == (2, 128, 4, 4)
 
 
 # ------------------------------------------------------------------------- input pipeline

@@ -94,10 +94,26 @@ X = torch.randn(2, 2, 6, 16, generator=g)      # [micro, rank, b, d]
 Y = torch.randn(2, 2, 6, 8, generator=g)
 def micro(i, r, m):
     return ((m(X[i, r]) - Y[i, r]) ** 2).mean()
-# warm-up backward to discover the unused parameters
-red.set_sync(False); micro(0, rank, model).backward(); red.discover_unused(bucket_bytes=1024)
+# discover_unused after zero_grad (every .grad None) must refuse instead of dropping everything
+try:
+    red.discover_unused(); raise SystemExit("discover_unused accepted a model without gradients")
+except RuntimeError:
+    pass
+assert len(red.params) == 6 and not red.discovered
+# the first synchronised step finds the unused parameters by itself: the incomplete bucket is
+# reduced with zeros standing in, then the buckets are rebuilt without the two unused tensors
+red.set_sync(True); micro(0, rank, model).backward(); red.finish()
+assert red.discovered and len(red.params) == 4 and len(red.dropped) == 2 and len(red.buckets) >= 2
+assert red.reduced_steps == 1
+m0 = [torch.zeros_like(p) for p in model.parameters()]
+for r in range(world):
+    m2 = torch.nn.Sequential(torch.nn.Linear(16, 32), torch.nn.GELU(), torch.nn.Linear(32, 8))
+    m2.load_state_dict(model.state_dict())
+    micro(0, r, m2).backward()
+    for a, p in zip(m0, m2.parameters()): a += p.grad / world
+for a, p in zip(m0, model.parameters()):
+    assert torch.allclose(a, p.grad, atol=1e-6), ("discovery step", rank, (a - p.grad).abs().max())
 for p in params: p.grad = None
-assert len(red.params) == 4 and len(red.buckets) >= 2
 # accumulate 2 micro-batches; exchange on the boundary only
 red.set_sync(False); micro(0, rank, model).backward()
 g_before = [p.grad.clone() for p in model.parameters()]
@@ -119,6 +135,24 @@ for p, gl in zip(model.parameters(), local): p.grad = gl.clone()
 red.set_sync(True); red.finish()
 for p in model.parameters():
     assert torch.allclose(p.grad, torch.full_like(p, 1.5)), rank      # mean of 1 and 2
+# a known parameter without a gradient on a synchronised step: loud, not a silently skipped bucket
+for p in model.parameters(): p.grad = None
+red.set_sync(True)
+try:
+    list(model.parameters())[0].grad = None
+    for p in list(model.parameters())[1:]: p.grad = torch.ones_like(p)
+    red.finish(); raise SystemExit("finish() accepted an incomplete bucket after discovery")
+except RuntimeError:
+    pass
+# a dropped parameter that does receive a gradient on a synchronised step: loud as well
+red2 = BucketedGradReducer(params, bucket_bytes=1024)
+for p in params: p.grad = None
+red2.set_sync(True); micro(0, rank, model).backward(); red2.finish()
+try:
+    red2.set_sync(True); unused(torch.ones(1, 4)).sum().backward()
+    raise SystemExit("a dropped parameter's gradient went unnoticed")
+except RuntimeError:
+    pass
 dist.barrier(); dist.destroy_process_group()
 print("rank", rank, "ok")
 '''

@@ -150,3 +150,93 @@ def test_dwconv_ln_ref_consistent_with_block():
     ref = torch.nn.functional.layer_norm(y, (C,), None, None, 1e-6)
     assert torch.allclose(xhat, ref, atol=1e-10)
     assert math.isclose(float(mean[0]), float(y[0, 0, 0].mean()), rel_tol=1e-10)
+
+
+# ------------------------------------------------------------------ the step loop (row a6)
+LOOP_CASES = [("plain", False), ("amp", True), ("plain_odd", False)]
+
+
+def _loop_fixture(golden_dir):
+    from oracle.gen_golden import loop_fixture_inputs
+    from oracle.loop_oracle import TinyListModel
+    g = _load(golden_dir, "loop_reference.npz")
+    model = TinyListModel()
+    model.load_state_dict({k[len("init_"):]: torch.from_numpy(g[k]) for k in g.files
+                           if k.startswith("init_")})
+    return g, model, loop_fixture_inputs
+
+
+def _check_loop_case(g, case, model, ema_shadow, lrs, mean_loss, snaps, tol):
+    n = int(g[f"{case}_n_micro"])
+    assert len(snaps) == n and len(lrs) == n
+    for i, sn in enumerate(snaps):
+        for k, v in sn.items():
+            ref = g[f"{case}_m{i}_{k}"]
+            assert np.allclose(v, ref, rtol=tol, atol=tol), (case, i, k, np.abs(v - ref).max())
+    assert np.allclose(np.array(lrs), g[f"{case}_lrs"], rtol=1e-12, atol=0)
+    assert abs(mean_loss - float(g[f"{case}_mean_loss"])) < tol * 10
+    for k, s in ema_shadow.items():
+        ref = g[f"{case}_shadow_{k}"]
+        assert np.allclose(s, ref, rtol=tol, atol=tol), (case, "shadow", k)
+    # the odd tail leaves its gradients in .grad (train_advanced_v4.py:225-231 never ran)
+    for k, p in model.named_parameters():
+        key = f"{case}_grad_{k}"
+        if key in g.files:
+            assert p.grad is not None and np.allclose(p.grad.detach().cpu().numpy(), g[key],
+                                                      rtol=tol, atol=tol), (case, "grad", k)
+        else:
+            assert p.grad is None or float(p.grad.abs().sum()) == 0.0, (case, "grad", k)
+
+
+@pytest.mark.parametrize("case,amp", LOOP_CASES)
+def test_loop_oracle_reproduces_reference_train_one_epoch(golden_dir, case, amp):
+    """oracle/loop_oracle.reference_loop vs the reference's OWN train_one_epoch + EMA + schedule
+    (fixture: oracle/gen_golden.py::gen_loop): parameters after every micro-batch, EMA shadows,
+    LR trace, returned mean loss — both branches and the odd-tail case."""
+    from oracle import loop_oracle
+    g, model, inputs = _loop_fixture(golden_dir)
+    n = int(g[f"{case}_n_micro"])
+    opt = torch.optim.AdamW(model.parameters(), lr=5e-3, weight_decay=1e-2)
+    sched = torch.optim.lr_scheduler.LambdaLR(opt, loop_oracle.cosine_warmup_lambda(1, 3, 1e-6))
+    ema = loop_oracle.EMARef(model, 0.9)
+    snaps, lrs = [], []
+
+    def on_micro(i):
+        snaps.append({k: v.detach().numpy().copy() for k, v in model.named_parameters()})
+        lrs.append(opt.param_groups[0]["lr"])
+
+    mean_loss = loop_oracle.reference_loop(model, inputs(n), torch.nn.CrossEntropyLoss(label_smoothing=0.1),
+                                           opt, sched, ema, accum=2, clip=1.0, amp_branch=amp,
+                                           on_micro=on_micro)
+    _check_loop_case(g, case, model, {k: v.numpy() for k, v in ema.shadow.items()}, lrs, mean_loss,
+                     snaps, 1e-6)
+
+
+@pytest.mark.parametrize("case,amp", LOOP_CASES)
+def test_train_step_reproduces_reference_train_one_epoch_cpu(golden_dir, case, amp):
+    """The PRODUCT's `TrainStep.micro_step` (torch optimizer calls; the fused CUDA step is covered
+    by tests/test_gpu_loop.py) against the same fixture, on CPU tensors."""
+    import warnings
+    from image_classification_b200 import train_step
+    from oracle import loop_oracle
+    g, model, inputs = _loop_fixture(golden_dir)
+    n = int(g[f"{case}_n_micro"])
+    opt = torch.optim.AdamW(model.parameters(), lr=5e-3, weight_decay=1e-2)
+    sched = train_step.get_cosine_schedule_with_warmup(opt, 1, 3, 1e-6)
+    ema = loop_oracle.EMARef(model, 0.9)
+    scaler = torch.amp.GradScaler("cpu", enabled=False) if amp else None
+    step = train_step.TrainStep(model, torch.nn.CrossEntropyLoss(label_smoothing=0.1), opt, sched,
+                                scaler, ema, train_step.StepConfig(2, 1.0, 10),
+                                use_fused_optim=False)
+    snaps, lrs, s, cnt = [], [], 0.0, 0
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")            # autocast('cuda') on a CPU-only machine
+        for i, (x, t) in enumerate(inputs(n)):
+            loss = step.micro_step(x, t, i)
+            s += float(loss) * x.size(0)
+            cnt += x.size(0)
+            snaps.append({k: v.detach().numpy().copy() for k, v in model.named_parameters()})
+            lrs.append(opt.param_groups[0]["lr"])
+    step.close()
+    _check_loop_case(g, case, model, {k: v.numpy() for k, v in ema.shadow.items()}, lrs, s / cnt,
+                     snaps, 1e-6)
