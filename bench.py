@@ -10,7 +10,15 @@ unscale / clip 1.0 / AdamW / scheduler / EMA.  `value` = images all ranks proces
 ranks device time with the raw batch already in HBM; `e2e` = same loop fed from pinned host
 buffers through the public API (`prefetch.DevicePrefetcher`: H2D copy of every micro-batch on a
 second stream, one batch ahead; D2H read of every step's loss through pinned memory — all inside
-the timed region).  Weak scaling: per-GPU work is fixed, global batch = 256 * N.
+the timed region).  The headline is WEAK scaling on BASELINE config 2's per-GPU shape (global
+batch = 256 * N) so rounds stay comparable; after the headline region the same process times the
+other BASELINE configs (~10 steps each) and prints them under `configs`:
+  cfg3 = global batch 1024 split over N ranks, accumulation 2 (/root/reference/config.py:37): micro
+         256 / 128 / 64 at N = 2 / 4 / 8 — STRONG scaling; at N = 1 the 8-GPU rank's share (micro 64)
+         is timed so the driver's 1-GPU record carries that shape too;
+  cfg4 = 384x384, micro-batch 64 per GPU;
+  cfg5 = EfficientNet-B2 260x260 batch 48 per GPU through swap_efficientnet +
+         GraphedForwardBackward (/root/reference/previous/V3-efb2/config.py:10-15).
 
 `--impl reference` times the reference's CPU PyTorch path for the same metric (oracle port of the
 model, the reference loop order, bounded micro-batches) on the host cores of rank 0.
@@ -54,6 +62,8 @@ def parse_args():
     ap.add_argument("--micro-batch", type=int, default=MICRO_BATCH)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the cfg3 / cfg4 / cfg5 legs")
+    ap.add_argument("--config-steps", type=int, default=10)
     return ap.parse_args()
 
 
@@ -168,6 +178,33 @@ def run_cpu_reference(steps: int, warmup: int, micro_batch: int, res: int, model
     return ips, 1e3 * total / steps, cores, sample
 
 
+def run_cpu_config1(warmup: int = 2, timed: int = 5):
+    """BASELINE config 1 exactly: ConvNeXt-Tiny, 44 classes, 224x224, batch 8, fp32,
+    random init, one forward + backward with CrossEntropyLoss(label_smoothing=0.1) on soft [8,44]
+    targets (train_advanced_v4.py:626, config.py:31); 2 warm-up + 5 timed iterations, median."""
+    from oracle import loop_oracle
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.manual_seed(0)
+    model = loop_oracle.build_oracle_model("convnext_tiny", NUM_CLASSES).train()
+    crit = torch.nn.CrossEntropyLoss(label_smoothing=0.1)
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(8, 3, 224, 224, generator=g)
+    t = torch.softmax(torch.randn(8, NUM_CLASSES, generator=g) * 2, 1)
+    ts = []
+    for i in range(warmup + timed):
+        t0 = time.perf_counter()
+        model.zero_grad(set_to_none=True)
+        crit(model(x), t).backward()
+        if i >= warmup:
+            ts.append(time.perf_counter() - t0)
+    med = statistics.median(ts)
+    return {"value": round(8 / med, 3), "unit": UNIT, "cores": cores, "kind": "port",
+            "ms_per_iter": round(1e3 * med, 1),
+            "sample": f"BASELINE config 1: convnext_tiny fp32 CPU, batch 8 at 224x224, forward + "
+                      f"backward + CE(ls=0.1) on soft targets, {warmup} warm-up + {timed} timed, median"}
+
+
 def main_reference(args):
     rank, world, _ = dist_env()
     if rank != 0:
@@ -199,14 +236,18 @@ def main_reference(args):
 # ---------------------------------------------------------------------------------------------
 # B200 arm
 # ---------------------------------------------------------------------------------------------
-# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture
-# (profiles/r01_ncu_gemm2_v6_summary.txt): mean over the six GEMM launches of one stage-3 block
-# (C=512, M=25088: fc1 173.5, fc2 141.4, dz 195.6, dxhat 113.4, wgrad 139.8 + 137.0 MB), the shape
-# 27 of the 36 blocks run.  Algorithmic operand+result bytes of the same six launches: 171 MB mean (part of the results is
-# still dirty in the 126 MB L2 when a kernel ends, so DRAM traffic can sit below that).
-NCU_TRAFFIC = {"mlp_gemm": 150.1e6}
-NCU_TRAFFIC_NOTE = ("bytes per launch, mean of the 6 GEMMs of a stage-3 block, ncu --set full "
-                    "(profiles/r01_ncu_gemm2_v6_summary.txt); algorithmic bytes of the same launches 171e6")
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant GEMM family, from
+    the committed summary of an `ncu --set full` capture of the SHIPPED build
+    (profiles/r02_ncu_gemm_traffic.json, written by tools/ncu_traffic.py with the git hash of the
+    build it profiled).  None when no capture is committed."""
+    path = os.path.join(ROOT, "profiles", "r02_ncu_gemm_traffic.json")
+    if not os.path.exists(path):
+        return None, None
+    d = json.load(open(path))
+    return d.get("bytes_per_launch_mean"), (f"{d.get('what', '')} (profiles/r02_ncu_gemm_traffic.json, "
+                                            f"build {d.get('git', '?')}); algorithmic bytes of the same "
+                                            f"launches {d.get('algorithmic_bytes_mean')}")
 
 
 class B200Trainer:
@@ -235,6 +276,7 @@ class B200Trainer:
         self.criterion = loss.SoftTargetCrossEntropyB200(0.1)  # config.py:31
         self.mixer = mix.BatchMixUpCutMix(0.2, 1.0, 0.5, NUM_CLASSES)   # config.py:16-17, :593-599
         self.rng = np.random.RandomState(1234 + rank)
+        # the reducer finds the never-used auxiliary heads on its first synchronised backward
         self.reducer = ddp.BucketedGradReducer(self.params) if world > 1 else None
         cfg = train_step.StepConfig(gradient_accumulation_steps=ACCUM, gradient_clip_val=1.0,
                                     num_classes=NUM_CLASSES)
@@ -290,6 +332,19 @@ class B200Trainer:
     def h2d_bytes_per_step(self):
         return ACCUM * (self.host_images[0].numel() * 4 + self.host_labels[0].numel() * 8)
 
+    def replica_checksums(self):
+        """(sum of parameters, sum of |parameters|, sum of EMA shadows) in float64."""
+        with torch.no_grad():
+            ps = torch.stack([p.detach().double().sum() for p in self.params]).sum()
+            pa = torch.stack([p.detach().double().abs().sum() for p in self.params]).sum()
+            es = torch.stack([s.double().sum() for s in self.ema.shadow.values()]).sum()
+        return torch.stack([ps, pa, es])
+
+    def close(self):
+        self.step_obj.close()
+        for h in (self.reducer._hooks if self.reducer is not None else []):
+            h.remove()
+
 
 def timed_region(fn, steps, world, device):
     """barrier + sync, K steps between CUDA events on the current stream, max over ranks (ms)."""
@@ -312,10 +367,10 @@ def timed_region(fn, steps, world, device):
 
 # per entry point: (family, bound, work(args) in bytes or flops) — SURVEY.md §8(d) accounting
 def _work_table(nparams=0):
-    def dw_fwd(a):   # (x, wt, b, xhat, mean, rstd, B, H, W, C, eps, stream)
+    def dw_fwd(a):   # (x, wt, b, xhat, mean, rstd, B, H, W, C, eps, stream): 2*E*s
         return 2.0 * a[6] * a[7] * a[8] * a[9] * 2
-    def dw_bwd(a):   # (dxhat, xhat, rstd, x, dy, wt, dx, dwt, dbias, dycs, B, H, W, C, ...)
-        return 4.0 * a[10] * a[11] * a[12] * a[13] * 2     # dxhat, xhat, x in + dx out (dy not counted)
+    def dw_bwd(a):   # (dxhat, xhat, rstd, x, dy, wt, dx, dwt, dbias, dycs, B, H, W, C, ...): 3*E*s
+        return 3.0 * a[10] * a[11] * a[12] * a[13] * 2     # dy_LN, x in + dx out
     def mlp(a, mi, ci, mult=1.0):
         return mult * 8.0 * a[mi] * a[ci] * a[ci]           # 2 * M * 4C * C
     return {
@@ -335,7 +390,7 @@ def _work_table(nparams=0):
 
 def profile_kernels(trainer, device):
     """One extra optimizer step with a CUDA-event pair around every library call (after the
-    timed region, so the events do not perturb `value`).  -> {family: stats}, launches/step."""
+    timed region, so the events do not perturb `value`).  -> {family: stats}, instrumented ms."""
     from image_classification_b200 import _lib
     table = _work_table(sum(p.numel() for p in trainer.params))
     recs, open_ev = [], {}
@@ -374,60 +429,14 @@ def profile_kernels(trainer, device):
     return fam, step_ms
 
 
-def main_b200(args):
-    rank, world, local = dist_env()
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; the B200 arm has no CPU fallback "
-                         "(use --impl reference for the CPU baseline)")
-    device = torch.device("cuda", local)
-    torch.cuda.set_device(device)
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=device)
-    from image_classification_b200 import _lib
-    _lib.load()
-    _lib.check(_lib.load().cnx_check_device(), "cnx_check_device")
-
-    tr = B200Trainer(device, world, rank, args.micro_batch, args.res)
-    imgs_per_step = ACCUM * args.micro_batch * world
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    for _ in range(max(3, args.warmup)):
-        tr.step_resident()
-    if tr.reducer is not None:
-        tr.reducer.discover_unused()
-    torch.cuda.synchronize(device)
-
-    sampler.mark()
-    l0 = _lib.launch_count
-    ms = timed_region(tr.step_resident, args.steps, world, device)
-    launches = _lib.launch_count - l0
-    clocks = sampler.stop() if rank == 0 else None
-    value = imgs_per_step * args.steps / (ms * 1e-3)
-
-    e2e = None
-    if not args.no_e2e:
-        tr.run_e2e(2)
-        e2e_losses = []
-        ms_e2e = timed_region(lambda: e2e_losses.extend(tr.run_e2e(args.steps)), 1, world, device)
-        assert len(e2e_losses) == args.steps and all(l == l for l in e2e_losses), e2e_losses
-        e2e = {"value": round(imgs_per_step * args.steps / (ms_e2e * 1e-3), 2), "unit": UNIT,
-               "h2d_bytes_per_step": tr.h2d_bytes_per_step, "d2h_bytes_per_step": 4,
-               "ms_per_step": round(ms_e2e / args.steps, 3)}
-
-    fam, prof_step_ms = profile_kernels(tr, device)
-    timeout_flag = _lib.load().cnx_debug_timeout_flag()
-    if rank != 0:
-        if world > 1:
-            torch.distributed.destroy_process_group()
-        return 0
-
-    pk = peaks()
+def kernel_table(fam, timed_step_ms, clocks, pk, keep=None):
+    """{family: launches, ms, share of the TIMED step, roofline fraction}."""
     kernels = {}
     for name, d in fam.items():
+        if keep is not None and name not in keep:
+            continue
         k = {"launches_per_step": d["launches"], "ms_per_step": round(d["ms"], 4),
-             "share_of_step": round(d["ms"] / prof_step_ms, 4)}
+             "share_of_step": round(d["ms"] / timed_step_ms, 4)}
         if d["work"] > 0:
             if d["bound"] == "hbm":
                 k.update(bound="hbm", achieved=round(d["work"] / d["ms"] * 1e-6, 1), unit="GB/s",
@@ -437,22 +446,186 @@ def main_b200(args):
                          unit="TFLOP/s", peak=pk["bf16_tflops_sustained"])
             k["frac"] = round(k["achieved"] / k["peak"], 4)
         if name in ("dwconv_ln_fwd", "dwconv_ln_bwd") and d["work"] > 0:
-            # these kernels are bound by the FP32 FMA pipe, not HBM: 49 FMAs per
-            # element forward (work = 2*E*2 B), 98 backward (work = 4*E*2 B); peak = 128 FMA/clk/SM
-            elems = d["work"] / (4.0 if name == "dwconv_ln_fwd" else 8.0)
+            # the 7x7 depthwise conv is bound by the FP32 FMA pipe before HBM:
+            # 49 FMAs per element forward (work = 2*E*2 B), 98 backward (work = 3*E*2 B)
+            elems = d["work"] / (4.0 if name == "dwconv_ln_fwd" else 6.0)
             fmas = elems * (49.0 if name == "dwconv_ln_fwd" else 98.0)
             sm_hz = ((clocks or {}).get("sm_mhz") or 1965.0) * 1e6
             peak = 128.0 * SM_COUNT * sm_hz
             k["fma_pipe"] = {"achieved_tfma": round(fmas / d["ms"] * 1e-9, 2),
                              "peak_tfma": round(peak * 1e-12, 2),
-                             "frac": round(fmas / (d["ms"] * 1e-3) / peak, 4),
-                             "note": "includes the LayerNorm row kernel's time; tensor cores measured "
-                                     "2.4x slower for this op (profiles/r01_ubench_diag_mma.txt)"}
+                             "frac": round(fmas / (d["ms"] * 1e-3) / peak, 4)}
+            if name == "dwconv_ln_bwd":
+                # what the implementation actually streams: dxhat, xhat (LayerNorm backward
+                # recomputes from the saved normalised tensor), x in + dx out = 4*E*s
+                k["declared_4Es_GBps"] = round(d["work"] * 4.0 / 3.0 / d["ms"] * 1e-6, 1)
         kernels[name] = k
+    return kernels
+
+
+def run_convnext_config(tag, device, world, rank, local, micro_batch, res, steps, warmup, pk,
+                        headline=False, want_e2e=False, sampler=None):
+    """Build a trainer for (micro_batch, res), warm up, time `steps` optimizer steps; -> dict."""
+    from image_classification_b200 import _lib
+    tr = B200Trainer(device, world, rank, micro_batch, res)
+    imgs_per_step = ACCUM * micro_batch * world
+    for _ in range(max(3, warmup)):
+        tr.step_resident()
+    torch.cuda.synchronize(device)
+    if tr.reducer is not None:
+        # the all-reduce must be live: buckets exist, the unused aux heads were found, steps joined
+        assert tr.reducer.buckets and tr.reducer.discovered and tr.reducer.reduced_steps >= 3, \
+            "gradient all-reduce did not run during warm-up"
+        assert len(tr.reducer.dropped) == (0 if os.environ.get("CNX_NO_AUX") else 6), \
+            len(tr.reducer.dropped)
+    if sampler is not None:
+        sampler.mark()
+    l0 = _lib.launch_count
+    ms = timed_region(tr.step_resident, steps, world, device)
+    launches = _lib.launch_count - l0
+    clocks = sampler.stop() if (sampler is not None and rank == 0) else None
+    out = {"images_per_s": round(imgs_per_step * steps / (ms * 1e-3), 2),
+           "ms_per_step": round(ms / steps, 3), "steps": steps, "global_batch": imgs_per_step,
+           "micro_batch_per_gpu": micro_batch, "res": res, "gpu_launches": launches}
+    if want_e2e:
+        tr.run_e2e(2)
+        e2e_losses = []
+        ms_e2e = timed_region(lambda: e2e_losses.extend(tr.run_e2e(steps)), 1, world, device)
+        assert len(e2e_losses) == steps and all(l == l for l in e2e_losses), e2e_losses
+        out["e2e"] = {"value": round(imgs_per_step * steps / (ms_e2e * 1e-3), 2), "unit": UNIT,
+                      "h2d_bytes_per_step": tr.h2d_bytes_per_step, "d2h_bytes_per_step": 4,
+                      "ms_per_step": round(ms_e2e / steps, 3)}
+    if world > 1:
+        import torch.distributed as dist
+        mine = tr.replica_checksums()
+        every = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(every, mine)
+        out["replicas_identical"] = all(torch.equal(every[0], c) for c in every)
+        out["allreduce_steps_joined"] = tr.reducer.reduced_steps
+        out["allreduce_buckets"] = len(tr.reducer.buckets)
+    fam, prof_ms = profile_kernels(tr, device)
+    keep = None if headline else ("dwconv_ln_fwd", "dwconv_ln_bwd", "mlp_gemm")
+    out["kernels"] = kernel_table(fam, ms / steps, clocks, pk, keep)
+    out["profiled_step_ms"] = round(prof_ms, 3)
+    out["clocks"] = clocks
+    out["timeout_flag"] = _lib.load().cnx_debug_timeout_flag()
+    tr.close()
+    del tr
+    import gc
+    gc.collect()
+    torch.cuda.empty_cache()
+    return out
+
+
+def run_effnet_config(device, world, rank, steps, warmup, batch=48, res=260):
+    """BASELINE config 5: EfficientNet-B2 (torchvision's, timm's architecture; timm is absent),
+    260x260, batch 48 per GPU (/root/reference/previous/V3-efb2/config.py:10-15), the V3 loop's
+    step (train_advanced_v3.0.py:96-113: bf16 autocast forward, hard-label CE, scaled backward,
+    unscale, clip 1.0, AdamW, scaler update) through swap_efficientnet + GraphedForwardBackward +
+    FusedOptimStep; data-parallel ranks all-reduce inside the captured graph."""
+    import torchvision
+    from image_classification_b200 import _lib
+    from image_classification_b200.efficientnet import swap_efficientnet
+    from image_classification_b200.graphed import GraphedForwardBackward
+    from image_classification_b200.loss import SoftTargetCrossEntropyB200
+    from image_classification_b200.optim_step import FusedOptimStep
+    torch.manual_seed(0)
+    model = torchvision.models.efficientnet_b2(weights=None, num_classes=NUM_CLASSES).to(device).train()
+    for m in model.modules():                  # timm's create_model default: no drop-path
+        if isinstance(m, torchvision.ops.StochasticDepth):
+            m.p = 0.0
+    swapped = swap_efficientnet(model)
+    model = model.to(memory_format=torch.channels_last)
+    g = torch.Generator().manual_seed(7 + rank)
+    x = torch.randn(batch, 3, res, res, generator=g).to(device).contiguous(
+        memory_format=torch.channels_last)
+    labels = torch.randint(0, NUM_CLASSES, (batch,), generator=g).to(device)
+    opt = torch.optim.AdamW(model.parameters(), lr=2e-4, weight_decay=1e-2)     # V3 config.py:17-18
+    scaler = torch.amp.GradScaler("cuda")
+    reducer = None
+    if world > 1:
+        from image_classification_b200.ddp import BucketedGradReducer
+        reducer = BucketedGradReducer(list(model.parameters()), bucket_bytes=8 << 20)
+    gfb = GraphedForwardBackward(model, SoftTargetCrossEntropyB200(0.0), scaler, x, labels,
+                                 grad_reducer=reducer)
+    fo = FusedOptimStep(model, opt, scaler, None, 1.0)
+
+    def step():
+        gfb(x, labels)
+        fo.step()
+
+    for _ in range(max(3, warmup)):
+        step()
+    l0 = _lib.launch_count
+    ms = timed_region(step, steps, world, device)
+    out = {"images_per_s": round(world * batch * steps / (ms * 1e-3), 2),
+           "ms_per_step": round(ms / steps, 3), "steps": steps, "global_batch": world * batch,
+           "batch_per_gpu": batch, "res": res, "modules_swapped": swapped,
+           "model": "efficientnet_b2 (torchvision build of timm's architecture), 44 classes",
+           "step": "one CUDA-graph replay (fwd + CE + scaled bwd" +
+                   (" + bucketed NCCL all-reduce" if world > 1 else "") + ") + 2 optimizer launches",
+           "gpu_launches_outside_graph": _lib.launch_count - l0,
+           "loss": round(float(gfb.loss), 4)}
+    if reducer is not None:
+        for h in reducer._hooks:
+            h.remove()
+    return out
+
+
+def main_b200(args):
+    rank, world, local = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 arm has no CPU fallback "
+                         "(use --impl reference for the CPU baseline)")
+    os.environ["CNX_STRICT"] = "1"       # a trunk module off the library path raises, never falls back
+    device = torch.device("cuda", local)
+    torch.cuda.set_device(device)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
+    from image_classification_b200 import _lib
+    _lib.load()
+    _lib.check(_lib.load().cnx_check_device(), "cnx_check_device")
+    pk = peaks()
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    head = run_convnext_config("cfg2", device, world, rank, local, args.micro_batch, args.res,
+                               args.steps, args.warmup, pk, headline=True,
+                               want_e2e=not args.no_e2e, sampler=sampler)
+
+    configs = {}
+    if not args.no_configs and args.res == RES and args.micro_batch == MICRO_BATCH:
+        ks = max(3, args.config_steps)
+        micro3 = 1024 // (world * ACCUM) if world > 1 else 64
+        c3 = run_convnext_config("cfg3", device, world, rank, local, micro3, 224, ks, 3, pk)
+        c3["workload"] = (f"BASELINE config 3: global batch 1024 over {world} GPUs, micro-batch {micro3} "
+                          f"x accumulation {ACCUM} (strong scaling)" if world > 1 else
+                          "BASELINE config 3, the share of ONE of 8 ranks: micro-batch 64 x "
+                          "accumulation 2 on 1 GPU (global batch 1024 needs N >= 2)")
+        c3["scaling"] = "strong" if world > 1 else "n/a (one rank's share of the 8-GPU split)"
+        configs["cfg3"] = c3
+        c4 = run_convnext_config("cfg4", device, world, rank, local, 64, 384, ks, 3, pk)
+        c4["workload"] = "BASELINE config 4: ConvNeXt-Base 384x384, micro-batch 64 x accumulation 2 per GPU"
+        c4["scaling"] = "weak"
+        configs["cfg4"] = c4
+        c5 = run_effnet_config(device, world, rank, ks, 3)
+        c5["workload"] = "BASELINE config 5: EfficientNet-B2 260x260, batch 48 per GPU"
+        c5["scaling"] = "weak"
+        configs["cfg5"] = c5
+
+    if rank != 0:
+        if world > 1:
+            torch.distributed.destroy_process_group()
+        return 0
+
+    kernels = head["kernels"]
     dom = max((n for n in kernels if "frac" in kernels[n]), key=lambda n: kernels[n]["ms_per_step"])
+    traffic, traffic_note = ncu_traffic() if dom == "mlp_gemm" else (None, None)
     roof = {"kernel": dom, "bound": kernels[dom]["bound"], "achieved": kernels[dom]["achieved"],
             "peak": kernels[dom]["peak"], "unit": kernels[dom]["unit"], "frac": kernels[dom]["frac"],
-            "traffic": NCU_TRAFFIC.get(dom), "traffic_note": NCU_TRAFFIC_NOTE if dom in NCU_TRAFFIC else None,
+            "traffic": traffic, "traffic_note": traffic_note,
             "peak_source": pk["source"] +
             (" sustained bf16" if kernels[dom]["bound"] == "tensor" else " copy bandwidth"),
             "how": "sum of algorithmic work over this family's launches in one optimizer step / "
@@ -460,30 +633,36 @@ def main_b200(args):
 
     cpu = None
     if not args.no_cpu_baseline and world == 1:
-        ips, cms, cores, sample = run_cpu_reference(2, 1, 8, args.res, "convnext_base")
+        ips, cms, cores, sample = run_cpu_reference(5, 1, 8, args.res, "convnext_base")
         cpu = {"value": round(ips, 3), "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": sample, "ms_per_step": round(cms, 1)}
+               "sample": sample, "ms_per_step": round(cms, 1), "config1": run_cpu_config1()}
 
     line = {
-        "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world,
-        "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": round(ms / args.steps, 3),
+        "metric": METRIC, "value": head["images_per_s"], "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": head["ms_per_step"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
         "data": "synthetic",
         "config": {"workload": f"ConvNeXt-Base 44-class {args.res}x{args.res} bf16 AMP training "
                                f"step, micro-batch {args.micro_batch} x accumulation {ACCUM} per "
-                               "GPU " + ("(BASELINE config 2; config 3 layout for N>1)"
+                               "GPU " + ("(BASELINE config 2's per-GPU shape on every rank: weak "
+                                         "scaling; config 3's strong-scaling split is under `configs`)"
                                          if args.res == 224 else "(BASELINE config 4 shape)"
                                          if args.res == 384 else "(non-BASELINE shape)"),
-                   "global_batch": imgs_per_step, "micro_batch_per_gpu": args.micro_batch,
+                   "global_batch": head["global_batch"], "micro_batch_per_gpu": args.micro_batch,
                    "accumulation": ACCUM, "parallelism": f"dp{world}",
                    "step": "mixup/cutmix + fwd + soft-CE + bwd (x2) + unscale + clip 1.0 + "
                            "AdamW + scheduler + EMA",
                    "l2": "per-step working set (activations + 350 MB fp32 weights, >10 GB) "
                          "exceeds the 126 MB L2; no explicit flush"},
-        "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+        "e2e": head.get("e2e"), "gpu_launches": head["gpu_launches"], "clocks": head["clocks"],
         "roofline": roof, "kernels": kernels, "cpu_baseline": cpu,
-        "profiled_step_ms": round(prof_step_ms, 3), "timeout_flag": timeout_flag,
+        "profiled_step_ms": head["profiled_step_ms"], "timeout_flag": head["timeout_flag"],
+        "configs": configs,
     }
+    if world > 1:
+        line["replicas_identical"] = head["replicas_identical"]
+        line["allreduce"] = {"steps_joined": head["allreduce_steps_joined"],
+                             "buckets": head["allreduce_buckets"], "payload_mb": 350.4}
     print(json.dumps(line), flush=True)
     if world > 1:
         torch.distributed.destroy_process_group()

@@ -34,23 +34,12 @@ int make_tensor_map(CUtensorMap* map, const void* base, int elem_bytes, int rank
                     const uint32_t* box, int swizzle);
 
 #ifdef __CUDACC__
-// cudaFuncAttributeMaxDynamicSharedMemorySize once per (kernel instantiation, device); safe to call
-// from the forward and the autograd thread at the same time and with several devices per process.
+// cudaFuncAttributeMaxDynamicSharedMemorySize once per (kernel, device); safe to call from the
+// forward and the autograd thread at the same time and with several devices per process.
+int ensure_dyn_smem_impl(const void* kernel, size_t bytes, const char* who);
 template <typename K>
 inline int ensure_dyn_smem(K kernel, size_t bytes, const char* who) {
-  static unsigned long long done = 0ull;        // bit d = attribute set on device d
-  const int dev = current_device_slot();
-  if (__atomic_load_n(&done, __ATOMIC_ACQUIRE) & (1ull << dev)) return CNX_OK;
-  // setting the attribute twice (two racing threads) is harmless; losing the bit is not possible
-  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       static_cast<int>(bytes));
-  if (e != cudaSuccess) {
-    set_last_error("%s: cudaFuncSetAttribute(dynamic shared memory %zu B): %s", who, bytes,
-                   cudaGetErrorString(e));
-    return CNX_ERR_LAUNCH;
-  }
-  __atomic_fetch_or(&done, 1ull << dev, __ATOMIC_RELEASE);
-  return CNX_OK;
+  return ensure_dyn_smem_impl(reinterpret_cast<const void*>(kernel), bytes, who);
 }
 
 // Launch with an optional cluster width and, unless CNX_NO_PDL is set, programmatic stream

@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstring>
 #include <mutex>
+#include <unordered_map>
 #include <stdlib.h>
 
 namespace cnx {
@@ -90,6 +91,24 @@ int zero_async(void* p, size_t bytes, cudaStream_t stream, const char* who) {
     set_last_error("%s: cudaMemsetAsync(%zu B): %s", who, bytes, cudaGetErrorString(e));
     return CNX_ERR_LAUNCH;
   }
+  return CNX_OK;
+}
+
+int ensure_dyn_smem_impl(const void* kernel, size_t bytes, const char* who) {
+  static std::mutex mu;
+  static std::unordered_map<const void*, unsigned long long> done;   // kernel -> device bit mask
+  const int dev = current_device_slot();
+  std::lock_guard<std::mutex> lock(mu);
+  unsigned long long& mask = done[kernel];
+  if (mask & (1ull << dev)) return CNX_OK;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       static_cast<int>(bytes));
+  if (e != cudaSuccess) {
+    set_last_error("%s: cudaFuncSetAttribute(dynamic shared memory %zu B): %s", who, bytes,
+                   cudaGetErrorString(e));
+    return CNX_ERR_LAUNCH;
+  }
+  mask |= 1ull << dev;
   return CNX_OK;
 }
 

@@ -58,7 +58,7 @@ def test_model_logits_loss_and_grads_vs_oracle(cnx_lib, gamma_mode):
     loss_o.backward()
     # product: bf16 autocast like the training loop
     with torch.autocast("cuda", dtype=torch.bfloat16):
-        lp = prod(x.contiguous(memory_format=torch.channels_last))
+        lp = prod(x)          # contiguous fp32 NCHW, what the loop feeds (:211-218)
         loss_p = SoftTargetCrossEntropyB200(0.1)(lp, t)
     loss_p.backward()
     assert _rel(lp.float(), lo) < BF16_REL, _rel(lp.float(), lo)
@@ -68,7 +68,11 @@ def test_model_logits_loss_and_grads_vs_oracle(cnx_lib, gamma_mode):
     assert abs(gn_p - gn_o) < BF16_REL * gn_o
     worst = max(((_rel(p.grad, q.grad), n) for (n, p), (_, q) in
                  zip(prod.named_parameters(), ref.named_parameters())), key=lambda v: v[0])
-    # per-tensor max error grows with depth in bf16; the block-level tests hold 2e-2 per kernel
+    # per-tensor max error grows with depth: every block rounds its dx to bf16 once (the reference
+    # keeps the gradient of its fp32 residual stream in fp32).  Measured on the full 36-block Base
+    # model (test_full_depth_..., profiles/r02_fulldepth_parity_*.json): worst single element 5.5e-2,
+    # worst tensor 3.6e-2 in L2, median tensor 1.2e-2 at gamma ~ U(0.1,1) with 3x weights; 1.2e-2 /
+    # 1.0e-2 / 5e-3 at the gamma = 1e-6 training starts from.  The block-level tests hold 2e-2 per kernel.
     assert worst[0] < 6e-2, worst
 
 
@@ -157,7 +161,7 @@ def test_grad_window_matches_per_microbatch_accumulation(cnx_lib):
                     window.begin()
                 window.set_boundary(i == 1)
             with torch.autocast("cuda", dtype=torch.bfloat16):
-                out = model(xs[i].contiguous(memory_format=torch.channels_last))
+                out = model(xs[i])
                 loss = -(ts[i] * torch.log_softmax(out.float(), 1)).sum(1).mean()
             loss.backward()
             if window is not None and i == 0:      # block parameters have no .grad yet

@@ -1,0 +1,154 @@
+"""Data-parallel equivalence on real GPUs (SURVEY.md §4 distributed item).
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
+        --master-port 29611 tools/ddp_equiv.py [--res 96] [--batch 8]
+
+Every rank builds the same ConvNeXt-Base (seed 0, gamma ~ U(0.1,1) so the blocks matter) and sees
+the same PRE-MIXED global batch (2 accumulation micro-batches of world*b images, soft targets).
+
+ 1. N-rank gradients: rank r runs its slice [r*b, (r+1)*b) of each micro-batch through the product
+    path (bf16 autocast, GradWindow on, BucketedGradReducer hooks, all-reduce on the boundary
+    micro-batch only) -> averaged gradients.
+ 2. 1-rank gradients of the same global batch: the same model on the whole world*b micro-batches,
+    no reducer.  mean over world*b samples == mean over ranks of the local means, so the two
+    gradient sets must agree up to fp32 summation order (tolerance 1e-3, relative to the tensor's
+    largest element).
+ 3. Replicas stay identical: 3 full optimizer steps through `TrainStep` (fused optimizer, EMA) on
+    per-rank data; parameter and EMA-shadow checksums are all-gathered and must be bit-equal.
+
+Rank 0 prints one JSON line; exit code 0 only if every check holds.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+os.environ.setdefault("CNX_STRICT", "1")
+
+import torch
+import torch.distributed as dist
+
+
+def build(dev):
+    from image_classification_b200.convnext import create_convnext, DeepSupervisionModelB200
+    torch.manual_seed(0)
+    m = DeepSupervisionModelB200(create_convnext("convnext_base", 44), 44).to(dev).train()
+    with torch.no_grad():
+        for n, p in m.named_parameters():
+            if n.endswith("gamma"):
+                p.copy_(torch.rand_like(p) * 0.9 + 0.1)
+    return m
+
+
+def grads_of(model):
+    return {n: (p.grad.detach().clone() if p.grad is not None else None)
+            for n, p in model.named_parameters()}
+
+
+def run_micro_batches(model, xs, ts, window, reducer):
+    from image_classification_b200.loss import SoftTargetCrossEntropyB200
+    crit = SoftTargetCrossEntropyB200(0.1)
+    model.zero_grad(set_to_none=True)
+    n = len(xs)
+    for i in range(n):
+        boundary = i == n - 1
+        if reducer is not None:
+            reducer.set_sync(boundary)
+        if i == 0:
+            window.begin()
+        window.set_boundary(boundary)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            out = model(xs[i])[0]
+            loss = crit(out, ts[i])
+        loss.backward()
+    if reducer is not None:
+        reducer.finish()
+    window.end()
+    return grads_of(model)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--res", type=int, default=96)
+    ap.add_argument("--batch", type=int, default=8)
+    args = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    from image_classification_b200 import ddp, ema as ema_mod, loss as loss_mod, train_step
+    from image_classification_b200.block import GradWindow
+
+    b, R = args.batch, args.res
+    g = torch.Generator().manual_seed(42)
+    X = [torch.randn(world * b, 3, R, R, generator=g).to(dev) for _ in range(2)]
+    T = [torch.softmax(torch.randn(world * b, 44, generator=g) * 2, 1).to(dev) for _ in range(2)]
+
+    # -- 1. N-rank gradients
+    model = build(dev)
+    params = [p for p in model.parameters() if p.requires_grad]
+    reducer = ddp.BucketedGradReducer(params, bucket_bytes=32 << 20)
+    window = GradWindow(model)
+    sl = slice(rank * b, (rank + 1) * b)
+    g_ddp = run_micro_batches(model, [x[sl] for x in X], [t[sl] for t in T], window, reducer)
+    n_dropped, n_buckets = len(reducer.dropped), len(reducer.buckets)
+    # a second pass after the bucket rebuild (the overlapped path: hooks launch the buckets)
+    g_ddp2 = run_micro_batches(model, [x[sl] for x in X], [t[sl] for t in T], window, reducer)
+    # -- 2. 1-rank gradients of the global batch, same weights (hooks silenced: world==1 path)
+    reducer.set_sync(False)
+    g_one = run_micro_batches(model, X, T, window, None)
+    worst, worst2, worst_name = 0.0, 0.0, ""
+    for n in g_one:
+        a, c, d = g_one[n], g_ddp[n], g_ddp2[n]
+        if a is None:
+            assert c is None and d is None, n
+            continue
+        s = float(a.abs().max().clamp_min(1e-30))
+        e1 = float((a - c).abs().max()) / s
+        e2 = float((a - d).abs().max()) / s
+        if max(e1, e2) > max(worst, worst2):
+            worst_name = n
+        worst, worst2 = max(worst, e1), max(worst2, e2)
+    window.detach()
+
+    # -- 3. replicas identical after optimizer steps on per-rank data
+    model.zero_grad(set_to_none=True)
+    opt = torch.optim.AdamW(params, lr=1e-3, weight_decay=1e-2)
+    ema = ema_mod.EMAB200(model, 0.9997)
+    step = train_step.TrainStep(model, loss_mod.SoftTargetCrossEntropyB200(0.1), opt, None,
+                                torch.amp.GradScaler("cuda"), ema, train_step.StepConfig(2, 1.0, 44),
+                                grad_reducer=reducer)
+    gr = torch.Generator().manual_seed(1000 + rank)            # DIFFERENT data per rank
+    for i in range(6):
+        x = torch.randn(b, 3, R, R, generator=gr).to(dev)
+        t = torch.softmax(torch.randn(b, 44, generator=gr), 1).to(dev)
+        step.micro_step(x, t, i)
+    step.close()
+    sums = torch.stack([torch.stack([p.detach().double().sum() for p in params]).sum(),
+                        torch.stack([s.double().sum() for s in ema.shadow.values()]).sum(),
+                        torch.stack([p.detach().double().abs().sum() for p in params]).sum()])
+    allsums = [torch.zeros_like(sums) for _ in range(world)]
+    dist.all_gather(allsums, sums)
+    identical = all(torch.equal(allsums[0], s) for s in allsums)
+    ok = worst < 1e-3 and worst2 < 1e-3 and identical and n_dropped == 6 and reducer.reduced_steps >= 5
+    if rank == 0:
+        print(json.dumps({"world": world, "res": R, "batch_per_rank": b,
+                          "grad_maxrel_vs_1rank_discovery_step": worst,
+                          "grad_maxrel_vs_1rank_overlapped_step": worst2, "worst_tensor": worst_name,
+                          "tolerance": 1e-3, "unused_params_dropped": n_dropped, "buckets": n_buckets,
+                          "reduced_steps": reducer.reduced_steps,
+                          "replicas_identical": identical,
+                          "param_checksums": [float(s[0]) for s in allsums], "ok": ok}), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    return 0 if ok else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())
