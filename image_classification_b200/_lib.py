@@ -127,7 +127,7 @@ def check(rc: int, what: str) -> None:
 # kernels launched by one successful call of each entry point (bench.py's `gpu_launches` claim;
 # cudaMemsetAsync nodes are not counted)
 LAUNCHES_PER_CALL = {
-    "cnx_prep_block_weights": 4, "cnx_unfold_block_grads": 2, "cnx_dwconv_ln_fwd": 2,
+    "cnx_prep_block_weights": 1, "cnx_unfold_block_grads": 2, "cnx_dwconv_ln_fwd": 2,
     "cnx_dwconv_ln_bwd": 2, "cnx_dwconv_ln_bwd_acc": 2, "cnx_gemm_bf16": 1, "cnx_layernorm_fwd": 1, "cnx_layernorm_bwd": 1, "cnx_colsum_bf16": 1, "cnx_dwconv_kxk_fwd": 1, "cnx_dwconv_kxk_bwd": 2, "cnx_avgpool_nhwc_fwd": 1, "cnx_avgpool_nhwc_bwd": 1, "cnx_layernorm_patch_fwd": 1, "cnx_layernorm_patch_bwd": 1, "cnx_patchify_nchw_f32": 1, "cnx_fc1_gelu_fwd": 1, "cnx_fc2_residual_fwd": 1,
     "cnx_mlp_bwd_dz": 1, "cnx_mlp_bwd_dxhat": 1, "cnx_mlp_bwd_wgrad": 2, "cnx_mix_batch": 1, "cnx_mix_batch_smooth": 1,
     "cnx_softce_fwd_bwd": 1, "cnx_ema_lerp_multi": 1, "cnx_optim_grad_norm": 1, "cnx_optim_adamw_ema": 1, "cnx_nchw_f32_to_nhwc_bf16": 1,

@@ -16,17 +16,16 @@ namespace cnx {
 namespace {
 
 // in [R][Cc] fp32 (row-major) -> out [R][Cc] bf16 and outT [Cc][R] bf16, scaled by
-// row_scale[r] (nullable) and col_scale[c] (nullable).  32x32 tile through padded smem.
-__global__ void __launch_bounds__(256)
-scale_cast_transpose_kernel(const float* __restrict__ in, const float* __restrict__ row_scale,
-                            const float* __restrict__ col_scale, __nv_bfloat16* __restrict__ out,
-                            __nv_bfloat16* __restrict__ outT, int R, int Cc) {
-  __shared__ float tile[32][33];
+// row_scale[r] (nullable) and col_scale[c] (nullable).  32x32 tile (bx, by) through padded smem.
+__device__ __forceinline__ void scale_cast_transpose_tile(
+    float (*tile)[33], int bx, int by, const float* __restrict__ in,
+    const float* __restrict__ row_scale, const float* __restrict__ col_scale,
+    __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ outT, int R, int Cc) {
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
-  const int c = blockIdx.x * 32 + tx;
+  const int c = bx * 32 + tx;
 #pragma unroll
   for (int i = 0; i < 32; i += 8) {
-    const int r = blockIdx.y * 32 + ty + i;
+    const int r = by * 32 + ty + i;
     float v = 0.f;
     if (r < R && c < Cc) {
       v = in[static_cast<size_t>(r) * Cc + c];
@@ -37,39 +36,63 @@ scale_cast_transpose_kernel(const float* __restrict__ in, const float* __restric
     tile[ty + i][tx] = v;
   }
   __syncthreads();
-  const int r2 = blockIdx.y * 32 + tx;  // transposed: threads run along original rows
+  const int r2 = by * 32 + tx;  // transposed: threads run along original rows
 #pragma unroll
   for (int i = 0; i < 32; i += 8) {
-    const int c2 = blockIdx.x * 32 + ty + i;
+    const int c2 = bx * 32 + ty + i;
     if (r2 < R && c2 < Cc)
       outT[static_cast<size_t>(c2) * R + r2] = __float2bfloat16_rn(tile[tx][ty + i]);
   }
 }
 
-// b1f[j] = fc1_b[j] + sum_c fc1_w[j,c] * ln_b[c]      (one warp per row j)
-__global__ void __launch_bounds__(256)
-fold_bias1_kernel(const float* __restrict__ w, const float* __restrict__ b,
-                  const float* __restrict__ ln_b, float* __restrict__ b1f, int R, int Cc) {
-  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
-  const int lane = threadIdx.x & 31;
-  if (row >= R) return;
-  float s = 0.f;
-  for (int c = lane; c < Cc; c += 32) s = fmaf(w[static_cast<size_t>(row) * Cc + c], ln_b[c], s);
-  s = warp_sum(s);
-  if (lane == 0) b1f[row] = b[row] + s;
-}
+struct PrepArgs {
+  const float *dw_w, *ln_w, *ln_b, *fc1_w, *fc1_b, *fc2_w, *fc2_b, *gamma;
+  float* wt_dw;
+  __nv_bfloat16 *w1f, *w1fT, *w2f, *w2fT;
+  float *b1f, *b2f;
+  int C;
+  int n_t1, n_t2, n_b1;      // CTA counts of the first three sections
+};
 
-// wt_dw[t][c] = dw_w[c][t];  b2f[c] = gamma[c] * fc2_b[c]
-__global__ void __launch_bounds__(256)
-prep_small_kernel(const float* __restrict__ dw_w, const float* __restrict__ gamma,
-                  const float* __restrict__ fc2_b, float* __restrict__ wt_dw,
-                  float* __restrict__ b2f, int C) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+// The whole fold of one block in ONE launch (four launches until round 2: ~1 ms per optimizer
+// step over 36 blocks, most of it launch overhead).  CTA sections, in order:
+//   [0, n_t1)          fc1_w [4C][C] tiles, columns scaled by ln_w  -> w1f, w1fT
+//   [n_t1, +n_t2)      fc2_w [C][4C] tiles, rows scaled by gamma    -> w2f, w2fT
+//   [.., +n_b1)        b1f[j] = fc1_b[j] + sum_c fc1_w[j,c] * ln_b[c]   (one warp per row j)
+//   the rest           wt_dw[t][c] = dw_w[c][t];  b2f[c] = gamma[c] * fc2_b[c]
+__global__ void __launch_bounds__(256) prep_block_kernel(const PrepArgs a) {
+  __shared__ float tile[32][33];
+  const int C = a.C, R4 = 4 * a.C;
+  int b = blockIdx.x;
+  if (b < a.n_t1) {
+    const int nbx = (C + 31) / 32;
+    scale_cast_transpose_tile(tile, b % nbx, b / nbx, a.fc1_w, nullptr, a.ln_w, a.w1f, a.w1fT, R4, C);
+    return;
+  }
+  b -= a.n_t1;
+  if (b < a.n_t2) {
+    const int nbx = (R4 + 31) / 32;
+    scale_cast_transpose_tile(tile, b % nbx, b / nbx, a.fc2_w, a.gamma, nullptr, a.w2f, a.w2fT, C, R4);
+    return;
+  }
+  b -= a.n_t2;
+  if (b < a.n_b1) {
+    const int row = b * 8 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= R4) return;
+    float s = 0.f;
+    for (int c = lane; c < C; c += 32) s = fmaf(a.fc1_w[static_cast<size_t>(row) * C + c], a.ln_b[c], s);
+    s = warp_sum(s);
+    if (lane == 0) a.b1f[row] = a.fc1_b[row] + s;
+    return;
+  }
+  b -= a.n_b1;
+  const int i = b * 256 + threadIdx.x;
   if (i < 49 * C) {
     const int t = i / C, c = i % C;
-    wt_dw[i] = dw_w[c * 49 + t];
+    a.wt_dw[i] = a.dw_w[c * 49 + t];
   }
-  if (i < C) b2f[i] = gamma[i] * fc2_b[i];
+  if (i < C) a.b2f[i] = a.gamma[i] * a.fc2_b[i];
 }
 
 // fc1 side of the adjoint.  grid (ceil(C/32), row_splits), block 32x8.
@@ -175,20 +198,17 @@ int prep_block_weights(const float* dw_w, const float* ln_w, const float* ln_b, 
     return CNX_ERR_BAD_SHAPE;
   }
   const int R4 = 4 * C;
-  {  // fc1_w [4C][C], columns scaled by ln_w
-    dim3 grid((C + 31) / 32, (R4 + 31) / 32);
-    scale_cast_transpose_kernel<<<grid, 256, 0, stream>>>(
-        fc1_w, nullptr, ln_w, static_cast<__nv_bfloat16*>(w1f), static_cast<__nv_bfloat16*>(w1fT),
-        R4, C);
-  }
-  {  // fc2_w [C][4C], rows scaled by gamma
-    dim3 grid((R4 + 31) / 32, (C + 31) / 32);
-    scale_cast_transpose_kernel<<<grid, 256, 0, stream>>>(
-        fc2_w, ls_gamma, nullptr, static_cast<__nv_bfloat16*>(w2f),
-        static_cast<__nv_bfloat16*>(w2fT), C, R4);
-  }
-  fold_bias1_kernel<<<(R4 + 7) / 8, 256, 0, stream>>>(fc1_w, fc1_b, ln_b, b1f, R4, C);
-  prep_small_kernel<<<(49 * C + 255) / 256, 256, 0, stream>>>(dw_w, ls_gamma, fc2_b, wt_dw, b2f, C);
+  PrepArgs a;
+  a.dw_w = dw_w; a.ln_w = ln_w; a.ln_b = ln_b; a.fc1_w = fc1_w; a.fc1_b = fc1_b; a.fc2_w = fc2_w;
+  a.fc2_b = fc2_b; a.gamma = ls_gamma; a.wt_dw = wt_dw;
+  a.w1f = static_cast<__nv_bfloat16*>(w1f); a.w1fT = static_cast<__nv_bfloat16*>(w1fT);
+  a.w2f = static_cast<__nv_bfloat16*>(w2f); a.w2fT = static_cast<__nv_bfloat16*>(w2fT);
+  a.b1f = b1f; a.b2f = b2f; a.C = C;
+  a.n_t1 = ((C + 31) / 32) * ((R4 + 31) / 32);
+  a.n_t2 = a.n_t1;
+  a.n_b1 = (R4 + 7) / 8;
+  const int n_small = (49 * C + 255) / 256;
+  prep_block_kernel<<<a.n_t1 + a.n_t2 + a.n_b1 + n_small, 256, 0, stream>>>(a);
   return check_launch("prep_block_weights");
 }
 

@@ -9,10 +9,14 @@ the same PRE-MIXED global batch (2 accumulation micro-batches of world*b images,
  1. N-rank gradients: rank r runs its slice [r*b, (r+1)*b) of each micro-batch through the product
     path (bf16 autocast, GradWindow on, BucketedGradReducer hooks, all-reduce on the boundary
     micro-batch only) -> averaged gradients.
- 2. 1-rank gradients of the same global batch: the same model on the whole world*b micro-batches,
-    no reducer.  mean over world*b samples == mean over ranks of the local means, so the two
-    gradient sets must agree up to fp32 summation order (tolerance 1e-3, relative to the tensor's
-    largest element).
+ 2. The same gradients WITHOUT the exchange layer: every rank also runs every other rank's slice
+    locally (same shapes, hence the same kernels and bit-identical forward passes) and averages:
+    must equal the all-reduced result up to fp32 summation order (tolerance 1e-3 relative to the
+    tensor's largest element; measured ~1e-6).  Informational, with bf16 tolerance: the 1-rank
+    gradient of the whole world*b batch in ONE pass — a different batch shape picks different GEMM
+    tilings, fp32 sums differ in their last bit, single bf16 roundings flip and the difference
+    grows over 36 blocks to ~2e-2, the same distance both have from the fp32 oracle
+    (tools/batch_split_equiv.py, profiles/r02_batch_split_equiv.json).
  3. Replicas stay identical: 3 full optimizer steps through `TrainStep` (fused optimizer, EMA) on
     per-rank data; parameter and EMA-shadow checksums are all-gathered and must be bit-equal.
 
@@ -100,12 +104,22 @@ def main():
     n_dropped, n_buckets = len(reducer.dropped), len(reducer.buckets)
     # a second pass after the bucket rebuild (the overlapped path: hooks launch the buckets)
     g_ddp2 = run_micro_batches(model, [x[sl] for x in X], [t[sl] for t in T], window, reducer)
-    # -- 2. 1-rank gradients of the global batch, same weights (hooks silenced: world==1 path)
+    # -- 2. the same thing without the exchange layer: every slice locally, averaged
     reducer.set_sync(False)
-    g_one = run_micro_batches(model, X, T, window, None)
-    worst, worst2, worst_name = 0.0, 0.0, ""
-    for n in g_one:
-        a, c, d = g_one[n], g_ddp[n], g_ddp2[n]
+    acc = None
+    for r in range(world):
+        slr = slice(r * b, (r + 1) * b)
+        gr_ = run_micro_batches(model, [x[slr] for x in X], [t[slr] for t in T], window, None)
+        if acc is None:
+            acc = {n: (v / world if v is not None else None) for n, v in gr_.items()}
+        else:
+            for n, v in gr_.items():
+                if v is not None:
+                    acc[n] += v / world
+    g_one = run_micro_batches(model, X, T, window, None)     # informational: one pass, batch world*b
+    worst, worst2, worst_name, worst_global = 0.0, 0.0, "", 0.0
+    for n in acc:
+        a, c, d = acc[n], g_ddp[n], g_ddp2[n]
         if a is None:
             assert c is None and d is None, n
             continue
@@ -115,6 +129,8 @@ def main():
         if max(e1, e2) > max(worst, worst2):
             worst_name = n
         worst, worst2 = max(worst, e1), max(worst2, e2)
+        worst_global = max(worst_global, float((g_one[n] - c).abs().max()) /
+                           float(g_one[n].abs().max().clamp_min(1e-30)))
     window.detach()
 
     # -- 3. replicas identical after optimizer steps on per-rank data
@@ -136,12 +152,15 @@ def main():
     allsums = [torch.zeros_like(sums) for _ in range(world)]
     dist.all_gather(allsums, sums)
     identical = all(torch.equal(allsums[0], s) for s in allsums)
-    ok = worst < 1e-3 and worst2 < 1e-3 and identical and n_dropped == 6 and reducer.reduced_steps >= 5
+    ok = (worst < 1e-3 and worst2 < 1e-3 and worst_global < 4e-2 and identical and n_dropped == 6
+          and reducer.reduced_steps >= 5)
     if rank == 0:
         print(json.dumps({"world": world, "res": R, "batch_per_rank": b,
-                          "grad_maxrel_vs_1rank_discovery_step": worst,
-                          "grad_maxrel_vs_1rank_overlapped_step": worst2, "worst_tensor": worst_name,
-                          "tolerance": 1e-3, "unused_params_dropped": n_dropped, "buckets": n_buckets,
+                          "grad_maxrel_vs_local_mean_discovery_step": worst,
+                          "grad_maxrel_vs_local_mean_overlapped_step": worst2,
+                          "worst_tensor": worst_name, "tolerance": 1e-3,
+                          "grad_maxrel_vs_one_pass_global_batch_bf16": worst_global,
+                          "tolerance_bf16": 4e-2, "unused_params_dropped": n_dropped, "buckets": n_buckets,
                           "reduced_steps": reducer.reduced_steps,
                           "replicas_identical": identical,
                           "param_checksums": [float(s[0]) for s in allsums], "ok": ok}), flush=True)
