@@ -285,6 +285,13 @@ class B200Trainer:
         self.step_obj = train_step.TrainStep(self.model, self.criterion, self.opt, self.sched,
                                              self.scaler, self.ema, cfg, self.reducer,
                                              use_fused_optim=fused)
+        # forward + CE + backward of the two micro-batch positions as two CUDA graphs
+        # (graphed.GraphedTrainStep); CNX_NO_GRAPH=1: every launch enqueued from Python (A/B switch)
+        self.graphed = None
+        if not os.environ.get("CNX_NO_GRAPH"):
+            from image_classification_b200.graphed import GraphedTrainStep
+            self.graphed = GraphedTrainStep(self.step_obj, (micro_batch, 3, res, res),
+                                            (micro_batch, NUM_CLASSES), device)
         g = torch.Generator().manual_seed(100 + rank)
         # synthetic "normalised pixels" (dataset.py:233-236) and hard labels, pinned on the host
         self.host_images = [torch.randn(micro_batch, 3, res, res, generator=g).pin_memory()
@@ -295,16 +302,22 @@ class B200Trainer:
         self.dev_labels = [t.to(device) for t in self.host_labels]
         self.batch_idx = 0
 
-    def _micro(self, images, labels):
-        mixed, targets = self.mixer(images, labels, rng=self.rng)
-        loss = self.step_obj.micro_step(mixed, targets, self.batch_idx)
+    def _micro(self, images, labels, eager=False):
+        if self.graphed is not None and not eager:   # the mix kernel writes the graphs' static inputs
+            mixed, targets = self.mixer(images, labels, rng=self.rng, out=self.graphed.images,
+                                        targets_out=self.graphed.targets)
+            loss = self.graphed.micro_step(mixed, targets, self.batch_idx)
+        else:
+            mixed, targets = self.mixer(images, labels, rng=self.rng)
+            loss = self.step_obj.micro_step(mixed, targets, self.batch_idx)
         self.batch_idx += 1
         return loss
 
-    def step_resident(self):
-        """inputs already in HBM"""
+    def step_resident(self, eager=False):
+        """inputs already in HBM; eager=True: every launch enqueued from Python (the per-kernel
+        event instrumentation of profile_kernels needs the individual library calls)"""
         for i in range(ACCUM):
-            loss = self._micro(self.dev_images[i], self.dev_labels[i])
+            loss = self._micro(self.dev_images[i], self.dev_labels[i], eager)
         return loss
 
     def run_e2e(self, steps: int) -> list[float]:
@@ -405,13 +418,13 @@ def profile_kernels(trainer, device):
             ev.record()
             recs.append((name, open_ev.pop(name), ev, args))
 
-    trainer.step_resident()                       # re-warm after the e2e loop
+    trainer.step_resident(eager=True)             # re-warm after the e2e loop (eager path)
     torch.cuda.synchronize(device)
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     _lib.call_hook = hook
     try:
         s.record()
-        trainer.step_resident()
+        trainer.step_resident(eager=True)
         e.record()
         torch.cuda.synchronize(device)
     finally:
@@ -486,7 +499,9 @@ def run_convnext_config(tag, device, world, rank, local, micro_batch, res, steps
     clocks = sampler.stop() if (sampler is not None and rank == 0) else None
     out = {"images_per_s": round(imgs_per_step * steps / (ms * 1e-3), 2),
            "ms_per_step": round(ms / steps, 3), "steps": steps, "global_batch": imgs_per_step,
-           "micro_batch_per_gpu": micro_batch, "res": res, "gpu_launches": launches}
+           "micro_batch_per_gpu": micro_batch, "res": res, "gpu_launches": launches,
+           "launch_mode": ("2 CUDA-graph replays (fwd + CE + bwd per micro-batch) + mix, optimizer "
+                           "launches" if tr.graphed is not None else "every kernel enqueued from Python")}
     if want_e2e:
         tr.run_e2e(2)
         e2e_losses = []

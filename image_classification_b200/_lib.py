@@ -51,6 +51,7 @@ SIGNATURES = {
     "cnx_debug_timeout_flag": (I, []),
     "cnx_debug_set_timeout_flag": (None, [I]),
     "cnx_debug_gemm_tuning": (None, [I, I, I, I]),
+    "cnx_debug_gemm_epilogue_warps": (None, [I]),
     "cnx_debug_max_clusters": (I, [I]),
     "cnx_workspace_bytes": (c_size_t, [I, I, I, I, I]),
     "cnx_prep_block_weights": (I, [P] * 8 + [P] * 7 + [I, P]),

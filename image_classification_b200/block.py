@@ -22,6 +22,13 @@ from . import _lib, ops
 _weight_epoch = 0
 
 
+# While a CUDA graph is being captured the fold is always recorded (a replay then folds the weights
+# of THAT replay).  A step made of several graphs replayed in a fixed order (one per micro-batch of
+# an accumulation window, graphed.GraphedTrainStep) records it in the first graph only and sets
+# this to True while capturing the others, which then read the tensors the first graph writes.
+capture_reuses_fold = False
+
+
 def notify_weights_changed() -> None:
     """Invalidate the folded-weight caches of all ConvNeXtBlockB200 modules.  Call after writing
     parameter storage with anything that is not a torch in-place op (raw-pointer kernels)."""
@@ -147,8 +154,10 @@ class ConvNeXtBlockB200(nn.Module):
         # Inside a CUDA-graph capture the fold is always recorded, so a replay refolds the weights
         # of that replay instead of baking a stale copy into the graph.
         key = (_weight_epoch,) + tuple((p.data_ptr(), p._version) for p in params)
-        if (self._fold is None or key != self._fold_key
-                or torch.cuda.is_current_stream_capturing()):
+        capturing = torch.cuda.is_current_stream_capturing()
+        if capturing and capture_reuses_fold and self._fold is not None:
+            return self._fold
+        if self._fold is None or key != self._fold_key or capturing:
             self._fold = ops.prep_block_weights(*[p.detach() for p in params])
             self._fold_key = key
         return self._fold

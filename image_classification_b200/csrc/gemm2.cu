@@ -37,8 +37,7 @@ namespace {
 
 constexpr int BM = 128;
 constexpr int BK = 64;                 // 64 bf16 = 128 B = one swizzle row
-constexpr int kThreads = 320;          // 10 warps
-constexpr int kEpiWarps = 8;
+constexpr int kDuos = 8;               // (TMEM lane quarter, column half) pairs = staging buffer pairs
 constexpr int EPI_ATOMIC_F32 = 5;      // internal: split-K fp32 reduction
 constexpr uint32_t kChunkBytes = 32 * 128;   // staging chunk: 32 rows x 64 bf16, 128B swizzle
 
@@ -54,7 +53,7 @@ struct Cfg {
   static constexpr uint32_t kBBytes = kBRows * BK * 2;
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
   // bf16 epilogues stage through shared memory (64 KB); the fp32 reduction epilogue does not
-  static constexpr uint32_t kEpiBytes = STAGED ? kEpiWarps * 2 * kChunkBytes : 0;
+  static constexpr uint32_t kEpiBytes = STAGED ? kDuos * 2 * kChunkBytes : 0;
   static constexpr uint32_t kBarBytes = 512;
   static constexpr uint32_t kSmemMax = 232448;           // 227 KB opt-in limit per CTA
   // as many operand stages as fit: the main loop is bound by bytes in flight towards L2
@@ -65,7 +64,7 @@ struct Cfg {
   static_assert(kStages >= 3, "operand ring too shallow");
 };
 
-struct GemmTuning { int stages = -1, pair = -1, bn = -1, splits = -1; };
+struct GemmTuning { int stages = -1, pair = -1, bn = -1, splits = -1, epi_warps = 0; };
 GemmTuning g_tune;                 // development overrides (cnx_debug_gemm_tuning)
 
 struct Gemm2Params {
@@ -166,8 +165,13 @@ __device__ __forceinline__ ItemCoord decode(const Gemm2Params& p, int w) {
   return c;
 }
 
-template <int BN, int EPI, bool PAIR>
-__global__ void __launch_bounds__(kThreads, 1)
+// EW = epilogue warps: 8 (one warp per (lane quarter, column half): both 32-column halves of every
+// 64-column chunk) or 16 (two warps per such pair, one 32-column half each, sharing the pair's
+// staging buffers through a 64-thread named barrier).  The GELU-carrying epilogues are latency-
+// bound with 2 warps per scheduler (ncu r01: issue slots 37 % busy, tensor pipe 40 %); 4 warps
+// per scheduler hide the tcgen05.ld / shared-memory / polynomial latencies.
+template <int BN, int EPI, bool PAIR, int EW>
+__global__ void __launch_bounds__(64 + 32 * EW, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
              const __grid_constant__ CUtensorMap map_d0, const __grid_constant__ CUtensorMap map_d1,
              const __grid_constant__ CUtensorMap map_r, const Gemm2Params p) {
@@ -187,8 +191,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
   uint64_t* empty_bar = full_bar + kStages;
   uint64_t* tmem_full_bar = empty_bar + kStages;     // [2]
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;      // [2]
-  uint64_t* r_bar = tmem_empty_bar + 2;              // [kEpiWarps]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(r_bar + kEpiWarps);
+  uint64_t* r_bar = tmem_empty_bar + 2;              // [kDuos]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(r_bar + kDuos);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = PAIR ? cluster_ctarank() : 0u;       // 0 = leader of the CTA pair
@@ -209,10 +213,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
 #pragma unroll
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tmem_full_bar[b], 1);
-      mbar_init(&tmem_empty_bar[b], PAIR ? 2 * kEpiWarps : kEpiWarps);
+      mbar_init(&tmem_empty_bar[b], PAIR ? 2 * EW : EW);
     }
 #pragma unroll
-    for (int w = 0; w < kEpiWarps; ++w) mbar_init(&r_bar[w], 1);
+    for (int w = 0; w < kDuos; ++w) mbar_init(&r_bar[w], 1);
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -320,6 +324,207 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
         else umma_commit(&tmem_full_bar[ab]);
       }
     }
+  } else if constexpr (EW == 16) {
+    // ------------------------------------------------- epilogue warps, two per staging buffer pair
+    static_assert(!kF32Out, "the fp32 reduction epilogue runs with 8 epilogue warps");
+    const int ew = warp - 2;                   // 0..15
+    const int q = warp & 3;                    // TMEM lane quarter this warp may read
+    const int part = ew >> 2;                  // 0..3
+    const int half = part >> 1;                // column half of the tile
+    const int mysub = part & 1;                // this warp's 32-column half of every 64-column chunk
+    const int duo = half * 4 + q;              // the warps (mysub 0, 1) of a duo share buffers
+    const bool lead = (mysub == 0) && (lane == 0);     // issues the duo's TMA loads / stores
+    unsigned char* buf0 = epi_base + duo * 2 * kChunkBytes;  // output staging (D0)
+    unsigned char* buf1 = buf0 + kChunkBytes;                // D1 staging or R landing zone
+    const uint32_t buf0_u = smem_u32(buf0), buf1_u = smem_u32(buf1);
+    const uint32_t row_off = static_cast<uint32_t>(lane) * 128u;
+    const uint32_t sw = static_cast<uint32_t>(lane & 7);
+    uint64_t* rbar = &r_bar[duo];
+    uint32_t r_jobs = 0;
+    auto duo_sync = [&]() { asm volatile("bar.sync %0, 64;" ::"r"(1 + duo) : "memory"); };
+
+    auto chunk_n = [&](const ItemCoord& c, int ch) { return c.n_blk * BN + half * (BN / 2) + ch * 64; };
+    auto next_valid = [&](int& w, int& ch) {
+      while (w < p.items) {
+        const ItemCoord c = decode(p, w);
+        for (; ch < kChunks; ++ch)
+          if (chunk_n(c, ch) < p.N) return;
+        ch = 0;
+        w += w_stride;
+      }
+    };
+    auto issue_r = [&](int w, int ch) {
+      const ItemCoord c = decode(p, w);
+      mbar_arrive_expect_tx(rbar, kChunkBytes);
+      tma_load_2d(buf1, &map_r, rbar, chunk_n(c, ch),
+                  c.m_blk * kTileM + static_cast<int>(rank) * BM + q * 32);
+    };
+    if (kHasR && lead) {
+      int w = w_first, ch = 0;
+      next_valid(w, ch);
+      if (w < p.items) issue_r(w, ch);
+    }
+
+    float2 cs_acc[kChunks];                    // column sums over this warp's 16 rows
+#pragma unroll
+    for (int ch = 0; ch < kChunks; ++ch) cs_acc[ch] = make_float2(0.f, 0.f);
+    int cs_nblk = -1;
+    auto flush_colsum = [&]() {
+      if (EPI == EPI_GELU_GRAD && p.colsum != nullptr && cs_nblk >= 0) {
+#pragma unroll
+        for (int ch = 0; ch < kChunks; ++ch) {
+          const int n = cs_nblk * BN + half * (BN / 2) + ch * 64 + 2 * lane;
+          if (n < p.N) {
+            atomicAdd(p.colsum + n, cs_acc[ch].x);
+            atomicAdd(p.colsum + n + 1, cs_acc[ch].y);
+          }
+          cs_acc[ch] = make_float2(0.f, 0.f);
+        }
+      }
+    };
+
+    int i = 0;
+    for (int w = w_first; w < p.items; w += w_stride, ++i) {
+      const ItemCoord c = decode(p, w);
+      const int ab = i & 1;
+      const int row0 = c.m_blk * kTileM + static_cast<int>(rank) * BM + q * 32;
+      if (EPI == EPI_GELU_GRAD && c.n_blk != cs_nblk) {
+        flush_colsum();
+        cs_nblk = c.n_blk;
+      }
+      mbar_wait(&tmem_full_bar[ab], (i >> 1) & 1, p.timeout_flag);
+      tc_fence_after();
+      const uint32_t tmem_acc = tmem_base + ab * BN + (static_cast<uint32_t>(q * 32) << 16) +
+                                half * (BN / 2);
+#pragma unroll
+      for (int ch = 0; ch < kChunks; ++ch) {
+        const int n_g = chunk_n(c, ch);
+        if (n_g >= p.N) continue;                        // uniform over the duo
+
+        if (kHasR) {
+          mbar_wait(rbar, r_jobs & 1, p.timeout_flag);
+          ++r_jobs;
+        }
+        uint32_t pk[16];
+        uint32_t hk[EPI == EPI_BIAS_GELU ? 16 : 1];
+#pragma unroll
+        for (int piece = 0; piece < 2; ++piece) {
+          const int col = mysub * 32 + piece * 16;       // column offset inside the chunk
+          uint32_t v[16];
+          tmem_ld_32x16(tmem_acc + ch * 64 + col, v);
+          uint32_t rr[8];
+          if (kHasR) {
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+              const uint32_t unit = static_cast<uint32_t>(mysub * 4 + piece * 2 + k);
+              const uint4 u = ld_shared_v4(buf1_u + row_off + ((unit ^ sw) << 4));
+              rr[4 * k] = u.x; rr[4 * k + 1] = u.y; rr[4 * k + 2] = u.z; rr[4 * k + 3] = u.w;
+            }
+          }
+          tmem_ld_wait();
+          const int n = n_g + col;
+          float2 f[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            f[j] = make_float2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+          if (EPI == EPI_BIAS_GELU || EPI == EPI_BIAS_RESIDUAL || EPI == EPI_BIAS) {
+#pragma unroll
+            for (int j = 0; j < 16; j += 4) {
+              if (n + j < p.N) {
+                const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + n + j));
+                f[j / 2].x += b.x; f[j / 2].y += b.y;
+                f[j / 2 + 1].x += b.z; f[j / 2 + 1].y += b.w;
+              }
+            }
+          }
+          if (EPI == EPI_BIAS_RESIDUAL) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float2 r2 = bf16x2_to_f32x2(rr[j]);
+              f[j].x += r2.x;
+              f[j].y += r2.y;
+            }
+          }
+          if (EPI == EPI_GELU_GRAD) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] = fmul2(f[j], gelu_grad2(bf16x2_to_f32x2(rr[j])));
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) pk[piece * 8 + j] = f32x2_to_bf16x2(f[j].x, f[j].y);
+          if (EPI == EPI_BIAS_GELU) {
+            // activation of the ROUNDED pre-activation (what backward will see), second output
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float2 h2 = gelu2(bf16x2_to_f32x2(pk[piece * 8 + j]));
+              hk[piece * 8 + j] = f32x2_to_bf16x2(h2.x, h2.y);
+            }
+          }
+        }
+
+        if (ch == kChunks - 1) {
+          // last TMEM read of this tile is done: hand the accumulator back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if (PAIR) mbar_arrive_cluster(dsmem_map(smem_u32(&tmem_empty_bar[ab]), 0));
+            else mbar_arrive(&tmem_empty_bar[ab]);
+          }
+        }
+
+        // A: the previous chunk's TMA stores have drained the staging buffers, and both warps are
+        // done reading this chunk's R (and the previous chunk's column sums)
+        if (lead) tma_store_wait_read();
+        duo_sync();
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint32_t unit = static_cast<uint32_t>(mysub * 4 + k);
+          st_shared_v4(buf0_u + row_off + ((unit ^ sw) << 4), pk[4 * k], pk[4 * k + 1],
+                       pk[4 * k + 2], pk[4 * k + 3]);
+          if (EPI == EPI_BIAS_GELU)
+            st_shared_v4(buf1_u + row_off + ((unit ^ sw) << 4), hk[4 * k], hk[4 * k + 1],
+                         hk[4 * k + 2], hk[4 * k + 3]);
+        }
+        fence_proxy_async();          // make this lane's st.shared visible to the TMA engine
+        duo_sync();                   // B: the whole 32 x 64 chunk is staged
+        if (lead) {
+          if (kHasR) {                // R of this chunk is consumed: fetch the next one
+            int w2 = w, ch2 = ch + 1;
+            next_valid(w2, ch2);
+            if (w2 < p.items) issue_r(w2, ch2);
+          }
+          tma_store_2d(&map_d0, buf0, n_g, row0);
+          if (EPI == EPI_BIAS_GELU) tma_store_2d(&map_d1, buf1, n_g, row0);
+          tma_store_commit();
+        }
+        if (EPI == EPI_GELU_GRAD) {
+          // column sums of the ROUNDED dz: lane l owns columns 2l, 2l+1 of the chunk, this warp
+          // the rows [16 * mysub, +16) (rows past M hold acc = 0 -> contribute nothing)
+          const uint32_t cchunk = static_cast<uint32_t>(lane >> 2), cword = static_cast<uint32_t>(lane & 3);
+          float2 s = cs_acc[ch];
+#pragma unroll
+          for (int r0 = 0; r0 < 16; ++r0) {
+            const int r = mysub * 16 + r0;
+            const float2 t2 = bf16x2_to_f32x2(
+                ld_shared_b32(buf0_u + r * 128 + ((cchunk ^ (r & 7)) << 4) + (cword << 2)));
+            s.x += t2.x;
+            s.y += t2.y;
+          }
+          cs_acc[ch] = s;
+        }
+      }
+
+      if (chunk_n(c, kChunks - 1) >= p.N) {
+        // the last chunk was skipped (ragged N): release the accumulator here
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if (PAIR) mbar_arrive_cluster(dsmem_map(smem_u32(&tmem_empty_bar[ab]), 0));
+          else mbar_arrive(&tmem_empty_bar[ab]);
+        }
+      }
+    }
+    flush_colsum();
+    if (lead) tma_store_wait_all();
   } else {
     // ------------------------------------------------------------------ epilogue warps
     const int ew = warp - 2;
@@ -560,16 +765,16 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
   }
 }
 
-template <int BN, int EPI, bool PAIR>
+template <int BN, int EPI, bool PAIR, int EW>
 int launch2(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md0,
             const CUtensorMap& md1, const CUtensorMap& mr, const Gemm2Params& p_in, int grid,
             cudaStream_t stream) {
   using L = Cfg<BN, PAIR, !(EPI == EPI_STORE_F32 || EPI == EPI_ATOMIC_F32)>;
   Gemm2Params p = p_in;
   p.stages = (g_tune.stages >= 2 && g_tune.stages < L::kStages) ? g_tune.stages : L::kStages;
-  const int rc_attr = ensure_dyn_smem(gemm2_kernel<BN, EPI, PAIR>, L::kTotal, "gemm_bf16");
+  const int rc_attr = ensure_dyn_smem(gemm2_kernel<BN, EPI, PAIR, EW>, L::kTotal, "gemm_bf16");
   if (rc_attr != CNX_OK) return rc_attr;
-  cudaError_t e = launch_pdl(gemm2_kernel<BN, EPI, PAIR>, grid, kThreads, L::kTotal, stream,
+  cudaError_t e = launch_pdl(gemm2_kernel<BN, EPI, PAIR, EW>, grid, 64 + 32 * EW, L::kTotal, stream,
                              PAIR ? 2u : 1u, ma, mb, md0, md1, mr, p);
   if (e != cudaSuccess) {
     set_last_error("gemm_bf16 launch: %s", cudaGetErrorString(e));
@@ -579,19 +784,24 @@ int launch2(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md0
 }
 
 template <int BN, bool PAIR>
-int dispatch(int epi, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md0,
+int dispatch(int epi, int ew, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md0,
              const CUtensorMap& md1, const CUtensorMap& mr, const Gemm2Params& p, int grid,
              cudaStream_t stream) {
+#define CNX_GEMM_CASE(E)                                                                   \
+  case E:                                                                                  \
+    return ew == 16 ? launch2<BN, E, PAIR, 16>(ma, mb, md0, md1, mr, p, grid, stream)      \
+                    : launch2<BN, E, PAIR, 8>(ma, mb, md0, md1, mr, p, grid, stream);
   switch (epi) {
-    case EPI_STORE_BF16:    return launch2<BN, EPI_STORE_BF16, PAIR>(ma, mb, md0, md1, mr, p, grid, stream);
-    case EPI_BIAS:          return launch2<BN, EPI_BIAS, PAIR>(ma, mb, md0, md1, mr, p, grid, stream);
-    case EPI_BIAS_GELU:     return launch2<BN, EPI_BIAS_GELU, PAIR>(ma, mb, md0, md1, mr, p, grid, stream);
-    case EPI_BIAS_RESIDUAL: return launch2<BN, EPI_BIAS_RESIDUAL, PAIR>(ma, mb, md0, md1, mr, p, grid, stream);
-    case EPI_GELU_GRAD:     return launch2<BN, EPI_GELU_GRAD, PAIR>(ma, mb, md0, md1, mr, p, grid, stream);
-    case EPI_STORE_F32:     return launch2<BN, EPI_STORE_F32, PAIR>(ma, mb, md0, md1, mr, p, grid, stream);
-    case EPI_ATOMIC_F32:    return launch2<BN, EPI_ATOMIC_F32, PAIR>(ma, mb, md0, md1, mr, p, grid, stream);
+    CNX_GEMM_CASE(EPI_STORE_BF16)
+    CNX_GEMM_CASE(EPI_BIAS)
+    CNX_GEMM_CASE(EPI_BIAS_GELU)
+    CNX_GEMM_CASE(EPI_BIAS_RESIDUAL)
+    CNX_GEMM_CASE(EPI_GELU_GRAD)
+    case EPI_STORE_F32:  return launch2<BN, EPI_STORE_F32, PAIR, 8>(ma, mb, md0, md1, mr, p, grid, stream);
+    case EPI_ATOMIC_F32: return launch2<BN, EPI_ATOMIC_F32, PAIR, 8>(ma, mb, md0, md1, mr, p, grid, stream);
     default: break;
   }
+#undef CNX_GEMM_CASE
   set_last_error("gemm_bf16: unsupported epilogue %d", epi);
   return CNX_ERR_BAD_ARG;
 }
@@ -622,12 +832,12 @@ int gemm_debug_max_clusters(int cluster_size) {
   // how many clusters of `cluster_size` pair-kernel CTAs (full shared-memory footprint) the device
   // can hold at once: GPC fragmentation shows up here (development probe)
   using L = Cfg<256, true, true>;
-  auto kern = gemm2_kernel<256, EPI_STORE_BF16, true>;
+  auto kern = gemm2_kernel<256, EPI_STORE_BF16, true, 8>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
   if (cluster_size > 8) cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(sm_count() / cluster_size * cluster_size);
-  cfg.blockDim = dim3(kThreads);
+  cfg.blockDim = dim3(64 + 32 * 8);
   cfg.dynamicSmemBytes = L::kTotal;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -645,6 +855,8 @@ int gemm_debug_max_clusters(int cluster_size) {
 void gemm_debug_tuning(int stages, int pair, int bn, int splits) {
   g_tune.stages = stages; g_tune.pair = pair; g_tune.bn = bn; g_tune.splits = splits;
 }
+
+void gemm_debug_epilogue_warps(int n) { g_tune.epi_warps = (n == 8 || n == 16) ? n : 0; }
 
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   if (a.M <= 0 || a.N <= 0 || a.K <= 0 || (a.N % 8) != 0 || (a.lda % 8) != 0 || (a.ldb % 8) != 0) {
@@ -806,11 +1018,15 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
     if (rc != CNX_OK) return rc;
   }
 
+  // 16 epilogue warps where the epilogue, not the tensor pipe, sets the pace (GELU / GELU');
+  // cnx_debug_gemm_epilogue_warps() forces 8 or 16 for every bf16 epilogue (A/B measurements)
+  int ew = (epi == EPI_BIAS_GELU || epi == EPI_GELU_GRAD) ? 16 : 8;
+  if (g_tune.epi_warps != 0) ew = g_tune.epi_warps;
   if (pair)
-    return BN == 256 ? dispatch<256, true>(epi, ma, mb, md0, md1, mr, p, grid, stream)
-                     : dispatch<128, true>(epi, ma, mb, md0, md1, mr, p, grid, stream);
-  return BN == 256 ? dispatch<256, false>(epi, ma, mb, md0, md1, mr, p, grid, stream)
-                   : dispatch<128, false>(epi, ma, mb, md0, md1, mr, p, grid, stream);
+    return BN == 256 ? dispatch<256, true>(epi, ew, ma, mb, md0, md1, mr, p, grid, stream)
+                     : dispatch<128, true>(epi, ew, ma, mb, md0, md1, mr, p, grid, stream);
+  return BN == 256 ? dispatch<256, false>(epi, ew, ma, mb, md0, md1, mr, p, grid, stream)
+                   : dispatch<128, false>(epi, ew, ma, mb, md0, md1, mr, p, grid, stream);
 }
 
 }  // namespace cnx

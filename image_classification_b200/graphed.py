@@ -79,3 +79,108 @@ class GraphedForwardBackward:
         for p, g in zip(self.params, self.grads):
             p.grad = g
         return self.loss
+
+
+class GraphedTrainStep:
+    """`train_step.TrainStep` with forward + loss + backward of every micro-batch position of the
+    accumulation window replayed as ONE CUDA graph each (the reference loop,
+    /root/reference/train_advanced_v4.py:215-237, accumulates 2 micro-batches: two graphs).
+
+    The ConvNeXt micro-step is ~500 library launches enqueued from Python in ~12 ms; at BASELINE
+    config 2's micro-batch of 128 the GPU needs 22 ms for them and the host stays ahead, at config
+    3's 8-GPU share (micro-batch 64) it does not.  Everything between "the mixed batch is in HBM"
+    and "the gradients are in .grad" is stream-ordered library / torch work with no host sync, so
+    it is recorded once per window position and replayed:
+
+      graph 0      zero the GradWindow accumulators, fold the block weights (from the CURRENT
+                   parameters: the fold kernels are inside the graph), forward, soft-target CE,
+                   scaled backward; block gradients stay in the window's accumulators
+      graph k      same without the fold (reads graph 0's folded tensors), accumulating
+      graph N-1    ... and the fold adjoint emits every parameter gradient; with a
+                   ddp.BucketedGradReducer the bucket all-reduces issued from its gradient hooks
+                   (NCCL) and their join are part of this graph
+    The optimizer section (fused unscale + clip + AdamW + EMA, scheduler) stays outside: two
+    launches, learning rate free to change.  The graphs share one memory pool (replayed in capture
+    order, so activations of graph k are recycled by graph k+1).
+
+    Contract: fixed batch shape; `micro_step(images, targets, batch_idx)` copies its arguments
+    into the static input buffers unless they already ARE those buffers (`self.images`,
+    `self.targets` — e.g. hand them to `mix.BatchMixUpCutMix(..., out=, targets_out=)`); windows
+    always start at position 0 (an odd trailing micro-batch is dropped at the next window start,
+    unlike the eager `TrainStep`, which carries it over like the reference does)."""
+
+    def __init__(self, step, images_shape, targets_shape, device, warmup_windows: int = 2):
+        from . import block as block_mod
+        self.step = step
+        self.N = step.cfg.gradient_accumulation_steps
+        self.device = torch.device(device)
+        self.images = torch.zeros(images_shape, device=self.device, dtype=torch.float32)
+        self.targets = torch.full(targets_shape, 1.0 / targets_shape[-1], device=self.device,
+                                  dtype=torch.float32)
+        self.params = step.params
+        if step.window is not None:
+            step.window.end()
+        cur = torch.cuda.current_stream(self.device)
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            # eager windows: lazy initialisation, and the reducer's unused-parameter discovery
+            for _ in range(warmup_windows):
+                for p in self.params:
+                    p.grad = None
+                for k in range(self.N):
+                    step.forward_backward(self.images, self.targets, k)
+                if step.grad_reducer is not None:
+                    step.grad_reducer.finish()
+                if step.window is not None:
+                    step.window.end()
+        cur.wait_stream(side)
+        torch.cuda.synchronize(self.device)
+        for p in self.params:
+            p.grad = None
+        from . import _lib
+        pool = torch.cuda.graph_pool_handle()
+        self.graphs, self.losses, self.launches = [], [], []
+        try:
+            for k in range(self.N):
+                block_mod.capture_reuses_fold = k > 0
+                g = torch.cuda.CUDAGraph()
+                n0 = _lib.launch_count
+                with torch.cuda.graph(g, pool=pool):
+                    loss = step.forward_backward(self.images, self.targets, k)
+                    if k == self.N - 1 and step.grad_reducer is not None:
+                        step.grad_reducer.finish()
+                self.graphs.append(g)
+                self.losses.append(loss)
+                self.launches.append(_lib.launch_count - n0)    # library kernels inside graph k
+        finally:
+            block_mod.capture_reuses_fold = False
+        if step.window is not None:
+            step.window.end()
+        self.grads = [p.grad for p in self.params]          # static buffers in the graphs' pool
+        for p in self.params:
+            p.grad = None
+
+    def micro_step(self, images: torch.Tensor, targets: torch.Tensor, batch_idx: int) -> torch.Tensor:
+        k = batch_idx % self.N
+        if images.shape != self.images.shape or targets.shape != self.targets.shape:
+            raise RuntimeError(f"GraphedTrainStep was captured for {tuple(self.images.shape)} / "
+                               f"{tuple(self.targets.shape)}, got {tuple(images.shape)} / "
+                               f"{tuple(targets.shape)}")
+        if images.data_ptr() != self.images.data_ptr():
+            self.images.copy_(images, non_blocking=True)
+        if targets.data_ptr() != self.targets.data_ptr():
+            self.targets.copy_(targets, non_blocking=True)
+        self.graphs[k].replay()
+        from . import _lib
+        _lib.launch_count += self.launches[k]        # the replay launched the recorded kernels
+        if k == self.N - 1:
+            for p, g in zip(self.params, self.grads):
+                p.grad = g
+            if self.step.grad_reducer is not None:
+                self.step.grad_reducer.reduced_steps += 1      # joined inside the graph
+            self.step.optimizer_section(reduce_grads=False)
+        return self.losses[k]
+
+    def close(self) -> None:
+        self.step.close()

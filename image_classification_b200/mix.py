@@ -67,10 +67,12 @@ def plan_mix_batch(batch_size: int, height: int, width: int, *, mixup_alpha: flo
 
 
 def mix_batch(images: torch.Tensor, labels: torch.Tensor, plan: np.ndarray, num_classes: int,
-              on_value: float = 1.0, off_value: float = 0.0):
+              on_value: float = 1.0, off_value: float = 0.0, out: torch.Tensor | None = None,
+              targets_out: torch.Tensor | None = None):
     """Apply `plan` on the device: images [B,CH,H,W] fp32 (NCHW), labels [B] int64 ->
     (mixed images, soft targets [B,num_classes] fp32).  on/off: values of the (smoothed) one-hot
-    rows that are blended (1/0 = the reference's plain one-hot)."""
+    rows that are blended (1/0 = the reference's plain one-hot).  out / targets_out: existing
+    result buffers (the static inputs of a CUDA-graph step, graphed.GraphedTrainStep)."""
     if not images.is_cuda:
         raise _lib.CnxError("mix_batch: images must be a CUDA tensor (no CPU path)")
     if images.dtype != torch.float32 or not images.is_contiguous():
@@ -81,8 +83,19 @@ def mix_batch(images: torch.Tensor, labels: torch.Tensor, plan: np.ndarray, num_
     labels = labels.to(device=images.device, dtype=torch.int64).contiguous()
     plan_dev = torch.from_numpy(plan.view(np.uint8).reshape(-1).copy()).to(images.device,
                                                                             non_blocking=True)
-    out = torch.empty_like(images)
-    targets = torch.empty(B, num_classes, device=images.device, dtype=torch.float32)
+    if out is None:
+        out = torch.empty_like(images)
+    elif (out.shape != images.shape or out.dtype != torch.float32 or not out.is_contiguous()
+          or out.device != images.device or out.data_ptr() == images.data_ptr()):
+        raise _lib.CnxError("mix_batch: `out` must be a distinct contiguous float32 tensor shaped "
+                            "like the images")
+    if targets_out is None:
+        targets = torch.empty(B, num_classes, device=images.device, dtype=torch.float32)
+    else:
+        targets = targets_out
+        if (tuple(targets.shape) != (B, num_classes) or targets.dtype != torch.float32
+                or not targets.is_contiguous() or targets.device != images.device):
+            raise _lib.CnxError(f"mix_batch: `targets_out` must be contiguous float32 [{B}, {num_classes}]")
     stream = torch.cuda.current_stream(images.device).cuda_stream
     if on_value == 1.0 and off_value == 0.0:
         _lib.call("cnx_mix_batch", images.data_ptr(), labels.data_ptr(), plan_dev.data_ptr(),
@@ -103,11 +116,12 @@ class BatchMixUpCutMix:
     prob: float = 0.5
     num_classes: int | None = None
 
-    def __call__(self, images: torch.Tensor, labels: torch.Tensor, rng=None):
+    def __call__(self, images: torch.Tensor, labels: torch.Tensor, rng=None, out=None,
+                 targets_out=None):
         B, _, H, W = images.shape
         plan = plan_mix_batch(B, H, W, mixup_alpha=self.mixup_alpha, cutmix_alpha=self.cutmix_alpha,
                               prob=self.prob, rng=rng)
-        return mix_batch(images, labels, plan, self.num_classes)
+        return mix_batch(images, labels, plan, self.num_classes, out=out, targets_out=targets_out)
 
 
 def plan_timm_batch_mixup(batch_size: int, height: int, width: int, *, mixup_alpha: float = 1.0,

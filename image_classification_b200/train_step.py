@@ -78,6 +78,14 @@ class TrainStep:
             self.window = w if w.blocks else None
 
     def micro_step(self, images: torch.Tensor, labels: torch.Tensor, batch_idx: int) -> torch.Tensor:
+        boundary = (batch_idx + 1) % self.cfg.gradient_accumulation_steps == 0     # :225
+        loss = self.forward_backward(images, labels, batch_idx)
+        if boundary:
+            self.optimizer_section()
+        return loss
+
+    def forward_backward(self, images: torch.Tensor, labels: torch.Tensor, batch_idx: int) -> torch.Tensor:
+        """:215-223 / :238-245 — forward, criterion, (scaled) backward of one micro-batch."""
         cfg = self.cfg
         boundary = (batch_idx + 1) % cfg.gradient_accumulation_steps == 0     # :225
         if self.grad_reducer is not None:
@@ -93,48 +101,40 @@ class TrainStep:
                     outputs = outputs[0]                                       # :219-220
                 loss = self.criterion(outputs, labels)                         # :221
             self.scaler.scale(loss).backward()                                 # :223 (no /accum)
-            if boundary:
-                if self.grad_reducer is not None:
-                    self.grad_reducer.finish()
-                if self.fused is not None:
-                    self.fused.step()                                          # :226-230, :236-237
-                else:
-                    self.scaler.unscale_(self.optimizer)                       # :226
-                    if cfg.gradient_clip_val > 0:
-                        torch.nn.utils.clip_grad_norm_(self.params, cfg.gradient_clip_val)   # :228
-                    self.scaler.step(self.optimizer)                           # :229
-                    self.scaler.update()                                       # :230
-                self.optimizer.zero_grad()                                     # :231
-                if self.scheduler is not None:
-                    self.scheduler.step()                                      # :233-234
-                if self.ema is not None and self.fused is None:
-                    self.ema.update()                                          # :236-237
-                if self.window is not None:
-                    self.window.end()
         else:
-            outputs = self.model(images)
+            outputs = self.model(images)                                       # :240
             if isinstance(outputs, (list, tuple)):
-                outputs = outputs[0]
-            loss = self.criterion(outputs, labels)
+                outputs = outputs[0]                                           # :241-242
+            loss = self.criterion(outputs, labels)                             # :243
             loss = loss / cfg.gradient_accumulation_steps                      # :244
-            loss.backward()
-            if boundary:
-                if self.grad_reducer is not None:
-                    self.grad_reducer.finish()
-                if self.fused is not None:
-                    self.fused.step()
-                else:
-                    if cfg.gradient_clip_val > 0:
-                        torch.nn.utils.clip_grad_norm_(self.params, cfg.gradient_clip_val)
-                    self.optimizer.step()
-                self.optimizer.zero_grad()
-                if self.scheduler is not None:
-                    self.scheduler.step()
-                if self.ema is not None and self.fused is None:
-                    self.ema.update()
-                if self.window is not None:
-                    self.window.end()
+            loss.backward()                                                    # :245
         return loss.detach()
+
+    def optimizer_section(self, reduce_grads: bool = True) -> None:
+        """:226-237 / :248-257 — what runs on the boundary micro-batch after backward.
+        reduce_grads=False: the data-parallel exchange already ran (inside a replayed graph)."""
+        cfg = self.cfg
+        if reduce_grads and self.grad_reducer is not None:
+            self.grad_reducer.finish()
+        if self.fused is not None:
+            self.fused.step()                                                  # :226-230, :236-237
+        elif self.scaler is not None:
+            self.scaler.unscale_(self.optimizer)                               # :226
+            if cfg.gradient_clip_val > 0:
+                torch.nn.utils.clip_grad_norm_(self.params, cfg.gradient_clip_val)   # :228
+            self.scaler.step(self.optimizer)                                   # :229
+            self.scaler.update()                                               # :230
+        else:
+            if cfg.gradient_clip_val > 0:
+                torch.nn.utils.clip_grad_norm_(self.params, cfg.gradient_clip_val)   # :249
+            self.optimizer.step()                                              # :250
+        self.optimizer.zero_grad()                                             # :231 / :251
+        if self.scheduler is not None:
+            self.scheduler.step()                                              # :233-234
+        if self.ema is not None and self.fused is None:
+            self.ema.update()                                                  # :236-237
+        if self.window is not None:
+            self.window.end()
 
     def close(self) -> None:
         """End of the loop: gradients of an odd trailing micro-batch still held by the

@@ -81,6 +81,9 @@ void cnx_debug_set_timeout_flag(int value);
  * compiled depth); pair: 0/1 CTA-pair kernel; bn: 128/256 column tile; splits: split-K count of the
  * fp32 reduction epilogue. */
 void cnx_debug_gemm_tuning(int stages, int pair, int bn, int splits);
+/* Debug / tuning: epilogue warps of the bf16-output GEMM kernels for the following calls: 8, 16, or
+ * 0 = automatic (16 for the GELU / GELU-gradient epilogues, 8 otherwise). */
+void cnx_debug_gemm_epilogue_warps(int n);
 /* Debug: clusters of `cluster_size` GEMM CTAs the device can hold at once (occupancy probe). */
 int cnx_debug_max_clusters(int cluster_size);
 /* Scratch bytes an op needs for the given problem (B*H*W*C*2 for CNX_OP_DWCONV_LN_BWD, else 0). */

@@ -147,11 +147,13 @@ def test_gemm_epilogues(cnx_lib):
     assert _rel(colsum, dz.double().sum(0)) < 1e-4      # sums of the rounded dz
 
 
+@pytest.mark.parametrize("epi_warps", [8, 16])
 @pytest.mark.parametrize("tuning", [(2, 0, 256, -1), (-1, 0, 128, -1), (-1, 1, 256, -1), (3, 1, 128, 3),
                                     (2, 1, 256, 5)])
-def test_gemm_forced_tilings(cnx_lib, tuning):
+def test_gemm_forced_tilings(cnx_lib, tuning, epi_warps):
     """Every kernel instantiation (single CTA / CTA pair, 128- and 256-wide tiles, shallow operand
-    ring, forced split-K) gives the same results: ragged M, N and K, several tiles per CTA."""
+    ring, forced split-K, 8 or 16 epilogue warps) gives the same results: ragged M, N and K,
+    several tiles per CTA."""
     from image_classification_b200 import ops, _lib
     dev = _dev()
     torch.manual_seed(11)
@@ -163,6 +165,7 @@ def test_gemm_forced_tilings(cnx_lib, tuning):
     acc = A.double() @ Bm.double().t()
     lib = _lib.load()
     lib.cnx_debug_gemm_tuning(*tuning)
+    lib.cnx_debug_gemm_epilogue_warps(epi_warps)
     try:
         D = ops.gemm_bf16(A, Bm)
         z, h = ops.gemm_bf16(A, Bm, epilogue=ops.EPI_BIAS_GELU, bias=bias)
@@ -175,6 +178,7 @@ def test_gemm_forced_tilings(cnx_lib, tuning):
         torch.cuda.synchronize()
     finally:
         lib.cnx_debug_gemm_tuning(-1, -1, -1, -1)
+        lib.cnx_debug_gemm_epilogue_warps(0)
     assert lib.cnx_debug_timeout_flag() == 0
     assert _rel(D, acc) < BF16_REL
     assert _rel(z, acc + bias.double()) < BF16_REL

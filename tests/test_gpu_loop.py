@@ -168,3 +168,59 @@ def test_mbarrier_timeout_is_sticky_until_cleared(cnx_lib):
     assert lib.cnx_debug_timeout_flag() == 0
     ops.colsum_bf16(x)
     torch.cuda.synchronize()
+
+
+def test_graphed_train_step_matches_eager(cnx_lib):
+    """graphed.GraphedTrainStep (two CUDA graphs per accumulate-2 window, weight fold recorded in
+    the first, fold adjoint in the second) against the eager TrainStep on identical models and
+    data: gradients of the window, then losses / parameters / EMA over further optimizer steps —
+    which also shows that a replay folds the UPDATED weights."""
+    import copy
+    from image_classification_b200 import ema as ema_mod, loss as loss_mod, train_step
+    from image_classification_b200.convnext import ConvNeXtTimmLike, DeepSupervisionModelB200
+    from image_classification_b200.graphed import GraphedTrainStep
+    dev = _dev()
+    torch.manual_seed(5)
+    base = DeepSupervisionModelB200(ConvNeXtTimmLike((1, 1, 2, 1), (64, 128, 256, 512), 44), 44).to(dev)
+    with torch.no_grad():
+        for n, p in base.named_parameters():
+            if n.endswith("gamma"):
+                p.copy_(torch.rand_like(p) * 0.9 + 0.1)
+    models = [base, copy.deepcopy(base)]
+    g = torch.Generator().manual_seed(9)
+    xs = [torch.randn(4, 3, 64, 64, generator=g).to(dev) for _ in range(6)]
+    ts = [torch.softmax(torch.randn(4, 44, generator=g) * 2, 1).to(dev) for _ in range(6)]
+    steps = []
+    for m in models:
+        m.train()
+        opt = torch.optim.AdamW(m.parameters(), lr=1e-3, weight_decay=1e-2)
+        steps.append(train_step.TrainStep(m, loss_mod.SoftTargetCrossEntropyB200(0.1), opt, None,
+                                          torch.amp.GradScaler("cuda"), ema_mod.EMAB200(m, 0.99),
+                                          train_step.StepConfig(2, 1.0, 44)))
+    eager, gts = steps[0], GraphedTrainStep(steps[1], (4, 3, 64, 64), (4, 44), dev)
+    assert len(gts.graphs) == 2 and gts.launches[0] > gts.launches[1] - 20 and gts.launches[0] > 30
+    # 1) gradients of one window, before any optimizer step
+    for k in range(2):
+        eager.forward_backward(xs[k], ts[k], k)
+        gts.images.copy_(xs[k]); gts.targets.copy_(ts[k])
+        gts.graphs[k].replay()
+    for (n, p), gg in zip(models[0].named_parameters(), gts.grads):
+        if p.grad is None:
+            assert gg is None, n
+            continue
+        s = float(p.grad.abs().max().clamp_min(1e-30))
+        assert float((p.grad - gg).abs().max()) / s < 1e-3, n        # atomics order only
+    eager.optimizer_section()
+    for p, gg in zip(gts.params, gts.grads):
+        p.grad = gg
+    gts.step.optimizer_section(reduce_grads=False)
+    # 2) two more optimizer steps through the public calls
+    for i in range(2, 6):
+        le = eager.micro_step(xs[i], ts[i], i)
+        lg = gts.micro_step(xs[i], ts[i], i)
+        assert abs(float(le) - float(lg)) < 2e-3 * abs(float(le)), (i, float(le), float(lg))
+    for (n, p), (_, q) in zip(models[0].named_parameters(), models[1].named_parameters()):
+        assert float((p - q).abs().max()) < 5e-3 * float(p.abs().max().clamp_min(1e-3)) + 2e-3, n
+    for k in steps[0].ema.shadow:
+        assert torch.allclose(steps[0].ema.shadow[k], steps[1].ema.shadow[k], rtol=1e-2, atol=2e-3), k
+    gts.close()

@@ -40,7 +40,11 @@ def main():
     ap.add_argument("--res", type=int, default=224)
     ap.add_argument("--stages", type=str, default="0,1,2,3")
     ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--epi-warps", type=int, default=0, help="force 8 / 16 GEMM epilogue warps")
+    ap.add_argument("--out", type=str, default="gpurun_out/microbench.json")
     args = ap.parse_args()
+    from image_classification_b200 import _lib
+    _lib.load().cnx_debug_gemm_epilogue_warps(args.epi_warps)
     dev = torch.device("cuda:0")
     dims = (128, 256, 512, 1024)
     flush = None if args.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -101,7 +105,7 @@ def main():
         del x, xhat, z, h, dz, dxhat, dy
         torch.cuda.empty_cache()
     os.makedirs("gpurun_out", exist_ok=True)
-    with open("gpurun_out/microbench.json", "w") as f:
+    with open(args.out, "w") as f:
         json.dump(rows, f, indent=1)
 
 
