@@ -277,7 +277,9 @@ class B200Trainer:
         self.mixer = mix.BatchMixUpCutMix(0.2, 1.0, 0.5, NUM_CLASSES)   # config.py:16-17, :593-599
         self.rng = np.random.RandomState(1234 + rank)
         # the reducer finds the never-used auxiliary heads on its first synchronised backward
-        self.reducer = ddp.BucketedGradReducer(self.params) if world > 1 else None
+        bucket_mb = int(os.environ.get("CNX_BUCKET_MB", "32"))       # A/B switch
+        self.reducer = (ddp.BucketedGradReducer(self.params, bucket_bytes=bucket_mb << 20)
+                        if world > 1 else None)
         cfg = train_step.StepConfig(gradient_accumulation_steps=ACCUM, gradient_clip_val=1.0,
                                     num_classes=NUM_CLASSES)
         # CNX_NO_FUSED_OPTIM=1: torch's unscale_/clip/AdamW/update + EMAB200.update (A/B switch)

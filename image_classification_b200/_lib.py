@@ -12,7 +12,8 @@ import os
 from ctypes import POINTER, c_char_p, c_float, c_int, c_int32, c_int64, c_size_t, c_void_p
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libcnx_b200.so")
+# CNX_LIB_PATH: load another build of the library (same-box A/B of two kernel versions)
+LIB_PATH = os.environ.get("CNX_LIB_PATH") or os.path.join(HERE, "libcnx_b200.so")
 
 
 class CnxError(RuntimeError):

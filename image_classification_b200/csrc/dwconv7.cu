@@ -27,8 +27,11 @@
 // is reported, not counted.
 #include "cnx_common.cuh"
 #include "cnx_kernels.h"
+#include <stdlib.h>
 
 namespace cnx {
+
+bool dwconv_ln_fwd_is_fused(int C);
 
 // ln_rows.cu
 int ln_rows_fwd(void* u_inout, float* mean, float* rstd, int64_t M, int C, float eps,
@@ -55,6 +58,9 @@ struct ConvParams {
   float* dwt;                  // [49][C]  (+=)
   float* dbias;                // [C]      (+=)
   float* dy_colsum;            // [C]      (+=)
+  float* mean;                 // fused LayerNorm (forward, C <= 128): [B*H*W]
+  float* rstd;
+  float eps;
   int B, H, W, C;
   int nslab, tiles_w, tiles_h, nitems;
 };
@@ -75,8 +81,31 @@ __device__ __forceinline__ Item decode_item(const ConvParams& p, int item, int T
   return it;
 }
 
+__device__ __forceinline__ void group_sync(int pg) {
+  asm volatile("bar.sync %0, 64;" ::"r"(1 + pg) : "memory");
+}
+
+// Sum of 16 per-lane values over the 32 lanes of a warp by halving: 16 shuffles instead of 80.
+// On return v[0] holds, on lanes 2k and 2k+1, the warp total of value index k.
+__device__ __forceinline__ void warp_reduce16(float (&v)[16], int lane) {
+#pragma unroll
+  for (int step = 0; step < 4; ++step) {
+    const int n = 8 >> step;                 // values kept after this step
+    const bool hi = (lane >> (4 - step)) & 1;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (i < n) {
+        const float keep = hi ? v[n + i] : v[i];
+        const float send = hi ? v[i] : v[n + i];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16 >> step);
+      }
+    }
+  }
+  v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+}
+
 // ------------------------------------------------------------------------------ forward
-template <int TW>
+template <int TW, bool FUSE_LN>
 __global__ void __launch_bounds__(kThreads, 1)
 dwconv7_fwd_kernel(const __grid_constant__ CUtensorMap x_map, const ConvParams p) {
   constexpr int WT = TW + 6, HT = kTH + 6;
@@ -85,15 +114,21 @@ dwconv7_fwd_kernel(const __grid_constant__ CUtensorMap x_map, const ConvParams p
   extern __shared__ __align__(128) unsigned char smem_dyn[];
   unsigned char* smem_raw = align128(smem_dyn);
   __shared__ __align__(8) uint64_t full_bar[2];
+  __shared__ float2 s_sum[kGroups][16];      // FUSE_LN: per pixel (warp 0, warp 1) partial sums
+  __shared__ float2 s_sq[kGroups][16];
 
   const int tid = threadIdx.x;
   const int pg = tid >> 6;
   const int cp = tid & 63;
+  const int lane = tid & 31;
+  const int wg = (tid >> 5) & 1;             // warp inside the pixel group
   const int slab = blockIdx.x % p.nslab;
   const int worker = blockIdx.x / p.nslab;
   const int nworkers = gridDim.x / p.nslab;
   const int c0 = slab * kSlab;
   const bool ch_active = (c0 + 2 * cp) < p.C;
+  const float inv_c = 1.0f / static_cast<float>(p.C);
+  const size_t pstride = static_cast<size_t>(p.C >> 1);
 
   if (tid == 0) {
     tma_prefetch_desc(&x_map);
@@ -166,7 +201,62 @@ dwconv7_fwd_kernel(const __grid_constant__ CUtensorMap x_map, const ConvParams p
           }
         }
       }
-      if (ch_active) {
+      if (FUSE_LN) {
+        // ---- channels-last LayerNorm of the 14 pixels of this micro-tile, all C (<= 128) channels
+        // of which live in the 64 lanes of this pixel group.  Statistics of the bf16-ROUNDED conv
+        // output (the reference's autocast hands LayerNorm a half-precision tensor), two-pass.
+        float2 u[MH][MW];
+        float red[16];
+#pragma unroll
+        for (int o = 0; o < MH; ++o)
+#pragma unroll
+          for (int j = 0; j < MW; ++j) {
+            u[o][j] = ch_active ? bf16x2_to_f32x2(f32x2_to_bf16x2(acc[o][j].x, acc[o][j].y))
+                                : make_float2(0.f, 0.f);
+            red[o * MW + j] = u[o][j].x + u[o][j].y;
+          }
+        red[14] = 0.f; red[15] = 0.f;
+        warp_reduce16(red, lane);
+        if ((lane & 1) == 0) reinterpret_cast<float*>(&s_sum[pg][lane >> 1])[wg] = red[0];
+        group_sync(pg);
+        float mean[MH * MW];
+#pragma unroll
+        for (int i = 0; i < MH * MW; ++i) {
+          const float2 t = s_sum[pg][i];
+          mean[i] = (t.x + t.y) * inv_c;
+        }
+#pragma unroll
+        for (int o = 0; o < MH; ++o)
+#pragma unroll
+          for (int j = 0; j < MW; ++j) {
+            const float m = mean[o * MW + j];
+            u[o][j].x -= m;
+            u[o][j].y -= m;
+            red[o * MW + j] = ch_active ? fmaf(u[o][j].x, u[o][j].x, u[o][j].y * u[o][j].y) : 0.f;
+          }
+        red[14] = 0.f; red[15] = 0.f;
+        warp_reduce16(red, lane);
+        if ((lane & 1) == 0) reinterpret_cast<float*>(&s_sq[pg][lane >> 1])[wg] = red[0];
+        group_sync(pg);
+#pragma unroll
+        for (int o = 0; o < MH; ++o) {
+          const int hh = ti.h0 + oy + o;
+          const size_t prow = (static_cast<size_t>(ti.n) * p.H + hh) * p.W + ti.w0 + ox;
+          uint32_t* dst = reinterpret_cast<uint32_t*>(p.out + prow * p.C + c0) + cp;
+#pragma unroll
+          for (int j = 0; j < MW; ++j) {
+            const float2 t = s_sq[pg][o * MW + j];
+            const float rs = rsqrtf((t.x + t.y) * inv_c + p.eps);
+            if (hh < p.H && ox + j < cols_valid) {
+              if (ch_active) dst[j * pstride] = f32x2_to_bf16x2(u[o][j].x * rs, u[o][j].y * rs);
+              if (cp == o * MW + j) {          // one lane per pixel records the statistics
+                p.mean[prow + j] = mean[o * MW + j];
+                p.rstd[prow + j] = rs;
+              }
+            }
+          }
+        }
+      } else if (ch_active) {
 #pragma unroll
         for (int o = 0; o < MH; ++o) {
           const int hh = ti.h0 + oy + o;
@@ -174,7 +264,6 @@ dwconv7_fwd_kernel(const __grid_constant__ CUtensorMap x_map, const ConvParams p
             uint32_t* dst = reinterpret_cast<uint32_t*>(
                                 p.out + ((static_cast<size_t>(ti.n) * p.H + hh) * p.W + ti.w0 + ox) *
                                             p.C + c0) + cp;
-            const size_t pstride = static_cast<size_t>(p.C >> 1);
 #pragma unroll
             for (int j = 0; j < MW; ++j)
               if (ox + j < cols_valid) dst[j * pstride] = f32x2_to_bf16x2(acc[o][j].x, acc[o][j].y);
@@ -401,16 +490,17 @@ int make_nhwc_map(CUtensorMap* map, const void* base, int B, int H, int W, int C
   return make_tensor_map(map, base, 2, 4, dims, strides, box, 0);
 }
 
-template <int TW>
+template <int TW, bool FUSE_LN>
 int launch_fwd(const void* x, ConvParams& p, int B, int H, int W, int C, cudaStream_t stream) {
   fill_geometry(p, B, H, W, C, TW);
   CUtensorMap map;
   int rc = make_nhwc_map(&map, x, B, H, W, C, TW + 6, kTH + 6);
   if (rc != CNX_OK) return rc;
   const size_t smem = 2ull * (kTH + 6) * (TW + 6) * kWords * 4 + 128;
-  rc = ensure_dyn_smem(dwconv7_fwd_kernel<TW>, smem, "dwconv7_fwd");
+  rc = ensure_dyn_smem(dwconv7_fwd_kernel<TW, FUSE_LN>, smem, "dwconv7_fwd");
   if (rc != CNX_OK) return rc;
-  cudaError_t e = launch_pdl(dwconv7_fwd_kernel<TW>, grid_size(p), kThreads, smem, stream, 1u, map, p);
+  cudaError_t e = launch_pdl(dwconv7_fwd_kernel<TW, FUSE_LN>, grid_size(p), kThreads, smem, stream,
+                             1u, map, p);
   if (e != cudaSuccess) {
     set_last_error("dwconv7_fwd launch: %s", cudaGetErrorString(e));
     return CNX_ERR_LAUNCH;
@@ -453,11 +543,26 @@ int dwconv_ln_fwd(const void* x, const float* wt, const float* bias, void* xhat,
   }
   p.wt = wt;
   p.bias = bias;
-  p.out = static_cast<__nv_bfloat16*>(xhat);     // conv output u lands in the xhat buffer ...
-  rc = (W > 7) ? launch_fwd<14>(x, p, B, H, W, C, stream) : launch_fwd<7>(x, p, B, H, W, C, stream);
+  p.out = static_cast<__nv_bfloat16*>(xhat);
+  p.mean = mean; p.rstd = rstd; p.eps = eps;
+  if (dwconv_ln_fwd_is_fused(C)) {
+    // one slab holds every channel of a pixel: LayerNorm happens in the conv kernel's epilogue
+    return (W > 7) ? launch_fwd<14, true>(x, p, B, H, W, C, stream)
+                   : launch_fwd<7, true>(x, p, B, H, W, C, stream);
+  }
+  // wider maps: the conv output u lands in the xhat buffer ...
+  rc = (W > 7) ? launch_fwd<14, false>(x, p, B, H, W, C, stream)
+               : launch_fwd<7, false>(x, p, B, H, W, C, stream);
   if (rc != CNX_OK) return rc;
-  // ... and is normalised in place, row by row
+  // ... and is normalised in place, row by row (L2-resident for every such stage)
   return ln_rows_fwd(xhat, mean, rstd, static_cast<int64_t>(B) * H * W, C, eps, stream);
+}
+
+// The fused kernel leaves DRAM traffic at the algorithmic 2*E*s but measured no faster than conv +
+// row kernel (stage 1, B=128: see DESIGN.md 3.1); CNX_DWCONV_NO_FUSE=1 selects the two-kernel path.
+bool dwconv_ln_fwd_is_fused(int C) {
+  static const bool no_fuse = getenv("CNX_DWCONV_NO_FUSE") != nullptr;
+  return C <= kSlab && !no_fuse;
 }
 
 size_t dwconv_ln_bwd_workspace_bytes(int B, int H, int W, int C) {

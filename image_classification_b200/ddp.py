@@ -65,7 +65,12 @@ class BucketedGradReducer:
         flat = torch.zeros(n, device=p0.device, dtype=p0.dtype)
         views, off = [], 0
         for p in plist:
-            views.append(flat[off:off + p.numel()].view_as(p))
+            # a view with the parameter's own (dense) memory order: channels_last conv weights keep
+            # gradients laid out like the parameter, which the fused optimizer step requires
+            dense = p.is_contiguous() or (p.dim() == 4 and
+                                          p.is_contiguous(memory_format=torch.channels_last))
+            chunk = flat[off:off + p.numel()]
+            views.append(chunk.as_strided(p.size(), p.stride()) if dense else chunk.view_as(p))
             off += p.numel()
         b = dict(params=list(plist), flat=flat, views=views, pending=len(plist))
         for p in plist:
@@ -115,7 +120,9 @@ class BucketedGradReducer:
                                "not be all-reduced (rebuild the reducer)")
 
     def _launch(self, b):
-        torch._foreach_copy_(b["views"], [p.grad for p in b["params"]])
+        src = [(v, p.grad) for v, p in zip(b["views"], b["params"]) if p.grad.data_ptr() != v.data_ptr()]
+        if src:
+            torch._foreach_copy_([v for v, _ in src], [g for _, g in src])
         h = dist.all_reduce(b["flat"], op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
         self._handles.append((h, b))
 
@@ -123,7 +130,8 @@ class BucketedGradReducer:
         """A bucket some of whose parameters hold no gradient: zeros stand in for them, so the
         collective keeps the same size on every rank."""
         b["flat"].zero_()
-        have = [(v, p.grad) for v, p in zip(b["views"], b["params"]) if p.grad is not None]
+        have = [(v, p.grad) for v, p in zip(b["views"], b["params"])
+                if p.grad is not None and p.grad.data_ptr() != v.data_ptr()]
         if have:
             torch._foreach_copy_([v for v, _ in have], [g for _, g in have])
         h = dist.all_reduce(b["flat"], op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
@@ -149,8 +157,12 @@ class BucketedGradReducer:
         for h, b in self._handles:
             h.wait()
             b["flat"].mul_(inv)
-            have = [(p.grad, v) for v, p in zip(b["views"], b["params"]) if p.grad is not None]
-            torch._foreach_copy_([g for g, _ in have], [v for _, v in have])
+            # no copy back: the parameter's .grad becomes the averaged slice of the bucket (the
+            # next backward allocates fresh gradients after zero_grad(set_to_none=True), or
+            # accumulates into the slice, which the next step's copy-in then finds in place)
+            for v, p in zip(b["views"], b["params"]):
+                if p.grad is not None:
+                    p.grad = v
         self._handles = []
         self.reduced_steps += 1
         if not self.discovered:

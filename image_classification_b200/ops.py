@@ -2,6 +2,7 @@
 allocator — the library owns no memory), current-stream plumbing.  Nothing here computes."""
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 
 import torch
@@ -95,6 +96,8 @@ def dwconv_ln_fwd(x_nhwc: torch.Tensor, wt_dw: torch.Tensor, bias: torch.Tensor,
     rstd = torch.empty_like(mean)
     _lib.call("cnx_dwconv_ln_fwd", _p(x_nhwc), _p(wt_dw), _p(bias), _p(xhat), _p(mean), _p(rstd),
               B, H, W, C, eps, _stream(x_nhwc))
+    if C <= 128 and not os.environ.get("CNX_DWCONV_NO_FUSE"):
+        _lib.launch_count -= 1      # one fused kernel (LayerNorm in the conv epilogue), not two
     return xhat, mean, rstd
 
 
