@@ -10,10 +10,29 @@ six backward); this file only routes tensors.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 from torch import nn
 
 from . import _lib, ops
+
+# Backward: the two weight-gradient GEMMs of a block depend only on tensors that exist once the dz
+# GEMM has run, and nothing downstream in the block needs their results — so they are enqueued on a
+# second stream and the data-gradient chain (dxhat GEMM -> LayerNorm-bwd -> conv-bwd) continues on
+# the main one; the streams join at the end of the block's backward.  Persistent kernels fill each
+# other's tails and the memory-bound row kernels run under the tensor-bound GEMMs.
+# CNX_BWD_SIDE_STREAM=0 keeps everything on one stream (A/B switch).
+_side_streams: dict = {}
+
+
+def _side_stream(device: torch.device):
+    if os.environ.get("CNX_BWD_SIDE_STREAM", "1") == "0":
+        return None
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    if key not in _side_streams:
+        _side_streams[key] = torch.cuda.Stream(device)
+    return _side_streams[key]
 
 
 # Bumped by every writer that changes parameter VALUES behind autograd's back (the fused optimizer
@@ -36,6 +55,31 @@ def notify_weights_changed() -> None:
     _weight_epoch += 1
 
 
+_fold_event = None          # recorded on the side stream by prefold_blocks(); consumed by the first block
+
+
+def prefold_blocks(blocks, device) -> None:
+    """Fold the weights of every block in `blocks` NOW, on the side stream, instead of one by one
+    as the forward pass reaches them: the ~36 small fold kernels then run under the stem (which
+    needs none of them).  The first block forward waits for the side stream.  Called by
+    `train_step.TrainStep` at the start of every accumulation window."""
+    global _fold_event, capture_reuses_fold
+    side = _side_stream(device)
+    if side is None or not blocks:
+        return
+    main = torch.cuda.current_stream(device)
+    side.wait_stream(main)
+    with torch.cuda.stream(side):
+        for b in blocks:
+            b._folded(b.conv_dw.weight, b.norm.weight, b.norm.bias, b.mlp.fc1.weight,
+                      b.mlp.fc1.bias, b.mlp.fc2.weight, b.mlp.fc2.bias, b.gamma)
+        ev = torch.cuda.Event()
+        ev.record(side)
+    _fold_event = ev
+    if torch.cuda.is_current_stream_capturing():
+        capture_reuses_fold = True      # the rest of this capture reads the tensors just recorded
+
+
 class _Mlp(nn.Module):
     """Parameter container named like timm's `Mlp` (fc1 / act / fc2)."""
 
@@ -54,6 +98,10 @@ class _BlockFn(torch.autograd.Function):
         B, C, H, W = x.shape
         x_nhwc = x.permute(0, 2, 3, 1)
         assert x_nhwc.is_contiguous() and x.dtype == torch.bfloat16
+        global _fold_event
+        if _fold_event is not None:          # folds enqueued on the side stream (prefold_blocks)
+            torch.cuda.current_stream(x.device).wait_event(_fold_event)
+            _fold_event = None
         fw = module._folded(conv_w, norm_w, norm_b, fc1_w, fc1_b, fc2_w, fc2_b, gamma)
         xhat, _mean, rstd = ops.dwconv_ln_fwd(x_nhwc, fw.wt_dw, conv_b.detach())
         M = B * H * W
@@ -77,12 +125,28 @@ class _BlockFn(torch.autograd.Function):
         win = ctx.module._window          # GradWindow slot of this block, or None
         a = win.acc if win is not None and win.owner.active else None
         dz, db1f = ops.mlp_bwd_dz(dy2d, fw.w2fT, z, None if a is None else a["db1f"])
-        dxhat = ops.mlp_bwd_dxhat(dz, fw.w1fT)
-        dw2f, dw1f = ops.mlp_bwd_wgrad(dy2d, h, dz, xhat.view(M, C),
-                                       None if a is None else (a["dw2f"], a["dw1f"]))
+        side = _side_stream(x.device)
+        if side is None:
+            dxhat = ops.mlp_bwd_dxhat(dz, fw.w1fT)
+            dw2f, dw1f = ops.mlp_bwd_wgrad(dy2d, h, dz, xhat.view(M, C),
+                                           None if a is None else (a["dw2f"], a["dw1f"]))
+        else:
+            # weight gradients on the side stream; their outputs are allocated here, on the main one
+            if a is None:
+                wacc = (torch.zeros(C, 4 * C, device=x.device, dtype=torch.float32),
+                        torch.zeros(4 * C, C, device=x.device, dtype=torch.float32))
+            else:
+                wacc = (a["dw2f"], a["dw1f"])
+            main = torch.cuda.current_stream(x.device)
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                dw2f, dw1f = ops.mlp_bwd_wgrad(dy2d, h, dz, xhat.view(M, C), wacc)
+            dxhat = ops.mlp_bwd_dxhat(dz, fw.w1fT)
         dx, dwt, dbias, db2f = ops.dwconv_ln_bwd(
             dxhat.view(B, H, W, C), xhat, rstd, x.permute(0, 2, 3, 1), dy_nhwc, fw.wt_dw,
             None if a is None else (a["dwt"], a["dbias"], a["db2f"]))
+        if side is not None:
+            torch.cuda.current_stream(x.device).wait_stream(side)
         if a is not None and not win.owner.boundary:
             # inside an accumulation window: the folded-parameter gradients stay in the window's
             # fp32 accumulators; parameter gradients are produced on the boundary micro-batch only

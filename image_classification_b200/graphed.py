@@ -143,7 +143,7 @@ class GraphedTrainStep:
         self.graphs, self.losses, self.launches = [], [], []
         try:
             for k in range(self.N):
-                block_mod.capture_reuses_fold = k > 0
+                block_mod.capture_reuses_fold = k > 0     # graph 0 folds (prefold_blocks), the others reuse
                 g = torch.cuda.CUDAGraph()
                 n0 = _lib.launch_count
                 with torch.cuda.graph(g, pool=pool):

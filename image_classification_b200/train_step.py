@@ -71,6 +71,8 @@ class TrainStep:
         if use_fused_optim:
             from .optim_step import FusedOptimStep
             self.fused = FusedOptimStep(model, optimizer, scaler, ema, self.cfg.gradient_clip_val)
+        from .block import ConvNeXtBlockB200
+        self.blocks = [m for m in model.modules() if isinstance(m, ConvNeXtBlockB200)]
         self.window = None
         if self.cfg.gradient_accumulation_steps > 1 and use_grad_window:
             from .block import GradWindow
@@ -94,6 +96,11 @@ class TrainStep:
             if batch_idx % cfg.gradient_accumulation_steps == 0:
                 self.window.begin()
             self.window.set_boundary(boundary)
+        if self.blocks and images.is_cuda and batch_idx % cfg.gradient_accumulation_steps == 0:
+            # the parameters only change in the optimizer section: fold every block's weights for
+            # this window now, on the side stream, under the stem
+            from .block import prefold_blocks
+            prefold_blocks(self.blocks, images.device)
         if self.scaler is not None:
             with torch.autocast("cuda", dtype=cfg.amp_dtype):                 # :217
                 outputs = self.model(images)                                   # :218
