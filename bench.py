@@ -420,6 +420,10 @@ def profile_kernels(trainer, device):
             ev.record()
             recs.append((name, open_ev.pop(name), ev, args))
 
+    # one stream for the instrumented step: with the weight-gradient GEMMs on the side stream two
+    # kernels share the SMs and an event pair would time both (block.py, CNX_BWD_SIDE_STREAM)
+    side_env = os.environ.get("CNX_BWD_SIDE_STREAM")
+    os.environ["CNX_BWD_SIDE_STREAM"] = "0"
     trainer.step_resident(eager=True)             # re-warm after the e2e loop (eager path)
     torch.cuda.synchronize(device)
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -431,6 +435,10 @@ def profile_kernels(trainer, device):
         torch.cuda.synchronize(device)
     finally:
         _lib.call_hook = None
+        if side_env is None:
+            del os.environ["CNX_BWD_SIDE_STREAM"]
+        else:
+            os.environ["CNX_BWD_SIDE_STREAM"] = side_env
     step_ms = s.elapsed_time(e)
     fam = {}
     for name, e0, e1, args in recs:

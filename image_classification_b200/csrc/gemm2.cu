@@ -1018,9 +1018,11 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
     if (rc != CNX_OK) return rc;
   }
 
-  // 16 epilogue warps where the epilogue, not the tensor pipe, sets the pace (GELU / GELU');
+  // 16 epilogue warps measured (profiles/r02_microbench_epi_warps_*.json): fc1+GELU 176 -> 170 us
+  // and 96 -> 94 us at K = 128 / 256 (stages 1-2, HBM-bound: more stores in flight), no change at
+  // K >= 512, GELU' (dz) 2 us SLOWER everywhere: so only the short-K fc1 uses them.
   // cnx_debug_gemm_epilogue_warps() forces 8 or 16 for every bf16 epilogue (A/B measurements)
-  int ew = (epi == EPI_BIAS_GELU || epi == EPI_GELU_GRAD) ? 16 : 8;
+  int ew = (epi == EPI_BIAS_GELU && a.K <= 256) ? 16 : 8;
   if (g_tune.epi_warps != 0) ew = g_tune.epi_warps;
   if (pair)
     return BN == 256 ? dispatch<256, true>(epi, ew, ma, mb, md0, md1, mr, p, grid, stream)
