@@ -80,6 +80,30 @@ def prefold_blocks(blocks, device) -> None:
         capture_reuses_fold = True      # the rest of this capture reads the tensors just recorded
 
 
+def _l2_sub_batches(B: int, H: int, W: int, C: int) -> int:
+    """L2 blocking over the batch — an experiment kept behind CNX_L2_CHUNK_MB (default 0 = off).
+
+    At the first two stages one `[M, 4C]` hidden tensor of a 128-image micro-batch (411 / 205 MB) is
+    several times the 126 MB L2, so every tensor a kernel of the block hands to the next one makes a
+    round trip through HBM.  Nothing in the block mixes samples (LayerNorm is per token), so the
+    block CAN run sub-batch by sub-batch through all its kernels, sized so that a sub-batch's hidden
+    tensor and what travels with it stay L2-resident between producer and consumer; in backward
+    `dz`, `dxhat` and `dconv` then live in chunk-sized buffers that are overwritten while still
+    dirty in L2.  Measured (same box, `tools/gpu_chunk_ab.sh`, profiles/r02_l2_chunk_ab.txt): with
+    ~50 MB chunks (8 sub-batches at stage 1, 4 at stage 2: +558 launches per step) the step takes
+    46.1 ms against 42.8 ms unchunked, with 28 MB chunks 49.7 ms — every launch costs its ~6 us of
+    prologue / tail whatever its size and the smaller GEMMs lose more to wave quantisation than the
+    L2 hits give back.  Off by default.  Returns the number of sub-batches (a divisor of B)."""
+    mb = float(os.environ.get("CNX_L2_CHUNK_MB", "0"))
+    hidden_mb = B * H * W * 4 * C * 2 / 1e6
+    if mb <= 0 or C > 256 or hidden_mb <= 2.0 * mb:
+        return 1
+    for d in range(2, B + 1):
+        if B % d == 0 and hidden_mb / d <= mb:
+            return d
+    return 1
+
+
 class _Mlp(nn.Module):
     """Parameter container named like timm's `Mlp` (fc1 / act / fc2)."""
 
@@ -88,6 +112,75 @@ class _Mlp(nn.Module):
         self.fc1 = nn.Linear(dim, hidden)
         self.act = nn.GELU()
         self.fc2 = nn.Linear(hidden, dim)
+
+
+def _forward_sub_batched(x_nhwc, fw, conv_b, nsub):
+    """The three forward kernels of a block, sub-batch by sub-batch (see _l2_sub_batches); full-size
+    outputs, every call works on a batch slice (contiguous in NHWC)."""
+    B, H, W, C = x_nhwc.shape
+    M, Bs = B * H * W, B // nsub
+    Ms = Bs * H * W
+    dev, bf16 = x_nhwc.device, torch.bfloat16
+    xhat = torch.empty_like(x_nhwc)
+    mean = torch.empty(M, device=dev, dtype=torch.float32)
+    rstd = torch.empty_like(mean)
+    z = torch.empty(M, 4 * C, device=dev, dtype=bf16)
+    h = torch.empty_like(z)
+    y = torch.empty(M, C, device=dev, dtype=bf16)
+    x2d, xh2d = x_nhwc.view(M, C), xhat.view(M, C)
+    st = torch.cuda.current_stream(dev).cuda_stream
+    fused = C <= 128 and not os.environ.get("CNX_DWCONV_NO_FUSE")
+    for i in range(nsub):
+        r0, r1 = i * Ms, (i + 1) * Ms
+        _lib.call("cnx_dwconv_ln_fwd", x2d[r0:r1].data_ptr(), fw.wt_dw.data_ptr(), conv_b.data_ptr(),
+                  xh2d[r0:r1].data_ptr(), mean[r0:r1].data_ptr(), rstd[r0:r1].data_ptr(),
+                  Bs, H, W, C, ops.LN_EPS, st)
+        if fused:
+            _lib.launch_count -= 1
+        _lib.call("cnx_fc1_gelu_fwd", xh2d[r0:r1].data_ptr(), fw.w1f.data_ptr(), fw.b1f.data_ptr(),
+                  z[r0:r1].data_ptr(), h[r0:r1].data_ptr(), Ms, C, st)
+        _lib.call("cnx_fc2_residual_fwd", h[r0:r1].data_ptr(), fw.w2f.data_ptr(), fw.b2f.data_ptr(),
+                  x2d[r0:r1].data_ptr(), y[r0:r1].data_ptr(), Ms, C, st)
+    return xhat, rstd, z, h, y
+
+
+def _backward_sub_batched(x_nhwc, xhat, rstd, z, h, dy_nhwc, fw, a, nsub):
+    """Backward of a block sub-batch by sub-batch: dz, dxhat and the LayerNorm-backward scratch live
+    in chunk-sized buffers that are rewritten while still dirty in L2 (they never reach HBM);
+    every parameter-gradient output accumulates (+=) over the sub-batches."""
+    B, H, W, C = x_nhwc.shape
+    M, Bs = B * H * W, B // nsub
+    Ms = Bs * H * W
+    dev, bf16, f32 = x_nhwc.device, torch.bfloat16, torch.float32
+    if a is None:
+        dw2f = torch.zeros(C, 4 * C, device=dev, dtype=f32)
+        dw1f = torch.zeros(4 * C, C, device=dev, dtype=f32)
+        db1f = torch.zeros(4 * C, device=dev, dtype=f32)
+        dwt = torch.zeros(49, C, device=dev, dtype=f32)
+        dbias = torch.zeros(C, device=dev, dtype=f32)
+        db2f = torch.zeros(C, device=dev, dtype=f32)
+    else:
+        dw2f, dw1f, db1f, dwt, dbias, db2f = (a["dw2f"], a["dw1f"], a["db1f"], a["dwt"], a["dbias"],
+                                              a["db2f"])
+    dx = torch.empty_like(x_nhwc)
+    dz_c = torch.empty(Ms, 4 * C, device=dev, dtype=bf16)
+    dxhat_c = torch.empty(Ms, C, device=dev, dtype=bf16)
+    ws_bytes = int(_lib.load().cnx_workspace_bytes(_lib.CNX_OP_DWCONV_LN_BWD, Bs, H, W, C))
+    ws = torch.empty(ws_bytes, device=dev, dtype=torch.uint8)
+    x2d, xh2d, dy2d, dx2d = x_nhwc.view(M, C), xhat.view(M, C), dy_nhwc.view(M, C), dx.view(M, C)
+    st = torch.cuda.current_stream(dev).cuda_stream
+    for i in range(nsub):
+        r0, r1 = i * Ms, (i + 1) * Ms
+        _lib.call("cnx_mlp_bwd_dz", dy2d[r0:r1].data_ptr(), fw.w2fT.data_ptr(), z[r0:r1].data_ptr(),
+                  dz_c.data_ptr(), db1f.data_ptr(), Ms, C, st)
+        _lib.call("cnx_mlp_bwd_dxhat", dz_c.data_ptr(), fw.w1fT.data_ptr(), dxhat_c.data_ptr(), Ms, C, st)
+        _lib.call("cnx_mlp_bwd_wgrad", dy2d[r0:r1].data_ptr(), h[r0:r1].data_ptr(), dz_c.data_ptr(),
+                  xh2d[r0:r1].data_ptr(), dw2f.data_ptr(), dw1f.data_ptr(), Ms, C, st)
+        _lib.call("cnx_dwconv_ln_bwd_acc", dxhat_c.data_ptr(), xh2d[r0:r1].data_ptr(),
+                  rstd[r0:r1].data_ptr(), x2d[r0:r1].data_ptr(), dy2d[r0:r1].data_ptr(),
+                  fw.wt_dw.data_ptr(), dx2d[r0:r1].data_ptr(), dwt.data_ptr(), dbias.data_ptr(),
+                  db2f.data_ptr(), Bs, H, W, C, ws.data_ptr(), ws_bytes, st)
+    return dx, dw2f, dw1f, db1f, dwt, dbias, db2f
 
 
 class _BlockFn(torch.autograd.Function):
@@ -103,10 +196,15 @@ class _BlockFn(torch.autograd.Function):
             torch.cuda.current_stream(x.device).wait_event(_fold_event)
             _fold_event = None
         fw = module._folded(conv_w, norm_w, norm_b, fc1_w, fc1_b, fc2_w, fc2_b, gamma)
-        xhat, _mean, rstd = ops.dwconv_ln_fwd(x_nhwc, fw.wt_dw, conv_b.detach())
         M = B * H * W
-        z, h = ops.fc1_gelu_fwd(xhat.view(M, C), fw.w1f, fw.b1f)
-        y = ops.fc2_residual_fwd(h, fw.w2f, fw.b2f, x_nhwc.reshape(M, C))
+        nsub = _l2_sub_batches(B, H, W, C)
+        if nsub == 1:
+            xhat, _mean, rstd = ops.dwconv_ln_fwd(x_nhwc, fw.wt_dw, conv_b.detach())
+            z, h = ops.fc1_gelu_fwd(xhat.view(M, C), fw.w1f, fw.b1f)
+            y = ops.fc2_residual_fwd(h, fw.w2f, fw.b2f, x_nhwc.reshape(M, C))
+        else:
+            xhat, rstd, z, h, y = _forward_sub_batched(x_nhwc, fw, conv_b.detach(), nsub)
+        ctx.nsub = nsub
         ctx.save_for_backward(x, xhat, rstd, z, h, norm_w, norm_b, fc1_w, fc2_w, fc2_b, gamma)
         ctx.fw = fw
         ctx.module = module
@@ -124,29 +222,33 @@ class _BlockFn(torch.autograd.Function):
         dy2d = dy_nhwc.view(M, C)
         win = ctx.module._window          # GradWindow slot of this block, or None
         a = win.acc if win is not None and win.owner.active else None
-        dz, db1f = ops.mlp_bwd_dz(dy2d, fw.w2fT, z, None if a is None else a["db1f"])
-        side = _side_stream(x.device)
-        if side is None:
-            dxhat = ops.mlp_bwd_dxhat(dz, fw.w1fT)
-            dw2f, dw1f = ops.mlp_bwd_wgrad(dy2d, h, dz, xhat.view(M, C),
-                                           None if a is None else (a["dw2f"], a["dw1f"]))
+        if ctx.nsub > 1:
+            dx, dw2f, dw1f, db1f, dwt, dbias, db2f = _backward_sub_batched(
+                x.permute(0, 2, 3, 1), xhat, rstd, z, h, dy_nhwc, fw, a, ctx.nsub)
         else:
-            # weight gradients on the side stream; their outputs are allocated here, on the main one
-            if a is None:
-                wacc = (torch.zeros(C, 4 * C, device=x.device, dtype=torch.float32),
-                        torch.zeros(4 * C, C, device=x.device, dtype=torch.float32))
+            dz, db1f = ops.mlp_bwd_dz(dy2d, fw.w2fT, z, None if a is None else a["db1f"])
+            side = _side_stream(x.device)
+            if side is None:
+                dxhat = ops.mlp_bwd_dxhat(dz, fw.w1fT)
+                dw2f, dw1f = ops.mlp_bwd_wgrad(dy2d, h, dz, xhat.view(M, C),
+                                               None if a is None else (a["dw2f"], a["dw1f"]))
             else:
-                wacc = (a["dw2f"], a["dw1f"])
-            main = torch.cuda.current_stream(x.device)
-            side.wait_stream(main)
-            with torch.cuda.stream(side):
-                dw2f, dw1f = ops.mlp_bwd_wgrad(dy2d, h, dz, xhat.view(M, C), wacc)
-            dxhat = ops.mlp_bwd_dxhat(dz, fw.w1fT)
-        dx, dwt, dbias, db2f = ops.dwconv_ln_bwd(
-            dxhat.view(B, H, W, C), xhat, rstd, x.permute(0, 2, 3, 1), dy_nhwc, fw.wt_dw,
-            None if a is None else (a["dwt"], a["dbias"], a["db2f"]))
-        if side is not None:
-            torch.cuda.current_stream(x.device).wait_stream(side)
+                # weight gradients on the side stream; their outputs are allocated here, on the main one
+                if a is None:
+                    wacc = (torch.zeros(C, 4 * C, device=x.device, dtype=torch.float32),
+                            torch.zeros(4 * C, C, device=x.device, dtype=torch.float32))
+                else:
+                    wacc = (a["dw2f"], a["dw1f"])
+                main = torch.cuda.current_stream(x.device)
+                side.wait_stream(main)
+                with torch.cuda.stream(side):
+                    dw2f, dw1f = ops.mlp_bwd_wgrad(dy2d, h, dz, xhat.view(M, C), wacc)
+                dxhat = ops.mlp_bwd_dxhat(dz, fw.w1fT)
+            dx, dwt, dbias, db2f = ops.dwconv_ln_bwd(
+                dxhat.view(B, H, W, C), xhat, rstd, x.permute(0, 2, 3, 1), dy_nhwc, fw.wt_dw,
+                None if a is None else (a["dwt"], a["dbias"], a["db2f"]))
+            if side is not None:
+                torch.cuda.current_stream(x.device).wait_stream(side)
         if a is not None and not win.owner.boundary:
             # inside an accumulation window: the folded-parameter gradients stay in the window's
             # fp32 accumulators; parameter gradients are produced on the boundary micro-batch only

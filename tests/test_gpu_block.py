@@ -313,3 +313,30 @@ def test_weight_fold_cache_tracks_versions(cnx_lib):
     y1 = blk(x)
     assert blk._fold is not f0
     assert not torch.equal(y0, y1)
+
+
+def test_block_sub_batched_path_equals_single_pass(cnx_lib, monkeypatch):
+    """CNX_L2_CHUNK_MB (block._l2_sub_batches, off by default): the block run sub-batch by sub-batch
+    through all its kernels gives the same output, input gradient and parameter gradients."""
+    from image_classification_b200 import block as block_mod
+    from image_classification_b200.block import ConvNeXtBlockB200
+    dev = _dev()
+    torch.manual_seed(4)
+    blk = ConvNeXtBlockB200(128).to(dev)
+    with torch.no_grad():
+        blk.gamma.copy_(torch.rand(128, device=dev) * 0.9 + 0.1)
+    x = torch.randn(8, 128, 12, 10, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    gy = torch.randn_like(x)
+    outs = []
+    for mb in ("0", "0.3"):                 # hidden tensor: 8*120*512*2 B = 0.98 MB -> 4 sub-batches
+        monkeypatch.setenv("CNX_L2_CHUNK_MB", mb)
+        assert block_mod._l2_sub_batches(8, 12, 10, 128) == (1 if mb == "0" else 4)
+        blk.zero_grad(set_to_none=True)
+        xi = x.clone().requires_grad_()
+        y = blk(xi)
+        y.backward(gy)
+        outs.append((y.detach(), xi.grad, {n: p.grad.clone() for n, p in blk.named_parameters()}))
+    (y0, dx0, g0), (y1, dx1, g1) = outs
+    assert torch.equal(y0, y1) and torch.equal(dx0, dx1)        # per-sample arithmetic is the same
+    for n in g0:
+        assert _rel(g1[n], g0[n]) < 1e-4, n                      # sums in a different order
