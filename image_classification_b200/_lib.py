@@ -55,7 +55,7 @@ SIGNATURES = {
     "cnx_debug_gemm_epilogue_warps": (None, [I]),
     "cnx_debug_max_clusters": (I, [I]),
     "cnx_workspace_bytes": (c_size_t, [I, I, I, I, I]),
-    "cnx_prep_block_weights": (I, [P] * 8 + [P] * 7 + [I, P]),
+    "cnx_prep_block_weights": (I, [P] * 8 + [P] * 8 + [I, P]),
     "cnx_unfold_block_grads": (I, [P] * 11 + [P] * 7 + [I, P]),
     "cnx_dwconv_ln_fwd": (I, [P, P, P, P, P, P, I, I, I, I, F, P]),
     "cnx_dwconv_ln_bwd": (I, [P] * 10 + [I, I, I, I, P, c_size_t, P]),
@@ -83,6 +83,9 @@ SIGNATURES = {
     "cnx_fc2_residual_fwd": (I, [P, P, P, P, P, I, I, P]),
     "cnx_mlp_bwd_dz": (I, [P, P, P, P, P, I, I, P]),
     "cnx_mlp_bwd_dxhat": (I, [P, P, P, I, I, P]),
+    "cnx_mlp_bwd_dz_stats": (I, [P, P, P, P, P, P, P, I, I, P]),
+    "cnx_mlp_bwd_dconv": (I, [P, P, P, P, P, P, I, I, P]),
+    "cnx_dwconv_bwd": (I, [P] * 8 + [I, I, I, I, I, P]),
     "cnx_mlp_bwd_wgrad": (I, [P, P, P, P, P, P, I, I, P]),
     "cnx_mix_batch": (I, [P, P, P, P, P, I, I, I, I, I, P]),
     "cnx_mix_batch_smooth": (I, [P, P, P, P, P, I, I, I, I, I, F, F, P]),
@@ -131,7 +134,7 @@ def check(rc: int, what: str) -> None:
 LAUNCHES_PER_CALL = {
     "cnx_prep_block_weights": 1, "cnx_unfold_block_grads": 2, "cnx_dwconv_ln_fwd": 2,
     "cnx_dwconv_ln_bwd": 2, "cnx_dwconv_ln_bwd_acc": 2, "cnx_gemm_bf16": 1, "cnx_layernorm_fwd": 1, "cnx_layernorm_bwd": 1, "cnx_colsum_bf16": 1, "cnx_dwconv_kxk_fwd": 1, "cnx_dwconv_kxk_bwd": 2, "cnx_avgpool_nhwc_fwd": 1, "cnx_avgpool_nhwc_bwd": 1, "cnx_layernorm_patch_fwd": 1, "cnx_layernorm_patch_bwd": 1, "cnx_patchify_nchw_f32": 1, "cnx_fc1_gelu_fwd": 1, "cnx_fc2_residual_fwd": 1,
-    "cnx_mlp_bwd_dz": 1, "cnx_mlp_bwd_dxhat": 1, "cnx_mlp_bwd_wgrad": 2, "cnx_mix_batch": 1, "cnx_mix_batch_smooth": 1,
+    "cnx_mlp_bwd_dz": 1, "cnx_mlp_bwd_dxhat": 1, "cnx_mlp_bwd_dz_stats": 1, "cnx_mlp_bwd_dconv": 1, "cnx_dwconv_bwd": 1, "cnx_mlp_bwd_wgrad": 2, "cnx_mix_batch": 1, "cnx_mix_batch_smooth": 1,
     "cnx_softce_fwd_bwd": 1, "cnx_ema_lerp_multi": 1, "cnx_optim_grad_norm": 1, "cnx_optim_adamw_ema": 1, "cnx_nchw_f32_to_nhwc_bf16": 1,
     "cnx_nhwc_bf16_to_nchw_f32": 1,
     "cnx_bn_stats": 1, "cnx_bn_act_fwd": 1, "cnx_bn_act_bwd": 2, "cnx_se_scale_fwd": 1,

@@ -226,10 +226,24 @@ class _BlockFn(torch.autograd.Function):
             dx, dw2f, dw1f, db1f, dwt, dbias, db2f = _backward_sub_batched(
                 x.permute(0, 2, 3, 1), xhat, rstd, z, h, dy_nhwc, fw, a, ctx.nsub)
         else:
-            dz, db1f = ops.mlp_bwd_dz(dy2d, fw.w2fT, z, None if a is None else a["db1f"])
+            # CNX_LNBWD_LINEARITY=1: LayerNorm backward by linearity (include/cnx_b200.h,
+            # cnx_mlp_bwd_dz_stats): the per-token sums it needs come out of the dz GEMM's epilogue,
+            # the fc1 data-gradient GEMM applies them in its own epilogue and hands the conv its
+            # output gradient directly — no LayerNorm-backward row kernel, no dxhat / dconv round trip
+            # (stage-1 DRAM traffic of the LayerNorm part 516 -> 309 MB, 144 launches fewer per step,
+            # half the rounding error).  Measured per stage (tools/lnbwd_microbench.py,
+            # profiles/r02_lnbwd_linearity_ab.txt): 637 / 363 / 232 / 194 us against 629 / 356 / 228 /
+            # 200 us for dz GEMM + dxhat GEMM + row kernel + conv-bwd — the three extra packed FMAs per
+            # two elements in the FMA-pipe-bound dz epilogue cost what the row kernel cost, and the
+            # step time is unchanged (43.7-44.2 vs 43.4-43.8 ms), so the default stays the row kernel.
+            rowk = os.environ.get("CNX_LNBWD_LINEARITY") != "1"
+            if rowk:
+                dz, db1f = ops.mlp_bwd_dz(dy2d, fw.w2fT, z, None if a is None else a["db1f"])
+            else:
+                dz, db1f, rowstats = ops.mlp_bwd_dz_stats(dy2d, fw.w2fT, z, fw.rb,
+                                                          None if a is None else a["db1f"])
             side = _side_stream(x.device)
             if side is None:
-                dxhat = ops.mlp_bwd_dxhat(dz, fw.w1fT)
                 dw2f, dw1f = ops.mlp_bwd_wgrad(dy2d, h, dz, xhat.view(M, C),
                                                None if a is None else (a["dw2f"], a["dw1f"]))
             else:
@@ -243,10 +257,15 @@ class _BlockFn(torch.autograd.Function):
                 side.wait_stream(main)
                 with torch.cuda.stream(side):
                     dw2f, dw1f = ops.mlp_bwd_wgrad(dy2d, h, dz, xhat.view(M, C), wacc)
+            cacc = None if a is None else (a["dwt"], a["dbias"], a["db2f"])
+            if rowk:
                 dxhat = ops.mlp_bwd_dxhat(dz, fw.w1fT)
-            dx, dwt, dbias, db2f = ops.dwconv_ln_bwd(
-                dxhat.view(B, H, W, C), xhat, rstd, x.permute(0, 2, 3, 1), dy_nhwc, fw.wt_dw,
-                None if a is None else (a["dwt"], a["dbias"], a["db2f"]))
+                dx, dwt, dbias, db2f = ops.dwconv_ln_bwd(dxhat.view(B, H, W, C), xhat, rstd,
+                                                         x.permute(0, 2, 3, 1), dy_nhwc, fw.wt_dw, cacc)
+            else:
+                dconv = ops.mlp_bwd_dconv(dz, fw.w1fT, xhat.view(M, C), rowstats, rstd)
+                dx, dwt, dbias, db2f = ops.dwconv_bwd(dconv.view(B, H, W, C), x.permute(0, 2, 3, 1),
+                                                      dy_nhwc, fw.wt_dw, cacc)
             if side is not None:
                 torch.cuda.current_stream(x.device).wait_stream(side)
         if a is not None and not win.owner.boundary:

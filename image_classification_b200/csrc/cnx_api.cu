@@ -50,15 +50,15 @@ size_t cnx_workspace_bytes(int op, int B, int H, int W, int C) {
 int cnx_prep_block_weights(const float* conv_dw_w, const float* norm_w, const float* norm_b,
                            const float* fc1_w, const float* fc1_b, const float* fc2_w,
                            const float* fc2_b, const float* gamma, float* wt_dw, void* w1f,
-                           void* w1fT, float* b1f, void* w2f, void* w2fT, float* b2f, int C,
-                           void* stream) {
+                           void* w1fT, float* b1f, void* w2f, void* w2fT, float* b2f, float* rb,
+                           int C, void* stream) {
   CNX_REQUIRE_DEVICE();
   CNX_REQUIRE_PTR(conv_dw_w); CNX_REQUIRE_PTR(norm_w); CNX_REQUIRE_PTR(norm_b);
   CNX_REQUIRE_PTR(fc1_w); CNX_REQUIRE_PTR(fc1_b); CNX_REQUIRE_PTR(fc2_w); CNX_REQUIRE_PTR(fc2_b);
   CNX_REQUIRE_PTR(gamma); CNX_REQUIRE_PTR(wt_dw); CNX_REQUIRE_PTR(w1f); CNX_REQUIRE_PTR(w1fT);
   CNX_REQUIRE_PTR(b1f); CNX_REQUIRE_PTR(w2f); CNX_REQUIRE_PTR(w2fT); CNX_REQUIRE_PTR(b2f);
   return prep_block_weights(conv_dw_w, norm_w, norm_b, fc1_w, fc1_b, fc2_w, fc2_b, gamma, wt_dw,
-                            w1f, w1fT, b1f, w2f, w2fT, b2f, C, as_stream(stream));
+                            w1f, w1fT, b1f, w2f, w2fT, b2f, rb, C, as_stream(stream));
 }
 
 int cnx_unfold_block_grads(const float* dw1f, const float* db1f, const float* dw2f,
@@ -277,6 +277,7 @@ int cnx_gemm_bf16(const void* A, int64_t lda, int a_mn_major, const void* B, int
   a.epilogue = epilogue;
   a.D0 = D0; a.ldd0 = ldd0; a.D1 = D1; a.ldd1 = ldd1;
   a.bias = bias; a.R = R; a.ldr = ldr; a.colsum = colsum;
+  a.rowvec2 = nullptr; a.rowstats = nullptr; a.rstd = nullptr;
   return gemm_bf16(a, as_stream(stream));
 }
 
@@ -296,6 +297,46 @@ int cnx_mlp_bwd_dz(const void* dy, const void* w2fT, const void* z, void* dz, fl
                    int C, void* stream) {
   return cnx_gemm_bf16(dy, C, 0, w2fT, C, 0, M, 4 * C, C, CNX_EPI_GELU_GRAD, dz, 4 * C, nullptr, 0,
                        nullptr, z, 4 * C, db1f, stream);
+}
+
+int cnx_mlp_bwd_dz_stats(const void* dy, const void* w2fT, const void* z, const float* rb, void* dz,
+                         float* db1f, float* rowstats, int M, int C, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(dy); CNX_REQUIRE_PTR(w2fT); CNX_REQUIRE_PTR(z); CNX_REQUIRE_PTR(rb);
+  CNX_REQUIRE_PTR(dz); CNX_REQUIRE_PTR(rowstats);
+  GemmArgs a{};
+  a.A = dy; a.lda = C; a.B = w2fT; a.ldb = C;
+  a.M = M; a.N = 4 * C; a.K = C;
+  a.epilogue = EPI_GELU_GRAD;
+  a.D0 = dz; a.ldd0 = 4 * C;
+  a.R = z; a.ldr = 4 * C; a.colsum = db1f;
+  a.rowvec2 = rb; a.rowstats = rowstats;
+  return gemm_bf16(a, as_stream(stream));
+}
+
+int cnx_mlp_bwd_dconv(const void* dz, const void* w1fT, const void* xhat, const float* rowstats,
+                      const float* rstd, void* dconv, int M, int C, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(dz); CNX_REQUIRE_PTR(w1fT); CNX_REQUIRE_PTR(xhat); CNX_REQUIRE_PTR(rowstats);
+  CNX_REQUIRE_PTR(rstd); CNX_REQUIRE_PTR(dconv);
+  GemmArgs a{};
+  a.A = dz; a.lda = 4 * C; a.B = w1fT; a.ldb = 4 * C;
+  a.M = M; a.N = C; a.K = 4 * C;
+  a.epilogue = EPI_LN_BWD;
+  a.D0 = dconv; a.ldd0 = C;
+  a.R = xhat; a.ldr = C;
+  a.rowstats = const_cast<float*>(rowstats); a.rstd = rstd;
+  return gemm_bf16(a, as_stream(stream));
+}
+
+int cnx_dwconv_bwd(const void* dconv, const void* x, const void* dy, const float* wt_dw, void* dx,
+                   float* dwt, float* dbias, float* dy_colsum, int B, int H, int W, int C,
+                   int accumulate, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(dconv); CNX_REQUIRE_PTR(x); CNX_REQUIRE_PTR(dy); CNX_REQUIRE_PTR(wt_dw);
+  CNX_REQUIRE_PTR(dx); CNX_REQUIRE_PTR(dwt); CNX_REQUIRE_PTR(dbias); CNX_REQUIRE_PTR(dy_colsum);
+  return dwconv_bwd(dconv, x, dy, wt_dw, dx, dwt, dbias, dy_colsum, B, H, W, C, accumulate,
+                    as_stream(stream));
 }
 
 int cnx_mlp_bwd_dxhat(const void* dz, const void* w1fT, void* dxhat, int M, int C, void* stream) {

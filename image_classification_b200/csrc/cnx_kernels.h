@@ -71,6 +71,8 @@ enum GemmEpilogue : int {
   EPI_GELU_GRAD = 3,        // D = acc * gelu'(Z[m,n]); colsum[n] += D  (bf16 out, Z bf16)
   EPI_STORE_F32 = 4,        // D = acc                                  (fp32 out; weight grads)
   EPI_BIAS = 6,             // D = acc + bias[n]                        (bf16 out; 5 is internal)
+  EPI_LN_BWD = 7,           // D = rstd[m] * (acc - s1[m]/N - R[m,n] * s2[m]/N): LayerNorm backward of
+                            // the fc1 data gradient (R = xhat, (s1, s2) = rowstats[m])   (bf16 out)
 };
 struct GemmArgs {
   // D[M,N] = A[M,K] * B[N,K]^T.  a_mn_major / b_mn_major: operand stored as [K,M] / [K,N].
@@ -84,6 +86,12 @@ struct GemmArgs {
   const float* bias;            // [N]
   const void* R; int64_t ldr;   // residual (EPI_BIAS_RESIDUAL) or Z (EPI_GELU_GRAD), bf16
   float* colsum;                // [N] fp32, atomically accumulated (EPI_GELU_GRAD), may be null
+  // LayerNorm backward by linearity (see gemm2.cu): EPI_GELU_GRAD also accumulates, per row m,
+  //   rowstats[m] += ( sum_n D[m,n] * rowvec2[n].x ,  sum_n D[m,n] * (Z[m,n] + rowvec2[n].y) )
+  // when rowvec2 / rowstats are given; EPI_LN_BWD consumes rowstats and rstd.
+  const float* rowvec2;         // [N][2] fp32
+  float* rowstats;              // [M][2] fp32
+  const float* rstd;            // [M] fp32 (EPI_LN_BWD)
 };
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream);      // gemm2.cu (persistent, warp-specialised)
 int gemm_debug_max_clusters(int cluster_size);                      // gemm2.cu, occupancy probe
@@ -124,7 +132,7 @@ int optim_adamw_ema(void* const* param_ptrs, const void* const* grad_ptrs, void*
 int prep_block_weights(const float* dw_w, const float* ln_w, const float* ln_b, const float* fc1_w,
                        const float* fc1_b, const float* fc2_w, const float* fc2_b,
                        const float* ls_gamma, float* wt_dw, void* w1f, void* w1fT, float* b1f,
-                       void* w2f, void* w2fT, float* b2f, int C, cudaStream_t stream);
+                       void* w2f, void* w2fT, float* b2f, float* rb, int C, cudaStream_t stream);
 int unfold_block_grads(const float* dw1f, const float* db1f, const float* dw2f, const float* db2f,
                        const float* dwt_dw, const float* ln_w, const float* ln_b,
                        const float* fc1_w, const float* fc2_w, const float* fc2_b,

@@ -76,6 +76,10 @@ struct Gemm2Params {
   float* D0f; int64_t ldd0;        // fp32 output (EPI_STORE_F32 / EPI_ATOMIC_F32)
   const float* bias;
   float* colsum;
+  const float2* rowvec2;           // EPI_GELU_GRAD: [N] (r[n], -b[n]) (nullable)
+  float* rowstats;                 // EPI_GELU_GRAD: [M][2] += ; EPI_LN_BWD: [M][2] read
+  const float* rstd;               // EPI_LN_BWD: [M]
+  float inv_n;                     // EPI_LN_BWD: 1 / N
 };
 
 // ---- packed-fp32 helpers (one issue slot, two lanes)
@@ -186,7 +190,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
   using L = Cfg<BN, PAIR, !(EPI == EPI_STORE_F32 || EPI == EPI_ATOMIC_F32)>;
   constexpr int kStages = L::kStages;
   constexpr int kTileM = L::kTileM;
-  constexpr bool kHasR = (EPI == EPI_BIAS_RESIDUAL || EPI == EPI_GELU_GRAD);
+  constexpr bool kHasR = (EPI == EPI_BIAS_RESIDUAL || EPI == EPI_GELU_GRAD || EPI == EPI_LN_BWD);
   constexpr bool kF32Out = (EPI == EPI_STORE_F32 || EPI == EPI_ATOMIC_F32);
   constexpr int kChunks = BN / 2 / 64;         // 64-column chunks per epilogue warp per tile
 
@@ -593,6 +597,19 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
         flush_colsum();
         cs_nblk = c.n_blk;
       }
+      // LayerNorm backward by linearity (EPI_LN_BWD): out = rs * acc + c0 + xhat * c1 with the
+      // per-row constants rs = rstd, c0 = -rstd * s1 / N, c1 = -rstd * s2 / N, where
+      // s1 = sum_n dxhat[m,n] and s2 = sum_n dxhat[m,n] * xhat[m,n] came out of the dz GEMM's
+      // epilogue (below): dxhat = dz W1f, so s1 = dz . rowsum(W1f) and, because
+      // z = xhat W1f^T + b1f,  s2 = dz . (z - b1f) — no pass over dxhat is needed.
+      float ln_rs = 0.f, ln_c0 = 0.f, ln_c1 = 0.f;
+      if (EPI == EPI_LN_BWD && row0 + lane < p.M) {
+        const float2 st2 = __ldg(reinterpret_cast<const float2*>(p.rowstats) + row0 + lane);
+        ln_rs = __ldg(p.rstd + row0 + lane);
+        ln_c0 = -ln_rs * st2.x * p.inv_n;
+        ln_c1 = -ln_rs * st2.y * p.inv_n;
+      }
+      float2 st_s1 = make_float2(0.f, 0.f), st_s2 = make_float2(0.f, 0.f);   // EPI_GELU_GRAD row sums
       mbar_wait(&tmem_full_bar[ab], (i >> 1) & 1, p.timeout_flag);
       tc_fence_after();
       const uint32_t tmem_acc = tmem_base + ab * BN + (static_cast<uint32_t>(q * 32) << 16) +
@@ -674,10 +691,27 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
 #pragma unroll
             for (int j = 0; j < 16; ++j) f[j] = fmul2(f[j], gelu_grad2(bf16x2_to_f32x2(rr[j])));
           }
+          if (EPI == EPI_LN_BWD) {
+            const float2 rs2 = splat(ln_rs), c02 = splat(ln_c0), c12 = splat(ln_c1);
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              f[j] = ffma2(bf16x2_to_f32x2(rr[j]), c12, ffma2(f[j], rs2, c02));
+          }
 
           uint32_t pk[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) pk[j] = f32x2_to_bf16x2(f[j].x, f[j].y);
+          if (EPI == EPI_GELU_GRAD && p.rowstats != nullptr && n + 31 < p.N) {
+            // row sums for the LayerNorm backward, taken over the ROUNDED dz (what the fc1
+            // data-gradient GEMM will consume) and the rounded z it was computed from
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float4 rb = __ldg(reinterpret_cast<const float4*>(p.rowvec2 + n + 2 * j));
+              const float2 dzr = bf16x2_to_f32x2(pk[j]);
+              st_s1 = ffma2(dzr, make_float2(rb.x, rb.z), st_s1);
+              st_s2 = ffma2(dzr, fadd2(bf16x2_to_f32x2(rr[j]), make_float2(rb.y, rb.w)), st_s2);
+            }
+          }
           uint32_t hk[EPI == EPI_BIAS_GELU ? 16 : 1];
           if (EPI == EPI_BIAS_GELU) {
             // activation of the ROUNDED pre-activation (what backward will see), second output
@@ -744,6 +778,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
         }
       }
 
+      if (EPI == EPI_GELU_GRAD && p.rowstats != nullptr && row0 + lane < p.M) {
+        atomicAdd(p.rowstats + 2 * (row0 + lane), st_s1.x + st_s1.y);
+        atomicAdd(p.rowstats + 2 * (row0 + lane) + 1, st_s2.x + st_s2.y);
+      }
       if (kF32Out || chunk_n(c, kChunks - 1) >= p.N) {
         // the last chunk was skipped (ragged N) or the fp32 path ran: release the accumulator here
         tc_fence_before();
@@ -799,6 +837,7 @@ int dispatch(int epi, int ew, const CUtensorMap& ma, const CUtensorMap& mb, cons
     CNX_GEMM_CASE(EPI_BIAS_GELU)
     CNX_GEMM_CASE(EPI_BIAS_RESIDUAL)
     CNX_GEMM_CASE(EPI_GELU_GRAD)
+    case EPI_LN_BWD:     return launch2<BN, EPI_LN_BWD, PAIR, 8>(ma, mb, md0, md1, mr, p, grid, stream);
     case EPI_STORE_F32:  return launch2<BN, EPI_STORE_F32, PAIR, 8>(ma, mb, md0, md1, mr, p, grid, stream);
     case EPI_ATOMIC_F32: return launch2<BN, EPI_ATOMIC_F32, PAIR, 8>(ma, mb, md0, md1, mr, p, grid, stream);
     default: break;
@@ -882,9 +921,11 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   }
   int epi = a.epilogue;
   const bool need_bias = (epi == EPI_BIAS_GELU || epi == EPI_BIAS_RESIDUAL || epi == EPI_BIAS);
-  const bool need_r = (epi == EPI_BIAS_RESIDUAL || epi == EPI_GELU_GRAD);
-  if (epi < 0 || (epi > EPI_STORE_F32 && epi != EPI_BIAS) || (need_bias && !a.bias) || (need_r && !a.R) ||
-      (epi == EPI_BIAS_GELU && !a.D1)) {
+  const bool need_r = (epi == EPI_BIAS_RESIDUAL || epi == EPI_GELU_GRAD || epi == EPI_LN_BWD);
+  if (epi < 0 || (epi > EPI_STORE_F32 && epi != EPI_BIAS && epi != EPI_LN_BWD) || (need_bias && !a.bias) ||
+      (need_r && !a.R) || (epi == EPI_BIAS_GELU && !a.D1) ||
+      (epi == EPI_LN_BWD && (!a.rowstats || !a.rstd)) ||
+      (epi == EPI_GELU_GRAD && ((a.rowvec2 != nullptr) != (a.rowstats != nullptr)))) {
     set_last_error("gemm_bf16: unsupported epilogue %d or missing operand", a.epilogue);
     return CNX_ERR_BAD_ARG;
   }
@@ -902,6 +943,10 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   p.b_mn = a.b_mn_major ? 1 : 0;
   p.bias = a.bias;
   p.colsum = a.colsum;
+  p.rowvec2 = reinterpret_cast<const float2*>(a.rowvec2);
+  p.rowstats = a.rowstats;
+  p.rstd = a.rstd;
+  p.inv_n = 1.0f / static_cast<float>(a.N);
   p.D0f = static_cast<float*>(a.D0);
   p.ldd0 = a.ldd0;
   p.nkb_total = nkb;
@@ -918,6 +963,7 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
     case EPI_STORE_F32:     pair = true; break;
     case EPI_STORE_BF16:
     case EPI_BIAS:
+    case EPI_LN_BWD:
     case EPI_BIAS_RESIDUAL: pair = a.K >= 1024 || (a.K >= 512 && a.N >= 1024); break;
     case EPI_BIAS_GELU:     pair = a.K >= 256; break;
     case EPI_GELU_GRAD:     pair = a.K >= 512; break;
@@ -1026,6 +1072,7 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   // cnx_debug_gemm_epilogue_warps() forces 8 or 16 for every bf16 epilogue (A/B measurements)
   int ew = (epi == EPI_BIAS_GELU && a.K <= 256) ? 16 : 8;
   if (g_tune.epi_warps != 0) ew = g_tune.epi_warps;
+  if (epi == EPI_LN_BWD || (epi == EPI_GELU_GRAD && a.rowstats != nullptr)) ew = 8;   // 8-warp path only
   if (pair)
     return BN == 256 ? dispatch<256, true>(epi, ew, ma, mb, md0, md1, mr, p, grid, stream)
                      : dispatch<128, true>(epi, ew, ma, mb, md0, md1, mr, p, grid, stream);

@@ -50,6 +50,7 @@ struct PrepArgs {
   float* wt_dw;
   __nv_bfloat16 *w1f, *w1fT, *w2f, *w2fT;
   float *b1f, *b2f;
+  float2* rb;                // [4C] (rowsum_c bf16(W1f[j,c]), -b1f[j]): LayerNorm-backward by linearity
   int C;
   int n_t1, n_t2, n_b1;      // CTA counts of the first three sections
 };
@@ -80,10 +81,19 @@ __global__ void __launch_bounds__(256) prep_block_kernel(const PrepArgs a) {
     const int row = b * 8 + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (row >= R4) return;
-    float s = 0.f;
-    for (int c = lane; c < C; c += 32) s = fmaf(a.fc1_w[static_cast<size_t>(row) * C + c], a.ln_b[c], s);
+    float s = 0.f, r = 0.f;
+    for (int c = lane; c < C; c += 32) {
+      const float w = a.fc1_w[static_cast<size_t>(row) * C + c];
+      s = fmaf(w, a.ln_b[c], s);
+      r += __bfloat162float(__float2bfloat16_rn(w * a.ln_w[c]));   // the value stored in w1f
+    }
     s = warp_sum(s);
-    if (lane == 0) a.b1f[row] = a.fc1_b[row] + s;
+    r = warp_sum(r);
+    if (lane == 0) {
+      const float b = a.fc1_b[row] + s;
+      a.b1f[row] = b;
+      if (a.rb != nullptr) a.rb[row] = make_float2(r, -b);
+    }
     return;
   }
   b -= a.n_b1;
@@ -192,7 +202,7 @@ int check_launch(const char* what) {
 int prep_block_weights(const float* dw_w, const float* ln_w, const float* ln_b, const float* fc1_w,
                        const float* fc1_b, const float* fc2_w, const float* fc2_b,
                        const float* ls_gamma, float* wt_dw, void* w1f, void* w1fT, float* b1f,
-                       void* w2f, void* w2fT, float* b2f, int C, cudaStream_t stream) {
+                       void* w2f, void* w2fT, float* b2f, float* rb, int C, cudaStream_t stream) {
   if (C <= 0 || (C % 8) != 0) {
     set_last_error("prep_block_weights: C=%d must be a positive multiple of 8", C);
     return CNX_ERR_BAD_SHAPE;
@@ -203,7 +213,7 @@ int prep_block_weights(const float* dw_w, const float* ln_w, const float* ln_b, 
   a.fc2_b = fc2_b; a.gamma = ls_gamma; a.wt_dw = wt_dw;
   a.w1f = static_cast<__nv_bfloat16*>(w1f); a.w1fT = static_cast<__nv_bfloat16*>(w1fT);
   a.w2f = static_cast<__nv_bfloat16*>(w2f); a.w2fT = static_cast<__nv_bfloat16*>(w2fT);
-  a.b1f = b1f; a.b2f = b2f; a.C = C;
+  a.b1f = b1f; a.b2f = b2f; a.rb = reinterpret_cast<float2*>(rb); a.C = C;
   a.n_t1 = ((C + 31) / 32) * ((R4 + 31) / 32);
   a.n_t2 = a.n_t1;
   a.n_b1 = (R4 + 7) / 8;

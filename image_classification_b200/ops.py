@@ -42,6 +42,7 @@ class FoldedWeights:
     w2f: torch.Tensor     # [C, 4C] bf16
     w2fT: torch.Tensor    # [4C, C] bf16
     b2f: torch.Tensor     # [C] fp32
+    rb: torch.Tensor      # [4C, 2] fp32: (rowsum of the bf16 w1f row, -b1f): LayerNorm backward by linearity
 
 
 def prep_block_weights(conv_dw_w, norm_w, norm_b, fc1_w, fc1_b, fc2_w, fc2_b, gamma) -> FoldedWeights:
@@ -60,10 +61,11 @@ def prep_block_weights(conv_dw_w, norm_w, norm_b, fc1_w, fc1_b, fc2_w, fc2_b, ga
         w2f=torch.empty(C, 4 * C, device=dev, dtype=torch.bfloat16),
         w2fT=torch.empty(4 * C, C, device=dev, dtype=torch.bfloat16),
         b2f=torch.empty(C, device=dev, dtype=f32),
+        rb=torch.empty(4 * C, 2, device=dev, dtype=f32),
     )
     _lib.call("cnx_prep_block_weights", _p(conv_dw_w), _p(norm_w), _p(norm_b), _p(fc1_w),
               _p(fc1_b), _p(fc2_w), _p(fc2_b), _p(gamma), _p(fw.wt_dw), _p(fw.w1f), _p(fw.w1fT),
-              _p(fw.b1f), _p(fw.w2f), _p(fw.w2fT), _p(fw.b2f), C, _stream(gamma))
+              _p(fw.b1f), _p(fw.w2f), _p(fw.w2fT), _p(fw.b2f), _p(fw.rb), C, _stream(gamma))
     return fw
 
 
@@ -460,6 +462,52 @@ def mlp_bwd_dz(dy2d, w2fT, z, db1f=None):
               _p(_chk(w2fT, torch.bfloat16, "w2fT")), _p(_chk(z, torch.bfloat16, "z")), _p(dz),
               _p(db1f), M, C, _stream(z))
     return dz, db1f
+
+
+def mlp_bwd_dz_stats(dy2d, w2fT, z, rb, db1f=None):
+    """cnx_mlp_bwd_dz that also returns rowstats [M,2] fp32 = (sum_c dxhat, sum_c dxhat * xhat)
+    per token, taken in the GEMM epilogue (see include/cnx_b200.h).  -> (dz, db1f, rowstats)."""
+    M, C = dy2d.shape
+    dz = torch.empty_like(z)
+    if db1f is None:
+        db1f = torch.zeros(4 * C, device=z.device, dtype=torch.float32)
+    rowstats = torch.zeros(M, 2, device=z.device, dtype=torch.float32)
+    _lib.call("cnx_mlp_bwd_dz_stats", _p(_chk(dy2d, torch.bfloat16, "dy")),
+              _p(_chk(w2fT, torch.bfloat16, "w2fT")), _p(_chk(z, torch.bfloat16, "z")),
+              _p(_chk(rb, torch.float32, "rb")), _p(dz), _p(db1f), _p(rowstats), M, C, _stream(z))
+    return dz, db1f, rowstats
+
+
+def mlp_bwd_dconv(dz, w1fT, xhat2d, rowstats, rstd):
+    """fc1 data-gradient GEMM with the LayerNorm backward in its epilogue -> dconv [M,C] bf16."""
+    M, C4 = dz.shape
+    C = C4 // 4
+    dconv = torch.empty(M, C, device=dz.device, dtype=torch.bfloat16)
+    _lib.call("cnx_mlp_bwd_dconv", _p(_chk(dz, torch.bfloat16, "dz")),
+              _p(_chk(w1fT, torch.bfloat16, "w1fT")), _p(_chk(xhat2d, torch.bfloat16, "xhat")),
+              _p(_chk(rowstats, torch.float32, "rowstats")), _p(_chk(rstd, torch.float32, "rstd")),
+              _p(dconv), M, C, _stream(dz))
+    return dconv
+
+
+def dwconv_bwd(dconv, x_nhwc, dy, wt_dw, acc=None):
+    """Depthwise 7x7 conv backward alone -> (dx, dwt [49,C], dbias [C], dy_colsum [C]);
+    acc=(dwt, dbias, dy_colsum): += into these buffers."""
+    for n, t in (("dconv", dconv), ("x", x_nhwc), ("dy", dy)):
+        _chk(t, torch.bfloat16, n)
+    _chk(wt_dw, torch.float32, "wt_dw")
+    B, H, W, C = x_nhwc.shape
+    dev = x_nhwc.device
+    dx = torch.empty_like(x_nhwc)
+    if acc is None:
+        dwt = torch.empty(49, C, device=dev, dtype=torch.float32)
+        dbias = torch.empty(C, device=dev, dtype=torch.float32)
+        dycs = torch.empty(C, device=dev, dtype=torch.float32)
+    else:
+        dwt, dbias, dycs = (_chk(t, torch.float32, "acc") for t in acc)
+    _lib.call("cnx_dwconv_bwd", _p(dconv), _p(x_nhwc), _p(dy), _p(wt_dw), _p(dx), _p(dwt), _p(dbias),
+              _p(dycs), B, H, W, C, int(acc is not None), _stream(x_nhwc))
+    return dx, dwt, dbias, dycs
 
 
 def mlp_bwd_dxhat(dz, w1fT):

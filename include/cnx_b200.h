@@ -52,7 +52,8 @@ typedef enum cnx_epilogue {
   CNX_EPI_BIAS_RESIDUAL = 2, /* D0 = acc + bias + R                        */
   CNX_EPI_GELU_GRAD = 3,     /* D0 = acc * gelu'(R) ; colsum += sum_m D0   */
   CNX_EPI_STORE_F32 = 4,     /* D0 (fp32, zero-filled by caller) += acc    */
-  CNX_EPI_BIAS = 6           /* D0 = acc + bias (patchify convolutions)    */
+  CNX_EPI_BIAS = 6,          /* D0 = acc + bias (patchify convolutions)    */
+  CNX_EPI_LN_BWD = 7         /* D0 = LayerNorm backward of acc (internal preset: cnx_mlp_bwd_dconv) */
 } cnx_epilogue;
 
 /* One entry of the host-generated MixUp/CutMix plan (see cnx_mix_batch). 32 bytes. */
@@ -99,7 +100,9 @@ int cnx_prep_block_weights(const float* conv_dw_w, const float* norm_w, const fl
                            const float* gamma, float* wt_dw /*[49][C]*/, void* w1f /*[4C][C] bf16*/,
                            void* w1fT /*[C][4C] bf16*/, float* b1f /*[4C]*/,
                            void* w2f /*[C][4C] bf16*/, void* w2fT /*[4C][C] bf16*/,
-                           float* b2f /*[C]*/, int C, void* stream);
+                           float* b2f /*[C]*/,
+                           float* rb /*[4C][2]: (rowsum of the bf16 w1f row, -b1f), may be NULL*/,
+                           int C, void* stream);
 
 /* Adjoint of cnx_prep_block_weights: gradients of the folded tensors -> gradients of the timm
  * parameters (d_fc1_b equals db1f and d_conv_dw_b equals dbias of cnx_dwconv_ln_bwd). */
@@ -250,6 +253,25 @@ int cnx_fc2_residual_fwd(const void* h, const void* w2f, const float* b2f, const
 /* dz = (dy @ w2f) * gelu'(z) ([M,4C] bf16); db1f[4C] (zero-filled by caller) += column sums. */
 int cnx_mlp_bwd_dz(const void* dy, const void* w2fT, const void* z, void* dz, float* db1f, int M,
                    int C, void* stream);
+/* LayerNorm backward WITHOUT a pass over dxhat (round 2).  dxhat = dz @ w1f and z = xhat @ w1f^T +
+ * b1f, hence per token m
+ *     s1[m] = sum_c dxhat[m,c]             = dz[m,:] . rowsum(w1f)
+ *     s2[m] = sum_c dxhat[m,c] * xhat[m,c] = dz[m,:] . (z[m,:] - b1f)
+ * cnx_mlp_bwd_dz_stats = cnx_mlp_bwd_dz that also accumulates rowstats[m] = (s1, s2) ([M][2] fp32,
+ * zero-filled by the caller) in its epilogue; `rb` [4C][2] fp32 = (rowsum of the bf16 w1f row, -b1f),
+ * written by cnx_prep_block_weights.  cnx_mlp_bwd_dconv = the fc1 data-gradient GEMM whose epilogue
+ * applies  dconv = rstd * (dxhat - s1/C - xhat * s2/C)  ([M,C] bf16): the gradient of the depthwise
+ * conv output, ready for cnx_dwconv_bwd.  Replaces cnx_mlp_bwd_dxhat + the LayerNorm-backward half
+ * of cnx_dwconv_ln_bwd for every channel count. */
+int cnx_mlp_bwd_dz_stats(const void* dy, const void* w2fT, const void* z, const float* rb, void* dz,
+                         float* db1f, float* rowstats, int M, int C, void* stream);
+int cnx_mlp_bwd_dconv(const void* dz, const void* w1fT, const void* xhat, const float* rowstats,
+                      const float* rstd, void* dconv, int M, int C, void* stream);
+/* Depthwise 7x7 conv backward alone (the conv half of cnx_dwconv_ln_bwd): dx = dy + conv^T(dconv),
+ * dwt[49,C], dbias[C], dy_colsum[C] overwritten (accumulate = 0) or += (accumulate != 0). */
+int cnx_dwconv_bwd(const void* dconv, const void* x, const void* dy, const float* wt_dw, void* dx,
+                   float* dwt, float* dbias, float* dy_colsum, int B, int H, int W, int C,
+                   int accumulate, void* stream);
 /* dxhat = dz @ w1f   ([M,C] bf16). */
 int cnx_mlp_bwd_dxhat(const void* dz, const void* w1fT, void* dxhat, int M, int C, void* stream);
 /* dw2f[C,4C] += dy^T @ h ; dw1f[4C,C] += dz^T @ xhat   (fp32; always accumulated: zero-fill or keep

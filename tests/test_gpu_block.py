@@ -340,3 +340,74 @@ def test_block_sub_batched_path_equals_single_pass(cnx_lib, monkeypatch):
     assert torch.equal(y0, y1) and torch.equal(dx0, dx1)        # per-sample arithmetic is the same
     for n in g0:
         assert _rel(g1[n], g0[n]) < 1e-4, n                      # sums in a different order
+
+
+def test_block_backward_ln_by_linearity_route(cnx_lib, monkeypatch):
+    """CNX_LNBWD_LINEARITY=1 (block.py): the block's backward with the LayerNorm backward taken in
+    the GEMM epilogues gives the row-kernel route's gradients within bf16 rounding."""
+    from image_classification_b200.block import ConvNeXtBlockB200
+    dev = _dev()
+    torch.manual_seed(6)
+    blk = ConvNeXtBlockB200(256).to(dev)
+    with torch.no_grad():
+        blk.gamma.copy_(torch.rand(256, device=dev) * 0.9 + 0.1)
+    x = torch.randn(4, 256, 14, 14, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    gy = torch.randn_like(x)
+    outs = []
+    for v in ("0", "1"):
+        monkeypatch.setenv("CNX_LNBWD_LINEARITY", v)
+        blk.zero_grad(set_to_none=True)
+        xi = x.clone().requires_grad_()
+        blk(xi).backward(gy)
+        outs.append((xi.grad, {n: p.grad.clone() for n, p in blk.named_parameters()}))
+    (dx0, g0), (dx1, g1) = outs
+    assert _rel(dx1, dx0.double()) < BF16_REL
+    for n in g0:
+        assert _rel(g1[n], g0[n].double()) < BF16_REL, n
+
+
+@pytest.mark.parametrize("shape", [(2, 9, 11, 64), (1, 14, 14, 128), (1, 12, 12, 256), (2, 14, 14, 512),
+                                   (1, 7, 7, 1024), (1, 24, 20, 192)])
+def test_ln_backward_by_linearity_matches_row_kernel_and_fp64(cnx_lib, shape):
+    """cnx_mlp_bwd_dz_stats + cnx_mlp_bwd_dconv (LayerNorm backward from row sums taken in the dz
+    GEMM's epilogue, applied in the fc1 data-gradient GEMM's epilogue) against the fp64 formula and
+    against the round-1 sequence (dxhat GEMM -> row kernel)."""
+    from image_classification_b200 import ops
+    B, H, W, C = shape
+    M = B * H * W
+    dev = _dev()
+    torch.manual_seed(C + H)
+    xhat = torch.randn(M, C, device=dev)
+    xhat = _bf((xhat - xhat.mean(1, keepdim=True)) / xhat.std(1, unbiased=False, keepdim=True))
+    w1 = torch.randn(4 * C, C, device=dev) * 0.08
+    params = [torch.randn(C, 1, 7, 7, device=dev), torch.rand(C, device=dev) + 0.5,
+              torch.randn(C, device=dev) * 0.1, w1, torch.randn(4 * C, device=dev) * 0.1,
+              torch.randn(C, 4 * C, device=dev) * 0.05, torch.randn(C, device=dev) * 0.1,
+              torch.rand(C, device=dev)]
+    fw = ops.prep_block_weights(*params)
+    w1f = fw.w1f.double()
+    assert _rel(fw.rb[:, 0], w1f.sum(1)) < 1e-5 and torch.equal(fw.rb[:, 1], -fw.b1f)
+    z, _h = ops.fc1_gelu_fwd(xhat.bfloat16(), fw.w1f, fw.b1f)
+    dy = _bf(torch.randn(M, C, device=dev) * 0.1).bfloat16()
+    rstd = torch.rand(M, device=dev) + 0.5
+    dz, db1f, stats = ops.mlp_bwd_dz_stats(dy, fw.w2fT, z, fw.rb)
+    dz_old, db1f_old = ops.mlp_bwd_dz(dy, fw.w2fT, z)
+    assert torch.equal(dz, dz_old) and _rel(db1f, db1f_old) < 1e-5
+    dxhat64 = dz.double() @ w1f                                  # what the GEMM accumulates
+    s1, s2 = dxhat64.sum(1), (dxhat64 * xhat.double()).sum(1)
+    scale = dxhat64.abs().sum(1).max()
+    assert float((stats[:, 0].double() - s1).abs().max() / scale) < 1e-5
+    # s2 is taken from the bf16-rounded z: a 2^-9 perturbation per term of a 4C-term sum
+    assert float((stats[:, 1].double() - s2).abs().max() / (dxhat64.abs() * xhat.double().abs()).sum(1).max()) < 4e-3
+    dconv = ops.mlp_bwd_dconv(dz, fw.w1fT, xhat.bfloat16(), stats, rstd)
+    ref = rstd.double()[:, None] * (dxhat64 - s1[:, None] / C - xhat.double() * s2[:, None] / C)
+    assert _rel(dconv, ref) < BF16_REL
+    # the round-1 sequence on the same inputs: both within bf16 tolerance of fp64, and of each other
+    dxhat = ops.mlp_bwd_dxhat(dz, fw.w1fT)
+    x = _bf(torch.randn(B, H, W, C, device=dev)).bfloat16()
+    dx_old, dwt_old, dbias_old, dycs_old = ops.dwconv_ln_bwd(
+        dxhat.view(B, H, W, C), xhat.bfloat16().view(B, H, W, C), rstd, x, dy.view(B, H, W, C), fw.wt_dw)
+    dx_new, dwt_new, dbias_new, dycs_new = ops.dwconv_bwd(dconv.view(B, H, W, C), x, dy.view(B, H, W, C), fw.wt_dw)
+    assert _rel(dx_new, dx_old.double()) < BF16_REL
+    assert _rel(dwt_new, dwt_old.double()) < BF16_REL and _rel(dbias_new, dbias_old.double()) < BF16_REL
+    assert _rel(dycs_new, dycs_old.double()) < 1e-5
