@@ -93,6 +93,8 @@ SIGNATURES = {
     "cnx_ema_lerp_multi": (I, [P, P, P, P, I, I64, F, F, P]),
     "cnx_ema_chunk_elems": (I, []),
     "cnx_optim_grad_norm": (I, [P, P, P, I, I64, P, F, P, P, P]),
+    "cnx_optim_grad_norm_noalloc": (I, [P, P, P, I, I64, P, F, P, P]),
+    "cnx_optim_grad_norm_noalloc_max_chunks": (I, []),
     "cnx_optim_adamw_ema": (I, [P, P, P, P, P, P, P, I, I64, F, F, F, F, F, F, F, P, P]),
     "cnx_nchw_f32_to_nhwc_bf16": (I, [P, P, I, I, I, I, P]),
     "cnx_nhwc_bf16_to_nchw_f32": (I, [P, P, I, I, I, I, P]),
@@ -135,7 +137,7 @@ LAUNCHES_PER_CALL = {
     "cnx_prep_block_weights": 1, "cnx_unfold_block_grads": 2, "cnx_dwconv_ln_fwd": 2,
     "cnx_dwconv_ln_bwd": 2, "cnx_dwconv_ln_bwd_acc": 2, "cnx_gemm_bf16": 1, "cnx_layernorm_fwd": 1, "cnx_layernorm_bwd": 1, "cnx_colsum_bf16": 1, "cnx_dwconv_kxk_fwd": 1, "cnx_dwconv_kxk_bwd": 2, "cnx_avgpool_nhwc_fwd": 1, "cnx_avgpool_nhwc_bwd": 1, "cnx_layernorm_patch_fwd": 1, "cnx_layernorm_patch_bwd": 1, "cnx_patchify_nchw_f32": 1, "cnx_fc1_gelu_fwd": 1, "cnx_fc2_residual_fwd": 1,
     "cnx_mlp_bwd_dz": 1, "cnx_mlp_bwd_dxhat": 1, "cnx_mlp_bwd_dz_stats": 1, "cnx_mlp_bwd_dconv": 1, "cnx_dwconv_bwd": 1, "cnx_mlp_bwd_wgrad": 2, "cnx_mix_batch": 1, "cnx_mix_batch_smooth": 1,
-    "cnx_softce_fwd_bwd": 1, "cnx_ema_lerp_multi": 1, "cnx_optim_grad_norm": 1, "cnx_optim_adamw_ema": 1, "cnx_nchw_f32_to_nhwc_bf16": 1,
+    "cnx_softce_fwd_bwd": 1, "cnx_ema_lerp_multi": 1, "cnx_optim_grad_norm": 1, "cnx_optim_grad_norm_noalloc": 1, "cnx_optim_adamw_ema": 1, "cnx_nchw_f32_to_nhwc_bf16": 1,
     "cnx_nhwc_bf16_to_nchw_f32": 1,
     "cnx_bn_stats": 1, "cnx_bn_act_fwd": 1, "cnx_bn_act_bwd": 2, "cnx_se_scale_fwd": 1,
     "cnx_se_scale_bwd_reduce": 1, "cnx_se_scale_bwd_apply": 1, "cnx_se_gate_fwd": 2,

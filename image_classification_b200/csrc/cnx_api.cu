@@ -406,6 +406,18 @@ int cnx_optim_grad_norm(const void* const* grad_ptrs, const int64_t* numels,
                          max_norm, partials, state, as_stream(stream));
 }
 
+int cnx_optim_grad_norm_noalloc(const void* const* grad_ptrs, const int64_t* numels,
+                                const int64_t* chunk_prefix, int num_tensors, int64_t total_chunks,
+                                const float* scale, float max_norm, float* state, void* stream) {
+  CNX_REQUIRE_DEVICE();
+  CNX_REQUIRE_PTR(grad_ptrs); CNX_REQUIRE_PTR(numels); CNX_REQUIRE_PTR(chunk_prefix);
+  CNX_REQUIRE_PTR(state);
+  return optim_grad_norm_static(grad_ptrs, numels, chunk_prefix, num_tensors, total_chunks, scale,
+                                max_norm, state, as_stream(stream));
+}
+
+int cnx_optim_grad_norm_noalloc_max_chunks(void) { return kStaticNormChunks; }
+
 int cnx_optim_adamw_ema(void* const* param_ptrs, const void* const* grad_ptrs, void* const* m_ptrs,
                         void* const* v_ptrs, void* const* shadow_ptrs, const int64_t* numels,
                         const int64_t* chunk_prefix, int num_tensors, int64_t total_chunks,

@@ -121,6 +121,12 @@ int optim_grad_norm(const void* const* grad_ptrs, const int64_t* numels,
                     const int64_t* chunk_prefix, int num_tensors, int64_t total_chunks,
                     const float* scale, float max_norm, float* partials, float* state,
                     cudaStream_t stream);
+// Allocation-free variant: the per-chunk partial sums live in a file-scope __device__ array of
+// kStaticNormChunks floats (optim.cu) instead of a caller buffer.
+constexpr int kStaticNormChunks = 65536;      // 256 KiB; 65536 chunks x 8192 = 536 870 912 elements
+int optim_grad_norm_static(const void* const* grad_ptrs, const int64_t* numels,
+                           const int64_t* chunk_prefix, int num_tensors, int64_t total_chunks,
+                           const float* scale, float max_norm, float* state, cudaStream_t stream);
 int optim_adamw_ema(void* const* param_ptrs, const void* const* grad_ptrs, void* const* m_ptrs,
                     void* const* v_ptrs, void* const* shadow_ptrs, const int64_t* numels,
                     const int64_t* chunk_prefix, int num_tensors, int64_t total_chunks, float lr,

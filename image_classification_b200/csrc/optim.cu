@@ -13,6 +13,8 @@
 //                                           arithmetic), EMA lerp of the NEW parameter
 // Tensors are addressed through device pointer tables cut into 8192-element chunks, like
 // ema_lerp_multi (elementwise.cu).
+#include <mutex>
+
 #include "cnx_common.cuh"
 #include "cnx_kernels.h"
 
@@ -217,6 +219,64 @@ int optim_grad_norm(const void* const* grad_ptrs, const int64_t* numels,
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_last_error("optim_grad_norm launch: %s", cudaGetErrorString(e));
+    return CNX_ERR_LAUNCH;
+  }
+  return CNX_OK;
+}
+
+// ---------------------------------------------------------------- allocation-free variant
+// The per-chunk partial sums of grad_norm_kernel in library-owned memory instead of a caller
+// buffer.  kStaticNormChunks floats (256 KiB) are held by every device that loads the library, from
+// module load until exit.  grad_norm_kernel writes partials[i] for every i < total_chunks before
+// the last CTA reads any of them, so nothing in the array has to start at zero and a call does not
+// depend on what the previous call left there; two calls that overlap on the GPU (different
+// streams) race on it.
+static __device__ __align__(256) float g_static_norm_partials[kStaticNormChunks];
+
+namespace {
+std::mutex g_static_mu;
+float* g_static_partials_addr[64] = {};      // per device slot: DEVICE address of the array above
+}  // namespace
+
+int optim_grad_norm_static(const void* const* grad_ptrs, const int64_t* numels,
+                           const int64_t* chunk_prefix, int num_tensors, int64_t total_chunks,
+                           const float* scale, float max_norm, float* state, cudaStream_t stream) {
+  int rc = check_table("optim_grad_norm_static", num_tensors, total_chunks);
+  if (rc != CNX_OK) return rc;
+  if (total_chunks > kStaticNormChunks) {
+    set_last_error("optim_grad_norm_static: %lld chunks of %d elements exceed the static scratch "
+                   "(max %d chunks = %lld elements incl. per-tensor round-up); use "
+                   "cnx_optim_grad_norm with a caller buffer",
+                   static_cast<long long>(total_chunks), kEmaChunkElems, kStaticNormChunks,
+                   static_cast<long long>(kStaticNormChunks) * kEmaChunkElems);
+    return CNX_ERR_BAD_ARG;
+  }
+  if (state == nullptr) {
+    set_last_error("optim_grad_norm_static: state (float[8]) required");
+    return CNX_ERR_BAD_ARG;
+  }
+  // In host code `g_static_norm_partials` is a host-side stand-in, not a device address: resolve it
+  // once per device, with that device current (it is: the caller's pointers live on it).
+  const int slot = current_device_slot();
+  float* partials = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    partials = g_static_partials_addr[slot];
+    if (partials == nullptr) {
+      void* addr = nullptr;
+      cudaError_t e = cudaGetSymbolAddress(&addr, g_static_norm_partials);
+      if (e != cudaSuccess || addr == nullptr) {
+        set_last_error("optim_grad_norm_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        return CNX_ERR_LAUNCH;
+      }
+      partials = g_static_partials_addr[slot] = static_cast<float*>(addr);
+    }
+  }
+  grad_norm_kernel<<<static_cast<unsigned>(total_chunks), kOptThreads, 0, stream>>>(
+      grad_ptrs, numels, chunk_prefix, num_tensors, scale, max_norm, partials, state);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_last_error("optim_grad_norm_static launch: %s", cudaGetErrorString(e));
     return CNX_ERR_LAUNCH;
   }
   return CNX_OK;

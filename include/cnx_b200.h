@@ -322,6 +322,24 @@ int cnx_optim_grad_norm(const void* const* grad_ptrs, const int64_t* numels,
                         const int64_t* chunk_prefix, int num_tensors, int64_t total_chunks,
                         const float* scale, float max_norm, float* partials, float* state,
                         void* stream);
+/* cnx_optim_grad_norm without a caller-provided `partials` buffer and without any allocation.
+ * NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid
+ * it).  The per-chunk partial sums go to a file-scope `static __device__ __align__(256)` array of
+ * cnx_optim_grad_norm_noalloc_max_chunks() = 65536 floats (256 KiB), which every GPU that loads the
+ * library holds until the process exits; its device address is resolved with cudaGetSymbolAddress
+ * once per device on the first call (that device current).  The call performs no cudaMalloc /
+ * cudaFree / allocating library routine.  total_chunks > 65536 (more than 536 870 912 gradient
+ * elements incl. the per-tensor round-up to 8192) -> CNX_ERR_BAD_ARG with a message naming the
+ * limit; use cnx_optim_grad_norm then.  All calls on a device SHARE the array and it keeps the
+ * last call's contents: every slot a call reads is written by that call first, so nothing needs
+ * clearing, but two calls that overlap on the GPU (different streams without an ordering edge)
+ * race — keep them on one stream or order them with events.  Everything else (arguments, `state`
+ * contract, results bit for bit) is cnx_optim_grad_norm's. */
+int cnx_optim_grad_norm_noalloc(const void* const* grad_ptrs, const int64_t* numels,
+                                const int64_t* chunk_prefix, int num_tensors, int64_t total_chunks,
+                                const float* scale, float max_norm, float* state, void* stream);
+int cnx_optim_grad_norm_noalloc_max_chunks(void);
 int cnx_optim_adamw_ema(void* const* param_ptrs, const void* const* grad_ptrs, void* const* m_ptrs,
                         void* const* v_ptrs, void* const* shadow_ptrs, const int64_t* numels,
                         const int64_t* chunk_prefix, int num_tensors, int64_t total_chunks,
