@@ -39,20 +39,25 @@ constexpr int BM = 128;
 constexpr int BK = 64;                 // 64 bf16 = 128 B = one swizzle row
 constexpr int kDuos = 8;               // (TMEM lane quarter, column half) pairs = staging buffer pairs
 constexpr int EPI_ATOMIC_F32 = 5;      // internal: split-K fp32 reduction
-constexpr uint32_t kChunkBytes = 32 * 128;   // staging chunk: 32 rows x 64 bf16, 128B swizzle
 
 // PAIR: two CTAs (a cluster of 2 on one TPC) share a 256 x BN tile through cta_group::2 MMAs; each
 // stages its own 128 rows of A and HALF of B, which halves the B bytes written into and read out
 // of every SM's shared memory (ncu on the single-CTA kernel: tensor pipe capped near 63 % because
 // TMA writes + MMA operand reads exceed the 128 B/clk shared-memory port).
-template <int BN, bool PAIR, bool STAGED>
+// CW = columns of one staging chunk (a 32-row x CW bf16 box of the output, per epilogue warp):
+// 64 (128B swizzle) or 32 (64B swizzle).  Every GEMM here is paced by operand bytes in flight
+// towards L2 (ring depth sweep, DESIGN.md 3.2: 3 / 4 / 5 / 6 stages = 62 / 56 / 52 / 50 us for the
+// stage-3 fc1 data-gradient), so the epilogues that need no residual operand stage through half-size
+// chunks and give the freed 32 KB to a sixth operand stage.
+template <int BN, bool PAIR, bool STAGED, int CW = 64>
 struct Cfg {
   static constexpr int kTileM = PAIR ? 2 * BM : BM;
   static constexpr int kBRows = PAIR ? BN / 2 : BN;      // rows of B staged by one CTA
   static constexpr uint32_t kABytes = BM * BK * 2;
   static constexpr uint32_t kBBytes = kBRows * BK * 2;
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
-  // bf16 epilogues stage through shared memory (64 KB); the fp32 reduction epilogue does not
+  static constexpr uint32_t kChunkBytes = 32 * CW * 2;
+  // bf16 epilogues stage through shared memory; the fp32 reduction epilogue does not
   static constexpr uint32_t kEpiBytes = STAGED ? kDuos * 2 * kChunkBytes : 0;
   static constexpr uint32_t kBarBytes = 512;
   static constexpr uint32_t kSmemMax = 232448;           // 227 KB opt-in limit per CTA
@@ -62,6 +67,7 @@ struct Cfg {
   static constexpr uint32_t kTotal = kStages * kStageBytes + kEpiBytes + kBarBytes + 1024;
   static constexpr uint32_t kTmemCols = 2 * BN;
   static_assert(kStages >= 3, "operand ring too shallow");
+  static_assert(CW == 64 || CW == 32, "staging chunks are 64 or 32 columns wide");
 };
 
 struct GemmTuning { int stages = -1, pair = -1, bn = -1, splits = -1, epi_warps = 0; };
@@ -182,17 +188,19 @@ __device__ __forceinline__ ItemCoord decode(const Gemm2Params& p, int w) {
 // staging buffers through a 64-thread named barrier).  The GELU-carrying epilogues are latency-
 // bound with 2 warps per scheduler (ncu r01: issue slots 37 % busy, tensor pipe 40 %); 4 warps
 // per scheduler hide the tcgen05.ld / shared-memory / polynomial latencies.
-template <int BN, int EPI, bool PAIR, int EW>
+template <int BN, int EPI, bool PAIR, int EW, int CW = 64>
 __global__ void __launch_bounds__(64 + 32 * EW, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
              const __grid_constant__ CUtensorMap map_d0, const __grid_constant__ CUtensorMap map_d1,
              const __grid_constant__ CUtensorMap map_r, const Gemm2Params p) {
-  using L = Cfg<BN, PAIR, !(EPI == EPI_STORE_F32 || EPI == EPI_ATOMIC_F32)>;
+  using L = Cfg<BN, PAIR, !(EPI == EPI_STORE_F32 || EPI == EPI_ATOMIC_F32), CW>;
   constexpr int kStages = L::kStages;
   constexpr int kTileM = L::kTileM;
+  constexpr uint32_t kChunkBytes = L::kChunkBytes;
+  static_assert(CW == 64 || EW == 8, "32-column staging chunks: 8-warp epilogue only");
   constexpr bool kHasR = (EPI == EPI_BIAS_RESIDUAL || EPI == EPI_GELU_GRAD || EPI == EPI_LN_BWD);
   constexpr bool kF32Out = (EPI == EPI_STORE_F32 || EPI == EPI_ATOMIC_F32);
-  constexpr int kChunks = BN / 2 / 64;         // 64-column chunks per epilogue warp per tile
+  constexpr int kChunks = BN / 2 / CW;         // staging chunks per epilogue warp per tile
 
   extern __shared__ unsigned char smem_dyn[];
   // 1024-byte alignment: the 128B swizzle pattern is a function of address bits [7,10)
@@ -542,12 +550,17 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
     unsigned char* buf0 = epi_base + ew * 2 * kChunkBytes;   // output staging (D0)
     unsigned char* buf1 = buf0 + kChunkBytes;                // D1 staging or R landing zone
     const uint32_t buf0_u = smem_u32(buf0), buf1_u = smem_u32(buf1);
-    const uint32_t row_off = static_cast<uint32_t>(lane) * 128u;
-    const uint32_t sw = static_cast<uint32_t>(lane & 7);
+    // staging rows are CW bf16 wide; 16-byte units are XOR-swizzled like the TMA box (128B swizzle:
+    // unit ^ (row & 7), 64B swizzle: unit ^ ((row >> 1) & 3)) so the row-per-lane stores and loads
+    // are bank-conflict-free
+    constexpr int kSubs = CW / 32;             // 32-column TMEM reads per chunk
+    constexpr uint32_t kRowBytes = CW * 2;
+    const uint32_t row_off = static_cast<uint32_t>(lane) * kRowBytes;
+    const uint32_t sw = (CW == 64) ? static_cast<uint32_t>(lane & 7) : static_cast<uint32_t>((lane >> 1) & 3);
     uint64_t* rbar = &r_bar[ew];
     uint32_t r_jobs = 0;                       // R chunks consumed so far (phase of rbar)
 
-    auto chunk_n = [&](const ItemCoord& c, int ch) { return c.n_blk * BN + half * (BN / 2) + ch * 64; };
+    auto chunk_n = [&](const ItemCoord& c, int ch) { return c.n_blk * BN + half * (BN / 2) + ch * CW; };
     // first valid (n < N) chunk at or after (w, ch); w >= items when none is left
     auto next_valid = [&](int& w, int& ch) {
       while (w < p.items) {
@@ -578,7 +591,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
       if (EPI == EPI_GELU_GRAD && p.colsum != nullptr && cs_nblk >= 0) {
 #pragma unroll
         for (int ch = 0; ch < kChunks; ++ch) {
-          const int n = cs_nblk * BN + half * (BN / 2) + ch * 64 + 2 * lane;
+          // CW == 32: lanes l and l ^ 16 hold partial sums (even / odd rows) of the same columns
+          const int n = cs_nblk * BN + half * (BN / 2) + ch * CW + 2 * (lane & (CW / 2 - 1));
           if (n < p.N) {
             atomicAdd(p.colsum + n, cs_acc[ch].x);
             atomicAdd(p.colsum + n + 1, cs_acc[ch].y);
@@ -623,9 +637,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
         if (kF32Out) {
           const int row = row0 + lane;
 #pragma unroll
-          for (int sub = 0; sub < 2; ++sub) {
+          for (int sub = 0; sub < kSubs; ++sub) {
             uint32_t v[32];
-            tmem_ld_32x32(tmem_acc + ch * 64 + sub * 32, v);
+            tmem_ld_32x32(tmem_acc + ch * CW + sub * 32, v);
             tmem_ld_wait();
             const int n = n_g + sub * 32;
             if (row < p.M) {
@@ -652,9 +666,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
         }
 
 #pragma unroll
-        for (int sub = 0; sub < 2; ++sub) {
+        for (int sub = 0; sub < kSubs; ++sub) {
           uint32_t v[32];
-          tmem_ld_32x32(tmem_acc + ch * 64 + sub * 32, v);
+          tmem_ld_32x32(tmem_acc + ch * CW + sub * 32, v);
           uint32_t rr[16];
           if (kHasR) {
 #pragma unroll
@@ -766,13 +780,27 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
           // column sums of the ROUNDED dz (what the weight-gradient GEMM will consume): lane l
           // owns columns 2l, 2l+1 of this chunk; 32 conflict-free word reads down the rows
           // (rows past M hold acc = 0 -> contribute nothing)
-          const uint32_t cchunk = static_cast<uint32_t>(lane >> 2), cword = static_cast<uint32_t>(lane & 3);
           float2 s = cs_acc[ch];
+          if (CW == 64) {
+            const uint32_t cchunk = static_cast<uint32_t>(lane >> 2), cword = static_cast<uint32_t>(lane & 3);
 #pragma unroll
-          for (int r = 0; r < 32; ++r) {
-            const float2 t2 = bf16x2_to_f32x2(
-                ld_shared_b32(buf0_u + r * 128 + ((cchunk ^ (r & 7)) << 4) + (cword << 2)));
-            s = fadd2(s, t2);
+            for (int r = 0; r < 32; ++r) {
+              const float2 t2 = bf16x2_to_f32x2(
+                  ld_shared_b32(buf0_u + r * 128 + ((cchunk ^ (r & 7)) << 4) + (cword << 2)));
+              s = fadd2(s, t2);
+            }
+          } else {
+            // 64-byte rows: lanes 0-15 walk the even rows, lanes 16-31 the odd rows (one 128-byte
+            // line per step, conflict-free); lane & 15 -> columns 2 (lane & 15), +1
+            const uint32_t cchunk = static_cast<uint32_t>((lane & 15) >> 2), cword = static_cast<uint32_t>(lane & 3);
+            const int rpar = lane >> 4;
+#pragma unroll
+            for (int i2 = 0; i2 < 16; ++i2) {
+              const int r = 2 * i2 + rpar;
+              const float2 t2 = bf16x2_to_f32x2(
+                  ld_shared_b32(buf0_u + r * 64 + ((cchunk ^ (i2 & 3)) << 4) + (cword << 2)));
+              s = fadd2(s, t2);
+            }
           }
           cs_acc[ch] = s;
         }
@@ -805,17 +833,17 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
   }
 }
 
-template <int BN, int EPI, bool PAIR, int EW>
+template <int BN, int EPI, bool PAIR, int EW, int CW = 64>
 int launch2(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md0,
             const CUtensorMap& md1, const CUtensorMap& mr, const Gemm2Params& p_in, int grid,
             cudaStream_t stream) {
-  using L = Cfg<BN, PAIR, !(EPI == EPI_STORE_F32 || EPI == EPI_ATOMIC_F32)>;
+  using L = Cfg<BN, PAIR, !(EPI == EPI_STORE_F32 || EPI == EPI_ATOMIC_F32), CW>;
   Gemm2Params p = p_in;
   p.stages = (g_tune.stages >= 2 && g_tune.stages < L::kStages) ? g_tune.stages : L::kStages;
-  const int rc_attr = ensure_dyn_smem(gemm2_kernel<BN, EPI, PAIR, EW>, L::kTotal, "gemm_bf16");
+  const int rc_attr = ensure_dyn_smem(gemm2_kernel<BN, EPI, PAIR, EW, CW>, L::kTotal, "gemm_bf16");
   if (rc_attr != CNX_OK) return rc_attr;
-  cudaError_t e = launch_pdl(gemm2_kernel<BN, EPI, PAIR, EW>, grid, 64 + 32 * EW, L::kTotal, stream,
-                             PAIR ? 2u : 1u, ma, mb, md0, md1, mr, p);
+  cudaError_t e = launch_pdl(gemm2_kernel<BN, EPI, PAIR, EW, CW>, grid, 64 + 32 * EW, L::kTotal,
+                             stream, PAIR ? 2u : 1u, ma, mb, md0, md1, mr, p);
   if (e != cudaSuccess) {
     set_last_error("gemm_bf16 launch: %s", cudaGetErrorString(e));
     return CNX_ERR_LAUNCH;
@@ -824,17 +852,23 @@ int launch2(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md0
 }
 
 template <int BN, bool PAIR>
-int dispatch(int epi, int ew, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md0,
+int dispatch(int epi, int ew, bool narrow, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md0,
              const CUtensorMap& md1, const CUtensorMap& mr, const Gemm2Params& p, int grid,
              cudaStream_t stream) {
 #define CNX_GEMM_CASE(E)                                                                   \
   case E:                                                                                  \
     return ew == 16 ? launch2<BN, E, PAIR, 16>(ma, mb, md0, md1, mr, p, grid, stream)      \
                     : launch2<BN, E, PAIR, 8>(ma, mb, md0, md1, mr, p, grid, stream);
+  // epilogues without a residual operand: 32-column staging chunks with 8 warps (one more stage)
+#define CNX_GEMM_CASE_NARROW(E)                                                            \
+  case E:                                                                                  \
+    return ew == 16 ? launch2<BN, E, PAIR, 16>(ma, mb, md0, md1, mr, p, grid, stream)      \
+           : narrow ? launch2<BN, E, PAIR, 8, 32>(ma, mb, md0, md1, mr, p, grid, stream)   \
+                    : launch2<BN, E, PAIR, 8>(ma, mb, md0, md1, mr, p, grid, stream);
   switch (epi) {
-    CNX_GEMM_CASE(EPI_STORE_BF16)
-    CNX_GEMM_CASE(EPI_BIAS)
-    CNX_GEMM_CASE(EPI_BIAS_GELU)
+    CNX_GEMM_CASE_NARROW(EPI_STORE_BF16)
+    CNX_GEMM_CASE_NARROW(EPI_BIAS)
+    CNX_GEMM_CASE_NARROW(EPI_BIAS_GELU)
     CNX_GEMM_CASE(EPI_BIAS_RESIDUAL)
     CNX_GEMM_CASE(EPI_GELU_GRAD)
     case EPI_LN_BWD:     return launch2<BN, EPI_LN_BWD, PAIR, 8>(ma, mb, md0, md1, mr, p, grid, stream);
@@ -843,6 +877,7 @@ int dispatch(int epi, int ew, const CUtensorMap& ma, const CUtensorMap& mb, cons
     default: break;
   }
 #undef CNX_GEMM_CASE
+#undef CNX_GEMM_CASE_NARROW
   set_last_error("gemm_bf16: unsupported epilogue %d", epi);
   return CNX_ERR_BAD_ARG;
 }
@@ -1020,6 +1055,22 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   if (splits > 1) workers = p.items < units ? p.items : units;
   const int grid = pair ? 2 * workers : workers;
 
+  // 16 epilogue warps measured (profiles/r02_microbench_epi_warps_*.json): fc1+GELU 176 -> 170 us
+  // and 96 -> 94 us at K = 128 / 256 (stages 1-2, HBM-bound: more stores in flight), no change at
+  // K >= 512, GELU' (dz) 2 us SLOWER everywhere: so only the short-K fc1 uses them.
+  // cnx_debug_gemm_epilogue_warps() forces 8 or 16 for every bf16 epilogue (A/B measurements)
+  int ew = (epi == EPI_BIAS_GELU && a.K <= 256) ? 16 : 8;
+  if (g_tune.epi_warps != 0) ew = g_tune.epi_warps;
+  if (epi == EPI_LN_BWD || (epi == EPI_GELU_GRAD && a.rowstats != nullptr)) ew = 8;   // 8-warp path only
+  // Narrow staging chunks (one more operand stage) for the 8-warp epilogues that read no residual
+  // operand: measured (tools/gpu_ring.sh) fc1+GELU at K = 512 67.6 -> 62.5 us, fc1 data-gradient
+  // 51.9 -> 50.0 us; with a residual operand the 2 KB loads one chunk ahead no longer cover their
+  // latency (GELU-gradient 72 -> 84 us), so those keep 64-column chunks.  CNX_GEMM_WIDE_CHUNKS=1
+  // forces 64 everywhere (A/B switch).
+  static const bool wide_chunks = getenv("CNX_GEMM_WIDE_CHUNKS") != nullptr;
+  const bool narrow = !wide_chunks && ew == 8 &&
+                      (epi == EPI_STORE_BF16 || epi == EPI_BIAS || epi == EPI_BIAS_GELU);
+
   CUtensorMap ma, mb, md0, md1, mr;
   int rc;
   {
@@ -1045,11 +1096,12 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
     if (rc != CNX_OK) return rc;
   }
   // epilogue maps: [M][N] bf16 row-major, box 64 cols x 32 rows, 128B swizzle (staging layout)
+  // (32 cols x 32 rows, 64B swizzle for the narrow-chunk epilogues)
   auto mn_map = [&](CUtensorMap* m, const void* base, int64_t ld) {
     const uint64_t dims[2] = {(uint64_t)a.N, (uint64_t)a.M};
     const uint64_t st[1] = {(uint64_t)ld * 2};
-    const uint32_t box[2] = {64, 32};
-    return make_tensor_map(m, base, 2, 2, dims, st, box, 3);
+    const uint32_t box[2] = {narrow ? 32u : 64u, 32};
+    return make_tensor_map(m, base, 2, 2, dims, st, box, narrow ? 2 : 3);
   };
   const bool f32_out = (epi == EPI_STORE_F32 || epi == EPI_ATOMIC_F32);
   md0 = ma; md1 = ma; mr = ma;    // placeholders for unused maps (never dereferenced)
@@ -1066,18 +1118,11 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
     if (rc != CNX_OK) return rc;
   }
 
-  // 16 epilogue warps measured (profiles/r02_microbench_epi_warps_*.json): fc1+GELU 176 -> 170 us
-  // and 96 -> 94 us at K = 128 / 256 (stages 1-2, HBM-bound: more stores in flight), no change at
-  // K >= 512, GELU' (dz) 2 us SLOWER everywhere: so only the short-K fc1 uses them.
-  // cnx_debug_gemm_epilogue_warps() forces 8 or 16 for every bf16 epilogue (A/B measurements)
-  int ew = (epi == EPI_BIAS_GELU && a.K <= 256) ? 16 : 8;
-  if (g_tune.epi_warps != 0) ew = g_tune.epi_warps;
-  if (epi == EPI_LN_BWD || (epi == EPI_GELU_GRAD && a.rowstats != nullptr)) ew = 8;   // 8-warp path only
   if (pair)
-    return BN == 256 ? dispatch<256, true>(epi, ew, ma, mb, md0, md1, mr, p, grid, stream)
-                     : dispatch<128, true>(epi, ew, ma, mb, md0, md1, mr, p, grid, stream);
-  return BN == 256 ? dispatch<256, false>(epi, ew, ma, mb, md0, md1, mr, p, grid, stream)
-                   : dispatch<128, false>(epi, ew, ma, mb, md0, md1, mr, p, grid, stream);
+    return BN == 256 ? dispatch<256, true>(epi, ew, narrow, ma, mb, md0, md1, mr, p, grid, stream)
+                     : dispatch<128, true>(epi, ew, narrow, ma, mb, md0, md1, mr, p, grid, stream);
+  return BN == 256 ? dispatch<256, false>(epi, ew, narrow, ma, mb, md0, md1, mr, p, grid, stream)
+                   : dispatch<128, false>(epi, ew, narrow, ma, mb, md0, md1, mr, p, grid, stream);
 }
 
 }  // namespace cnx
