@@ -20,11 +20,17 @@
 //                     128B-swizzled shared memory (conflict-free 16-byte stores) and written by TMA
 //                     (cp.async.bulk.tensor store: fully coalesced, clips ragged M / N edges);
 //                     residual / pre-activation operands arrive by TMA into the same staging
-//                     layout one chunk ahead of use.
+//                     layout one chunk ahead of use.  Staging chunks are 32 rows x 64 columns
+//                     (128B swizzle), or 32 x 32 (64B swizzle) for the epilogues without a second
+//                     operand: the 32 KB that frees go to one more operand stage.
+//                     Variants: 16 epilogue warps (two per staging pair) for the short-K fc1;
+//                     CTA pairs (cta_group::2, 256-row tiles, each CTA stages half of B).
 // A CTA keeps the same column block for its whole life whenever the tile grid allows it, so the
 // per-column sums of the GELU-gradient epilogue stay in registers (one atomic per column per CTA).
 // GELU and its derivative are degree-6/7 odd minimax polynomials evaluated with packed
-// fma.rn.f32x2 (|err| < 3e-4, below the bf16 output resolution): those epilogues are FMA-pipe-bound.
+// fma.rn.f32x2 (|err| < 3e-4, below the bf16 output resolution).  Measured: the
+// epilogue arithmetic is free; the loop is paced by operand bytes in flight per SM (ring depth),
+// and every byte the epilogue moves competes with the operand stream.
 // Operands may be K-major (row-major [rows,K]) or MN-major (stored [K,rows]); the latter is what
 // the weight-gradient GEMMs need (K = tokens), so no activation transpose ever touches HBM.
 #include "cnx_common.cuh"
