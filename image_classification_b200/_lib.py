@@ -53,6 +53,7 @@ SIGNATURES = {
     "cnx_debug_set_timeout_flag": (None, [I]),
     "cnx_debug_gemm_tuning": (None, [I, I, I, I]),
     "cnx_debug_gemm_epilogue_warps": (None, [I]),
+    "cnx_debug_gemm_staging_chunk": (None, [I]),
     "cnx_debug_max_clusters": (I, [I]),
     "cnx_workspace_bytes": (c_size_t, [I, I, I, I, I]),
     "cnx_prep_block_weights": (I, [P] * 8 + [P] * 8 + [I, P]),

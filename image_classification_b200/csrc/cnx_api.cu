@@ -41,6 +41,7 @@ void cnx_debug_gemm_tuning(int stages, int pair, int bn, int splits) {
   gemm_debug_tuning(stages, pair, bn, splits);
 }
 void cnx_debug_gemm_epilogue_warps(int n) { gemm_debug_epilogue_warps(n); }
+void cnx_debug_gemm_staging_chunk(int cols) { gemm_debug_staging_chunk(cols); }
 
 size_t cnx_workspace_bytes(int op, int B, int H, int W, int C) {
   if (op == CNX_OP_DWCONV_LN_BWD) return dwconv_ln_bwd_workspace_bytes(B, H, W, C);

@@ -96,7 +96,8 @@ struct GemmArgs {
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream);      // gemm2.cu (persistent, warp-specialised)
 int gemm_debug_max_clusters(int cluster_size);                      // gemm2.cu, occupancy probe
 void gemm_debug_tuning(int stages, int pair, int bn, int splits);   // gemm2.cu, -1 = automatic
-void gemm_debug_epilogue_warps(int n);                              // 8 / 16, 0 = automatic
+void gemm_debug_epilogue_warps(int n);
+void gemm_debug_staging_chunk(int cols);   // 64 = wide staging chunks everywhere, 0 = automatic                              // 8 / 16, 0 = automatic
 
 // ---- elementwise.cu
 struct MixPlanEntry {          // one per sample; integers are bit-exact vs the reference RNG order

@@ -76,7 +76,7 @@ struct Cfg {
   static_assert(CW == 64 || CW == 32, "staging chunks are 64 or 32 columns wide");
 };
 
-struct GemmTuning { int stages = -1, pair = -1, bn = -1, splits = -1, epi_warps = 0; };
+struct GemmTuning { int stages = -1, pair = -1, bn = -1, splits = -1, epi_warps = 0, chunk_cols = 0; };
 GemmTuning g_tune;                 // development overrides (cnx_debug_gemm_tuning)
 
 struct Gemm2Params {
@@ -940,6 +940,8 @@ void gemm_debug_tuning(int stages, int pair, int bn, int splits) {
 
 void gemm_debug_epilogue_warps(int n) { g_tune.epi_warps = (n == 8 || n == 16) ? n : 0; }
 
+void gemm_debug_staging_chunk(int cols) { g_tune.chunk_cols = (cols == 64) ? 64 : 0; }
+
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   if (a.M <= 0 || a.N <= 0 || a.K <= 0 || (a.N % 8) != 0 || (a.lda % 8) != 0 || (a.ldb % 8) != 0) {
     set_last_error("gemm_bf16: bad shape M=%d N=%d K=%d lda=%lld ldb=%lld (N, lda, ldb must be "
@@ -1072,8 +1074,9 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   // operand: measured (tools/gpu_ring.sh) fc1+GELU at K = 512 67.6 -> 62.5 us, fc1 data-gradient
   // 51.9 -> 50.0 us; with a residual operand the 2 KB loads one chunk ahead no longer cover their
   // latency (GELU-gradient 72 -> 84 us), so those keep 64-column chunks.  CNX_GEMM_WIDE_CHUNKS=1
-  // forces 64 everywhere (A/B switch).
-  static const bool wide_chunks = getenv("CNX_GEMM_WIDE_CHUNKS") != nullptr;
+  // or cnx_debug_gemm_staging_chunk(64) force 64 everywhere (A/B switch, parity tests).
+  static const bool wide_env = getenv("CNX_GEMM_WIDE_CHUNKS") != nullptr;
+  const bool wide_chunks = wide_env || g_tune.chunk_cols == 64;
   const bool narrow = !wide_chunks && ew == 8 &&
                       (epi == EPI_STORE_BF16 || epi == EPI_BIAS || epi == EPI_BIAS_GELU);
 

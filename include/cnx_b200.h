@@ -85,6 +85,10 @@ void cnx_debug_gemm_tuning(int stages, int pair, int bn, int splits);
 /* Debug / tuning: epilogue warps of the bf16-output GEMM kernels for the following calls: 8, 16, or
  * 0 = automatic (16 for the GELU / GELU-gradient epilogues, 8 otherwise). */
 void cnx_debug_gemm_epilogue_warps(int n);
+/* Debug / tuning: 64 = every bf16 epilogue stages through 64-column chunks (the layout of the
+ * epilogues with a residual operand); 0 = automatic (32-column chunks and one more operand stage for
+ * the 8-warp epilogues without a residual operand). */
+void cnx_debug_gemm_staging_chunk(int cols);
 /* Debug: clusters of `cluster_size` GEMM CTAs the device can hold at once (occupancy probe). */
 int cnx_debug_max_clusters(int cluster_size);
 /* Scratch bytes an op needs for the given problem (B*H*W*C*2 for CNX_OP_DWCONV_LN_BWD, else 0). */

@@ -147,13 +147,14 @@ def test_gemm_epilogues(cnx_lib):
     assert _rel(colsum, dz.double().sum(0)) < 1e-4      # sums of the rounded dz
 
 
-@pytest.mark.parametrize("epi_warps", [8, 16])
+@pytest.mark.parametrize("epi_warps", [8, 16, 64])
 @pytest.mark.parametrize("tuning", [(2, 0, 256, -1), (-1, 0, 128, -1), (-1, 1, 256, -1), (3, 1, 128, 3),
                                     (2, 1, 256, 5)])
 def test_gemm_forced_tilings(cnx_lib, tuning, epi_warps):
     """Every kernel instantiation (single CTA / CTA pair, 128- and 256-wide tiles, shallow operand
-    ring, forced split-K, 8 or 16 epilogue warps) gives the same results: ragged M, N and K,
-    several tiles per CTA."""
+    ring, forced split-K, 8 or 16 epilogue warps, 32- or 64-column staging chunks) gives the same
+    results: ragged M, N and K, several tiles per CTA.  epi_warps == 64 stands for 8 warps with
+    64-column staging chunks forced (8 alone: 32-column chunks where the epilogue has no residual)."""
     from image_classification_b200 import ops, _lib
     dev = _dev()
     torch.manual_seed(11)
@@ -165,7 +166,8 @@ def test_gemm_forced_tilings(cnx_lib, tuning, epi_warps):
     acc = A.double() @ Bm.double().t()
     lib = _lib.load()
     lib.cnx_debug_gemm_tuning(*tuning)
-    lib.cnx_debug_gemm_epilogue_warps(epi_warps)
+    lib.cnx_debug_gemm_epilogue_warps(8 if epi_warps == 64 else epi_warps)
+    lib.cnx_debug_gemm_staging_chunk(64 if epi_warps == 64 else 0)
     try:
         D = ops.gemm_bf16(A, Bm)
         z, h = ops.gemm_bf16(A, Bm, epilogue=ops.EPI_BIAS_GELU, bias=bias)
@@ -179,6 +181,7 @@ def test_gemm_forced_tilings(cnx_lib, tuning, epi_warps):
     finally:
         lib.cnx_debug_gemm_tuning(-1, -1, -1, -1)
         lib.cnx_debug_gemm_epilogue_warps(0)
+        lib.cnx_debug_gemm_staging_chunk(0)
     assert lib.cnx_debug_timeout_flag() == 0
     assert _rel(D, acc) < BF16_REL
     assert _rel(z, acc + bias.double()) < BF16_REL
